@@ -1,0 +1,431 @@
+// api.cu — the extern "C" surface declared in include/b2f.h.
+#include <cstring>
+#include <fstream>
+#include "internal.h"
+
+namespace b2f {
+
+static thread_local char g_error[1024] = "";
+
+void set_error(const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int status, const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+  return status;
+}
+
+int fail_cuda(cudaError_t e, const char* what)
+{
+  snprintf(g_error, sizeof(g_error), "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return B2F_ERR_CUDA;
+}
+
+} // namespace b2f
+
+using namespace b2f;
+
+#define B2F_CHECK_HANDLE(h)                                        \
+  if ((h) == nullptr)                                              \
+  return fail(B2F_ERR_INVALID_ARGUMENT, "%s: null handle", __func__)
+#define B2F_NEED_PATTERN(h)                                        \
+  if (!(h)->has_pattern)                                           \
+  return fail(B2F_ERR_STATE, "%s: b2f_compute_sparsity has not been called", __func__)
+
+extern "C" {
+
+int b2f_version(void) { return B2F_VERSION_MAJOR * 1000 + B2F_VERSION_MINOR; }
+
+const char* b2f_last_error_string(void) { return g_error; }
+
+const char* b2f_status_string(int status)
+{
+  switch (status) {
+  case B2F_OK: return "B2F_OK";
+  case B2F_ERR_INVALID_ARGUMENT: return "B2F_ERR_INVALID_ARGUMENT";
+  case B2F_ERR_NOT_IMPLEMENTED: return "B2F_ERR_NOT_IMPLEMENTED";
+  case B2F_ERR_CUDA: return "B2F_ERR_CUDA";
+  case B2F_ERR_STATE: return "B2F_ERR_STATE";
+  case B2F_ERR_NOT_FOUND: return "B2F_ERR_NOT_FOUND";
+  case B2F_ERR_OVERFLOW: return "B2F_ERR_OVERFLOW";
+  case B2F_ERR_NCCL: return "B2F_ERR_NCCL";
+  }
+  return "B2F_ERR_UNKNOWN";
+}
+
+int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle* out)
+{
+  if (!mesh || !options || !out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: null argument");
+  *out = nullptr;
+  // BSRFormat::initialize: "Only supports 2D and 3D" (femutils/BSRFormat.h:393-394)
+  if (mesh->dim != 2 && mesh->dim != 3)
+    return fail(B2F_ERR_NOT_IMPLEMENTED, "BSRFormat(initialize): Only supports 2D and 3D");
+  if (!((mesh->dim == 2 && mesh->nodes_per_cell == 3) || (mesh->dim == 3 && mesh->nodes_per_cell == 4)))
+    return fail(B2F_ERR_NOT_IMPLEMENTED, "only P1 triangles (dim 2) and P1 tetrahedra (dim 3) are supported (dim=%d, nodes_per_cell=%d)", mesh->dim, mesh->nodes_per_cell);
+  // BSRMatrix::initialize argument checks (femutils/BSRFormat.h:121-125)
+  if (options->block_size <= 0 || mesh->nb_node <= 0 || mesh->nb_cell < 0)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "BSRMatrix(initialize): arguments should be positive and not null (block_size=%d, nb_cell=%lld and nb_row=%lld)",
+                options->block_size, (long long)mesh->nb_cell, (long long)mesh->nb_node);
+  if (options->block_size > 3)
+    return fail(B2F_ERR_NOT_IMPLEMENTED, "block_size %d: only 1, 2 and 3 dofs per node are built", options->block_size);
+  if (options->block_size > mesh->nb_node)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "BSRMatrix(initialize): block_size should be less than nb_row");
+  if (mesh->nb_node > 2147483647ll)
+    return fail(B2F_ERR_OVERFLOW, "nb_node=%lld does not fit Int32 node ids", (long long)mesh->nb_node);
+  if (!mesh->cell_node && mesh->nb_cell > 0)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node is null");
+  if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(B2F_ERR_CUDA, "no CUDA device available (%s); libb200fem has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  b2f_context_s* h = new b2f_context_s();
+  h->mesh = *mesh;
+  h->opt = *options;
+  h->bs = options->block_size;
+  h->nv = mesh->nodes_per_cell;
+  h->per_block = options->use_csr == 0; // order_values_per_block = !does_linear_system_use_csr, BSRFormat.h:405
+  h->variant = options->assembly_variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : options->assembly_variant;
+  cudaGetDevice(&h->device);
+  *out = h;
+  return B2F_OK;
+}
+
+int b2f_destroy(b2f_handle h)
+{
+  if (!h)
+    return B2F_OK;
+  DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+                     &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
+                     &h->coords_stage, &h->ghost.send_rows, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_slot };
+  for (DevBuf* b : bufs)
+    b->release();
+  delete h;
+  return B2F_OK;
+}
+
+int b2f_set_coords(b2f_handle h, const double* coords)
+{
+  B2F_CHECK_HANDLE(h);
+  h->mesh.coords = coords;
+  return B2F_OK;
+}
+
+int b2f_compute_sparsity(b2f_handle h, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  return build_pattern(h, (cudaStream_t)stream);
+}
+
+int b2f_release_workspace(b2f_handle h)
+{
+  B2F_CHECK_HANDLE(h);
+  h->ws_keys_a.release();
+  h->ws_keys_b.release();
+  h->ws_tmp.release();
+  h->ws_i32a.release();
+  h->ws_i64.release();
+  return B2F_OK;
+}
+
+int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!op)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble: null operator");
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble: mesh coordinates are null");
+  return assemble(h, op, (cudaStream_t)stream);
+}
+
+int b2f_reset_values(b2f_handle h, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)h->nb_nz, (cudaStream_t)stream));
+  return B2F_OK;
+}
+
+int b2f_get_bsr(b2f_handle h, b2f_bsr_view* out)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_bsr: null output");
+  out->block_size = h->bs;
+  out->layout = h->per_block ? B2F_LAYOUT_PER_BLOCK : B2F_LAYOUT_PER_ROW;
+  out->nb_row = h->mesh.nb_node;
+  out->nb_col = h->nb_col;
+  out->nb_nz = h->nb_nz;
+  out->nb_edge = h->nb_edge;
+  out->row_index = h->row_index.as<int32_t>();
+  out->columns = h->columns.as<int32_t>();
+  out->nb_nz_per_row = h->nb_nz_per_row.as<int32_t>();
+  out->values = h->values.as<double>();
+  return B2F_OK;
+}
+
+int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_to_csr: null output");
+  if (!h->has_csr) {
+    int rc = to_csr(h, (cudaStream_t)stream);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  out->nb_row = h->mesh.nb_node * h->bs;
+  out->nb_value = h->nb_nz;
+  if (h->bs == 1) {
+    out->rows = h->row_index.as<int32_t>();
+    out->rows_nb_column = h->nb_nz_per_row.as<int32_t>();
+    out->columns = h->columns.as<int32_t>();
+  }
+  else {
+    out->rows = h->csr_rows.as<int32_t>();
+    out->rows_nb_column = h->csr_nbcol.as<int32_t>();
+    out->columns = h->csr_cols.as<int32_t>();
+  }
+  out->values = h->values.as<double>();
+  return B2F_OK;
+}
+
+int b2f_get_system(b2f_handle h, b2f_system_view* out)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_system: null output");
+  out->nb_dof = h->nb_dof;
+  out->rhs = h->rhs.as<double>();
+  out->forced_info = h->forced_info.as<uint8_t>();
+  out->forced_value = h->forced_value.as<double>();
+  out->elimination_info = h->elim_info.as<uint8_t>();
+  out->elimination_value = h->elim_value.as<double>();
+  return B2F_OK;
+}
+
+int b2f_get_stats(b2f_handle h, b2f_stats* out)
+{
+  B2F_CHECK_HANDLE(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_stats: null output");
+  memset(out, 0, sizeof(*out));
+  out->nb_edge = h->nb_edge;
+  out->nb_col = h->nb_col;
+  out->nb_nz = h->nb_nz;
+  if (h->counters.p) {
+    unsigned long long c[4] = { 0, 0, 0, 0 };
+    B2F_CUDA(cudaMemcpy(c, h->counters.p, sizeof(c), cudaMemcpyDeviceToHost));
+    out->columns_not_found = (int64_t)c[0];
+    out->gather_fallback_tiles = (int64_t)c[1];
+  }
+  out->workspace_bytes = (int64_t)(h->ws_keys_a.bytes + h->ws_keys_b.bytes + h->ws_tmp.bytes + h->ws_i32a.bytes + h->ws_i64.bytes);
+  const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+                          &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage };
+  for (const DevBuf* b : res)
+    out->resident_bytes += (int64_t)b->bytes;
+  return B2F_OK;
+}
+
+// findValueIndex, femutils/BSRFormat.h:145-171 (host walk over one row copied from the device).
+static int find_value_index(b2f_handle h, int64_t row, int64_t col, int64_t* idx)
+{
+  const int bs = h->bs;
+  if (row < 0 || col < 0 || row >= h->nb_dof || col >= h->nb_dof)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "dof (%lld,%lld) out of range", (long long)row, (long long)col);
+  const int64_t br = row / bs, bc = col / bs;
+  int32_t rr[2];
+  B2F_CUDA(cudaMemcpy(rr, h->row_index.as<int32_t>() + br, sizeof(rr), cudaMemcpyDeviceToHost));
+  const int k = rr[1] - rr[0];
+  std::vector<int32_t> cols((size_t)k);
+  B2F_CUDA(cudaMemcpy(cols.data(), h->columns.as<int32_t>() + rr[0], sizeof(int32_t) * (size_t)k, cudaMemcpyDeviceToHost));
+  for (int x = 0; x < k; ++x) {
+    if (cols[x] == bc) {
+      const int i = (int)(row % bs), j = (int)(col % bs);
+      if (!h->per_block)
+        *idx = (int64_t)rr[0] * bs * bs + (int64_t)bs * x + (int64_t)i * bs * k + j;
+      else
+        *idx = ((int64_t)rr[0] + x) * bs * bs + (i * bs + j);
+      return B2F_OK;
+    }
+  }
+  return fail(B2F_ERR_NOT_FOUND, "BSRMatrix(findValueIndex): Value not found");
+}
+
+int b2f_set_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double value)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  int64_t idx = 0;
+  int rc = find_value_index(h, row_dof, col_dof, &idx);
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(cudaMemcpy(h->values.as<double>() + idx, &value, sizeof(double), cudaMemcpyHostToDevice));
+  return B2F_OK;
+}
+
+int b2f_get_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double* value)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!value)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_value: null output");
+  int64_t idx = 0;
+  int rc = find_value_index(h, row_dof, col_dof, &idx);
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(cudaMemcpy(value, h->values.as<double>() + idx, sizeof(double), cudaMemcpyDeviceToHost));
+  return B2F_OK;
+}
+
+// BSRMatrix::dump, femutils/BSRFormat.h:285-307 (same text layout).
+int b2f_dump(b2f_handle h, const char* filename)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!filename)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dump: null filename");
+  const int64_t nn = h->mesh.nb_node;
+  std::vector<int32_t> ri((size_t)nn + 1), co((size_t)h->nb_col);
+  std::vector<double> va((size_t)h->nb_nz);
+  B2F_CUDA(cudaMemcpy(ri.data(), h->row_index.p, sizeof(int32_t) * ri.size(), cudaMemcpyDeviceToHost));
+  B2F_CUDA(cudaMemcpy(co.data(), h->columns.p, sizeof(int32_t) * co.size(), cudaMemcpyDeviceToHost));
+  B2F_CUDA(cudaMemcpy(va.data(), h->values.p, sizeof(double) * va.size(), cudaMemcpyDeviceToHost));
+  std::ofstream file(filename);
+  if (!file)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dump: cannot open %s", filename);
+  file << "size :" << h->nb_nz << "\n";
+  for (int64_t i = 0; i < nn; ++i) {
+    file << ri[i] << " ";
+    for (int32_t j = ri[i] + 1; j < ri[i + 1]; ++j)
+      file << "  ";
+  }
+  file << "\n";
+  for (int64_t i = 0; i < h->nb_col; ++i)
+    file << co[i] << " ";
+  file << "\n";
+  for (int64_t i = 0; i < h->nb_nz; ++i)
+    file << va[i] << " ";
+  file << "\n";
+  return B2F_OK;
+}
+
+int b2f_clear_values(b2f_handle h, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  return clear_values(h, (cudaStream_t)stream);
+}
+
+int b2f_rhs_fill(b2f_handle h, double value, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  return rhs_fill(h, value, (cudaStream_t)stream);
+}
+
+int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_constant_source: mesh coordinates are null");
+  return rhs_constant_source(h, qdot, (cudaStream_t)stream);
+}
+
+int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!bc || (bc->nb_face > 0 && !bc->face_node))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_neumann: null boundary condition / face list");
+  return rhs_neumann(h, bc, (cudaStream_t)stream);
+}
+
+int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_penalty: bad arguments (dof_index=%d, n=%lld)", dof_index, (long long)n);
+  return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, (cudaStream_t)stream);
+}
+
+int b2f_dirichlet_flag_elimination(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, int32_t mode, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids) || (mode != B2F_ELIMINATE_ROW && mode != B2F_ELIMINATE_ROW_COLUMN))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_elimination: bad arguments (dof_index=%d, n=%lld, mode=%d)", dof_index, (long long)n, mode);
+  return dirichlet_flag_elimination(h, node_ids, n, dof_index, value, mode, (cudaStream_t)stream);
+}
+
+int b2f_dirichlet_apply(b2f_handle h, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  return dirichlet_apply(h, (cudaStream_t)stream);
+}
+
+int b2f_spmv(b2f_handle h, const double* x, double* y, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!x || !y)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_spmv: null vector");
+  return spmv(h, x, y, (cudaStream_t)stream);
+}
+
+int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords_host, double* values_host, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!op || !coords_host)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_host: null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t cbytes = sizeof(double) * 3 * (size_t)h->mesh.nb_node;
+  B2F_CUDA(h->coords_stage.alloc(cbytes));
+  B2F_CUDA(cudaMemcpyAsync(h->coords_stage.p, coords_host, cbytes, cudaMemcpyHostToDevice, s));
+  const double* saved = h->mesh.coords;
+  h->mesh.coords = h->coords_stage.as<double>();
+  int rc = assemble(h, op, s);
+  h->mesh.coords = saved;
+  if (rc != B2F_OK)
+    return rc;
+  if (values_host)
+    B2F_CUDA(cudaMemcpyAsync(values_host, h->values.p, sizeof(double) * (size_t)h->nb_nz, cudaMemcpyDeviceToHost, s));
+  B2F_CUDA(cudaStreamSynchronize(s));
+  return B2F_OK;
+}
+
+int b2f_ghost_plan(b2f_handle h, int32_t rank, int32_t world, int64_t nb_ghost, const int32_t* ghost_node_host, const int32_t* ghost_owner_rank_host,
+                   const int64_t* node_global_id_host)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  return ghost_plan(h, rank, world, nb_ghost, ghost_node_host, ghost_owner_rank_host, node_global_id_host);
+}
+
+int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  return ghost_exchange(h, nccl_comm, (cudaStream_t)stream);
+}
+
+} // extern "C"

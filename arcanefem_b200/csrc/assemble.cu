@@ -1,0 +1,60 @@
+// assemble.cu — dispatch of b2f_assemble onto the kernel templates of include/b2f/assemble.cuh.
+// Replaces BSRFormat::assembleBilinear and its four kernels (femutils/BSRFormat.h:786-1111) together with the
+// shipped element callbacks (modules/poisson/FemModule.h:139-186, modules/elasticity/FemModule.h:112-152,
+// modules/heat/FemModule.cc:678-770).
+#include "internal.h"
+#include "b2f/assemble.cuh"
+
+namespace b2f {
+
+namespace {
+  template <class Op>
+  int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stream)
+  {
+    AssembleArgs A;
+    A.cell_node = h->mesh.cell_node;
+    A.coords = h->mesh.coords;
+    A.node_is_own = h->mesh.node_is_own;
+    A.nb_cell = h->mesh.nb_cell;
+    A.nb_node = h->mesh.nb_node;
+    A.row_index = h->row_index.as<int32_t>();
+    A.columns = h->columns.as<int32_t>();
+    A.values = h->values.as<double>();
+    A.nc_ptr = h->nc_ptr.as<int32_t>();
+    A.nc_list = h->nc_list.as<uint32_t>();
+    A.counters = h->counters.as<unsigned long long>();
+    A.accumulate = accumulate;
+    int variant = h->variant;
+    if (variant == B2F_ASM_DEFAULT)
+      variant = B2F_ASM_NODE_GATHER;
+    B2F_CUDA(launch_assemble<Op>(A, op, variant, h->per_block, h->nb_nz, stream));
+    return B2F_OK;
+  }
+} // namespace
+
+int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream)
+{
+  const int nv = h->nv, bs = h->bs;
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, stream));
+  switch (op->kind) {
+  case B2F_OP_LAPLACE:
+    if (bs != 1)
+      return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_LAPLACE needs block_size 1 (got %d)", bs);
+    return nv == 3 ? run(h, LaplaceTri{}, op->accumulate, stream) : run(h, LaplaceTet{}, op->accumulate, stream);
+  case B2F_OP_ELASTICITY:
+    if (nv == 3 && bs == 2)
+      return run(h, ElasticityTri{ op->lambda, op->mu2 }, op->accumulate, stream);
+    if (nv == 4 && bs == 3)
+      return run(h, ElasticityTet{ op->lambda, op->mu2 }, op->accumulate, stream);
+    return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_ELASTICITY needs block_size == dim (dim=%d, block_size=%d)", h->mesh.dim, bs);
+  case B2F_OP_HEAT:
+    if (bs != 1)
+      return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_HEAT needs block_size 1 (got %d)", bs);
+    return nv == 3 ? run(h, HeatTri{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream)
+                   : run(h, HeatTet{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream);
+  default:
+    return fail(B2F_ERR_NOT_IMPLEMENTED, "unknown operator kind %d", op->kind);
+  }
+}
+
+} // namespace b2f

@@ -1,0 +1,110 @@
+// internal.h — handle layout and helpers shared by the translation units of libb200fem.so.
+#pragma once
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "b2f.h"
+
+namespace b2f {
+
+void set_error(const char* fmt, ...);
+int fail(int status, const char* fmt, ...);
+int fail_cuda(cudaError_t e, const char* what);
+
+#define B2F_CUDA(expr)                                   \
+  do {                                                   \
+    cudaError_t b2f_e__ = (expr);                        \
+    if (b2f_e__ != cudaSuccess)                          \
+      return ::b2f::fail_cuda(b2f_e__, #expr);           \
+  } while (0)
+
+// Owning device buffer (plain cudaMalloc: buffers live as long as the pattern; temporaries are freed
+// explicitly by b2f_release_workspace).
+struct DevBuf
+{
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t alloc(size_t n)
+  {
+    if (p && bytes >= n && n * 2 >= bytes)
+      return cudaSuccess;
+    release();
+    if (n == 0)
+      n = 16;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e == cudaSuccess)
+      bytes = n;
+    else
+      p = nullptr;
+    return e;
+  }
+  void release()
+  {
+    if (p)
+      cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct GhostPlan
+{
+  bool ready = false;
+  int rank = 0, world = 1;
+  // per peer: rows this rank sends (its ghost rows owned by peer) / receives (its own rows that are ghosts on peer)
+  std::vector<int64_t> send_blocks, recv_blocks; // number of blocks exchanged with each peer
+  std::vector<int64_t> send_off, recv_off; // offsets (in blocks) into the packed buffers
+  DevBuf send_rows, send_vals, recv_vals, recv_slot; // device: row ids to pack; packed values; target value slots
+  int64_t total_send = 0, total_recv = 0;
+};
+
+} // namespace b2f
+
+struct b2f_context_s
+{
+  b2f_mesh_view mesh{};
+  b2f_options opt{};
+  int bs = 1, nv = 4, variant = B2F_ASM_NODE_GATHER;
+  bool per_block = true;
+  int device = 0;
+
+  bool has_pattern = false;
+  bool has_csr = false;
+  int64_t nb_col = 0, nb_nz = 0, nb_edge = 0, nb_dof = 0;
+
+  b2f::DevBuf row_index, columns, nb_nz_per_row, values; // BSRMatrix arrays
+  b2f::DevBuf nc_ptr, nc_list; // node -> cell lists
+  b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
+  b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
+  b2f::DevBuf counters; // 4 x u64
+  b2f::DevBuf ws_keys_a, ws_keys_b, ws_tmp, ws_i32a, ws_i64; // workspace
+  b2f::DevBuf coords_stage; // b2f_assemble_host
+  b2f::GhostPlan ghost;
+  int64_t last_not_found = 0;
+  int64_t last_fallback_tiles = 0;
+};
+
+namespace b2f {
+// sparsity.cu
+int build_pattern(b2f_context_s* h, cudaStream_t stream);
+// assemble.cu
+int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream);
+// boundary.cu
+int rhs_fill(b2f_context_s* h, double v, cudaStream_t s);
+int clear_values(b2f_context_s* h, cudaStream_t s);
+int rhs_constant_source(b2f_context_s* h, double qdot, cudaStream_t s);
+int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s);
+int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, cudaStream_t s);
+int dirichlet_flag_elimination(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, int mode, cudaStream_t s);
+int dirichlet_apply(b2f_context_s* h, cudaStream_t s);
+// convert.cu
+int to_csr(b2f_context_s* h, cudaStream_t s);
+int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
+// ghost.cu
+int ghost_plan(b2f_context_s* h, int rank, int world, int64_t nb_ghost, const int32_t* ghost_node, const int32_t* ghost_owner, const int64_t* node_gid);
+int ghost_exchange(b2f_context_s* h, void* comm, cudaStream_t s);
+} // namespace b2f

@@ -1,0 +1,390 @@
+// sparsity.cu — BSR sparsity build on device (sm_100a) + node->cell lists.
+//
+// Replaces BSRFormat::computeSparsityAtomic and its helpers (femutils/BSRFormat.h:602-770):
+//   K1 computeSortedEdges :602-651   cell -> packed edge keys, device radix sort
+//   K3 computeNeighbors   :656-672   degree count on the last key of every run
+//   K4 computeRowIndex    :677-688   exclusive scan (here with the closing entry, nb_node+1 values)
+//   K5 computeColumns     :703-744   diagonal first, then neighbours
+//   K6 computeNzPerRowArray :435-474
+// and the host-side edge count of BSRFormat::computeNbEdge (:370-385), which falls out of the scan.
+//
+// Differences by design (results identical to the reference executed in key order):
+//   * keys are packed as (min << nbits) | max with nbits = bit width of nb_node-1, so the radix sort runs over
+//     2*nbits significant bits instead of 64 (same order as the reference's (min<<32)|max keys);
+//   * the reference fills neighbour slots in atomic-arrival order, which is non-deterministic on a GPU; here every
+//     row is then sorted (warp rank sort), giving the canonical order "diagonal, then ascending ids";
+//   * all sizes are 64-bit internally; Int32 overflow of a per-rank count is reported, not wrapped.
+#include <cub/cub.cuh>
+#include "internal.h"
+
+namespace b2f {
+
+namespace {
+
+  __device__ __forceinline__ unsigned long long pack_key(int32_t n0, int32_t n1, int shift)
+  {
+    const unsigned mn = (unsigned)(n0 > n1 ? n1 : n0);
+    const unsigned mx = (unsigned)(n0 > n1 ? n0 : n1);
+    return ((unsigned long long)mn << shift) | (unsigned long long)mx;
+  }
+
+  // K1: one thread per cell (femutils/BSRFormat.h:616-643; edge order (01)(02)(12) / (01)(02)(03)(12)(13)(23)).
+  template <int NV>
+  __global__ void __launch_bounds__(256) k_expand_edges(const int32_t* __restrict__ cell_node, long long nb_cell, long long nb_node, int shift,
+                                                        unsigned long long* __restrict__ keys, unsigned long long* __restrict__ counters)
+  {
+    const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= nb_cell)
+      return;
+    int32_t n[NV];
+    if (NV == 4) {
+      const int4 v = __ldg(reinterpret_cast<const int4*>(cell_node) + cell);
+      n[0] = v.x;
+      n[1] = v.y;
+      n[2] = v.z;
+      n[NV - 1] = v.w;
+    }
+    else {
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+        n[k] = __ldg(cell_node + cell * NV + k);
+    }
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      bad |= (n[k] < 0 || n[k] >= nb_node);
+    if (bad) {
+      atomicAdd(counters + 2, 1ull);
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+        n[k] = 0;
+    }
+    constexpr int EPE = (NV == 3) ? 3 : 6;
+    unsigned long long* e = keys + cell * EPE;
+    if (NV == 3) {
+      e[0] = pack_key(n[0], n[1], shift);
+      e[1] = pack_key(n[0], n[2], shift);
+      e[2] = pack_key(n[1], n[2], shift);
+    }
+    else {
+      e[0] = pack_key(n[0], n[1], shift);
+      e[1] = pack_key(n[0], n[2], shift);
+      e[2] = pack_key(n[0], n[NV - 1], shift);
+      e[3] = pack_key(n[1], n[2], shift);
+      e[4] = pack_key(n[1], n[NV - 1], shift);
+      e[EPE - 1] = pack_key(n[2], n[NV - 1], shift);
+    }
+  }
+
+  __global__ void k_fill_i32(int32_t* p, long long n, int32_t v)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+      p[i] = v;
+  }
+
+  // K3: degree count, one thread per sorted key, only the last key of a run counts (BSRFormat.h:661-671).
+  __global__ void __launch_bounds__(256) k_count_degrees(const unsigned long long* __restrict__ keys, long long n, int shift, int32_t* __restrict__ deg)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+      return;
+    const unsigned long long cur = keys[i];
+    if (i == n - 1 || cur != keys[i + 1]) {
+      const unsigned long long mask = (1ull << shift) - 1ull;
+      atomicAdd(deg + (int32_t)(cur >> shift), 1);
+      atomicAdd(deg + (int32_t)(cur & mask), 1);
+    }
+  }
+
+  // K5: diagonal (BSRFormat.h:712-717) ...
+  __global__ void k_fill_diagonal(const int32_t* __restrict__ row_index, long long nb_node, int32_t* __restrict__ columns)
+  {
+    const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < nb_node)
+      columns[row_index[n]] = (int32_t)n;
+  }
+
+  // ... then both directions of every unique edge (registerEdgeInColumns, BSRFormat.h:693-698,732-742).
+  __global__ void __launch_bounds__(256) k_fill_neighbours(const unsigned long long* __restrict__ keys, long long n, int shift, const int32_t* __restrict__ row_index,
+                                                           int32_t* __restrict__ cursor, int32_t* __restrict__ columns)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+      return;
+    const unsigned long long cur = keys[i];
+    if (i == n - 1 || cur != keys[i + 1]) {
+      const unsigned long long mask = (1ull << shift) - 1ull;
+      const int32_t n0 = (int32_t)(cur >> shift), n1 = (int32_t)(cur & mask);
+      columns[row_index[n0] + atomicAdd(cursor + n0, 1)] = n1;
+      columns[row_index[n1] + atomicAdd(cursor + n1, 1)] = n0;
+    }
+  }
+
+  // Sort seg[0..len) ascending, one warp per segment.  Rank sort: every element counts the elements smaller than
+  // itself (ties broken by position) and is written at that rank.
+  template <class T>
+  __device__ __forceinline__ void warp_sort_segment(T* seg, int len, unsigned lane)
+  {
+    if (len <= 1)
+      return;
+    if (len <= 32) {
+      const T v = (int)lane < len ? seg[lane] : T(0);
+      int rank = 0;
+      for (int j = 0; j < len; ++j) {
+        const T o = __shfl_sync(0xffffffffu, v, j);
+        rank += (o < v) || (o == v && j < (int)lane);
+      }
+      __syncwarp();
+      if ((int)lane < len)
+        seg[rank] = v;
+      return;
+    }
+    constexpr int PER = 8;
+    if (len <= 32 * PER) {
+      T v[PER];
+      int rank[PER];
+#pragma unroll
+      for (int p = 0; p < PER; ++p) {
+        const int idx = (int)lane + 32 * p;
+        v[p] = idx < len ? seg[idx] : T(0);
+        rank[p] = 0;
+      }
+      for (int j = 0; j < len; ++j) {
+        const T o = seg[j];
+#pragma unroll
+        for (int p = 0; p < PER; ++p) {
+          const int idx = (int)lane + 32 * p;
+          rank[p] += (o < v[p]) || (o == v[p] && j < idx);
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int p = 0; p < PER; ++p)
+        if ((int)lane + 32 * p < len)
+          seg[rank[p]] = v[p];
+      return;
+    }
+    if (lane == 0) { // very long segment: serial insertion sort
+      for (int i = 1; i < len; ++i) {
+        const T x = seg[i];
+        int j = i - 1;
+        while (j >= 0 && seg[j] > x) {
+          seg[j + 1] = seg[j];
+          --j;
+        }
+        seg[j + 1] = x;
+      }
+    }
+  }
+
+  // Sort the neighbour part of every row (entries 1..k-1; entry 0 is the diagonal) / every node->cell list.
+  template <class T>
+  __global__ void __launch_bounds__(256) k_sort_segments(const int32_t* __restrict__ ptr, long long nb_seg, int skip, T* __restrict__ data)
+  {
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31u;
+    if (w >= nb_seg)
+      return;
+    const int32_t b = ptr[w] + skip, e = ptr[w + 1];
+    warp_sort_segment<T>(data + b, e - b, lane);
+  }
+
+  // K6 (BSRFormat.h:450-470)
+  __global__ void k_nz_per_row(const int32_t* __restrict__ row_index, long long nb_node, int32_t* __restrict__ out)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nb_node)
+      out[i] = row_index[i + 1] - row_index[i];
+  }
+
+  __global__ void __launch_bounds__(256) k_count_node_cells(const int32_t* __restrict__ cell_node, long long n_entries, int32_t* __restrict__ cnt)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_entries)
+      atomicAdd(cnt + cell_node[i], 1);
+  }
+
+  template <int NV>
+  __global__ void __launch_bounds__(256) k_fill_node_cells(const int32_t* __restrict__ cell_node, long long nb_cell, const int32_t* __restrict__ nc_ptr,
+                                                           int32_t* __restrict__ cursor, uint32_t* __restrict__ nc_list)
+  {
+    const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= nb_cell)
+      return;
+#pragma unroll
+    for (int a = 0; a < NV; ++a) {
+      const int32_t node = cell_node[cell * NV + a];
+      nc_list[nc_ptr[node] + atomicAdd(cursor + node, 1)] = (uint32_t)(cell * 4 + a);
+    }
+  }
+
+  __global__ void k_narrow_offsets(const long long* __restrict__ in, long long n, int32_t* __restrict__ out)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+      out[i] = (int32_t)in[i];
+  }
+
+  __global__ void k_widen_counts(const int32_t* __restrict__ in, long long n, long long* __restrict__ out)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+      out[i] = in[i];
+    else if (i == n)
+      out[i] = 0; // closing entry: the scan's last output is the total
+  }
+
+  inline unsigned grid_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+  // counts[0..n) (int32) -> offsets[0..n] (int32), total returned on the host (synchronises the stream).
+  int scan_counts(b2f_context_s* h, const int32_t* counts, long long n, int32_t* offsets, long long* total_out, cudaStream_t stream)
+  {
+    B2F_CUDA(h->ws_i64.alloc(sizeof(long long) * (size_t)(n + 1)));
+    long long* tmp = h->ws_i64.as<long long>();
+    k_widen_counts<<<grid_for(n + 1, 256), 256, 0, stream>>>(counts, n, tmp);
+    size_t temp_bytes = 0;
+    B2F_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, tmp, tmp, n + 1, stream));
+    B2F_CUDA(h->ws_tmp.alloc(temp_bytes));
+    B2F_CUDA(cub::DeviceScan::ExclusiveSum(h->ws_tmp.p, temp_bytes, tmp, tmp, n + 1, stream));
+    long long total = 0;
+    B2F_CUDA(cudaMemcpyAsync(&total, tmp + n, sizeof(long long), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    if (total > 2147483647ll)
+      return fail(B2F_ERR_OVERFLOW, "per-rank count %lld does not fit Int32 indices (femutils/BSRFormat.h:401-402); split the mesh over more ranks", total);
+    k_narrow_offsets<<<grid_for(n + 1, 256), 256, 0, stream>>>(tmp, n + 1, offsets);
+    B2F_CUDA(cudaGetLastError());
+    *total_out = total;
+    return B2F_OK;
+  }
+
+} // namespace
+
+int build_pattern(b2f_context_s* h, cudaStream_t stream)
+{
+  const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
+  const int nv = h->nv;
+  const int epe = (nv == 3) ? 3 : 6;
+  const long long nkeys = nc * epe;
+  if (nc * 4 > 4294967295ll || nc * (long long)nv > 2147483647ll)
+    return fail(B2F_ERR_OVERFLOW, "nb_cell=%lld is too large for one rank (node->cell entries are 32-bit)", nc);
+  int shift = 1;
+  while ((1ll << shift) < nn)
+    ++shift;
+
+  h->has_pattern = false;
+  h->has_csr = false;
+  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 4));
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
+  unsigned long long* counters = h->counters.as<unsigned long long>();
+
+  // --- K1: edge keys + radix sort over the 2*shift significant bits
+  B2F_CUDA(h->ws_keys_a.alloc(sizeof(unsigned long long) * (size_t)nkeys));
+  B2F_CUDA(h->ws_keys_b.alloc(sizeof(unsigned long long) * (size_t)nkeys));
+  unsigned long long* ka = h->ws_keys_a.as<unsigned long long>();
+  unsigned long long* kb = h->ws_keys_b.as<unsigned long long>();
+  if (nc > 0) {
+    if (nv == 3)
+      k_expand_edges<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, nn, shift, ka, counters);
+    else
+      k_expand_edges<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, nn, shift, ka, counters);
+    B2F_CUDA(cudaGetLastError());
+  }
+  cub::DoubleBuffer<unsigned long long> keys(ka, kb);
+  if (nkeys > 0) {
+    size_t temp_bytes = 0;
+    B2F_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, temp_bytes, keys, nkeys, 0, 2 * shift, stream));
+    B2F_CUDA(h->ws_tmp.alloc(temp_bytes));
+    B2F_CUDA(cub::DeviceRadixSort::SortKeys(h->ws_tmp.p, temp_bytes, keys, nkeys, 0, 2 * shift, stream));
+  }
+  const unsigned long long* sorted = keys.Current();
+
+  // --- K3/K4: degrees (diagonal pre-counted) and row_index
+  B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  int32_t* deg = h->ws_i32a.as<int32_t>();
+  k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(deg, nn, 1);
+  if (nkeys > 0)
+    k_count_degrees<<<grid_for(nkeys, 256), 256, 0, stream>>>(sorted, nkeys, shift, deg);
+  B2F_CUDA(cudaGetLastError());
+  B2F_CUDA(h->row_index.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  long long nb_col = 0;
+  int rc = scan_counts(h, deg, nn, h->row_index.as<int32_t>(), &nb_col, stream);
+  if (rc != B2F_OK)
+    return rc;
+  {
+    unsigned long long host_counters[4];
+    B2F_CUDA(cudaMemcpyAsync(host_counters, counters, sizeof(host_counters), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    if (host_counters[2] != 0)
+      return fail(B2F_ERR_INVALID_ARGUMENT, "cell_node holds %llu cells with node ids outside [0, nb_node)", host_counters[2]);
+  }
+  const long long nb_nz = nb_col * h->bs * h->bs;
+  if (nb_nz > 2147483647ll)
+    return fail(B2F_ERR_OVERFLOW, "nb_non_zero_value=%lld does not fit the reference's Int32 (femutils/BSRFormat.h:402)", nb_nz);
+  h->nb_col = nb_col;
+  h->nb_nz = nb_nz;
+  h->nb_edge = (nb_col - nn) / 2;
+
+  // --- K5: columns, then canonical order inside every row
+  B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)nb_col));
+  B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
+  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)nb_nz, stream)); // BSRMatrix::initialize fills 0, BSRFormat.h:136
+  int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724
+  k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(cursor, nn, 1);
+  k_fill_diagonal<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->columns.as<int32_t>());
+  if (nkeys > 0)
+    k_fill_neighbours<<<grid_for(nkeys, 256), 256, 0, stream>>>(sorted, nkeys, shift, h->row_index.as<int32_t>(), cursor, h->columns.as<int32_t>());
+  k_sort_segments<int32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, 1, h->columns.as<int32_t>());
+  B2F_CUDA(cudaGetLastError());
+
+  // --- K6
+  B2F_CUDA(h->nb_nz_per_row.alloc(sizeof(int32_t) * (size_t)nn));
+  k_nz_per_row<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->nb_nz_per_row.as<int32_t>());
+  B2F_CUDA(cudaGetLastError());
+
+  // --- node -> cell lists (the reference takes them from Arcane's nodeCell() connectivity, BSRFormat.h:942)
+  B2F_CUDA(cudaStreamSynchronize(stream));
+  h->ws_keys_a.release();
+  h->ws_keys_b.release();
+  int32_t* cnt = deg;
+  B2F_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
+  if (nc > 0)
+    k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, nc * nv, cnt);
+  B2F_CUDA(cudaGetLastError());
+  B2F_CUDA(h->nc_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  long long nb_adj = 0;
+  rc = scan_counts(h, cnt, nn, h->nc_ptr.as<int32_t>(), &nb_adj, stream);
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(h->nc_list.alloc(sizeof(uint32_t) * (size_t)nb_adj));
+  B2F_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
+  if (nc > 0) {
+    if (nv == 3)
+      k_fill_node_cells<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+    else
+      k_fill_node_cells<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+  }
+  k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
+  B2F_CUDA(cudaGetLastError());
+
+  // --- linear-system state (HypreDoFLinearSystem.cc:224-242)
+  h->nb_dof = nn * h->bs;
+  B2F_CUDA(h->rhs.alloc(sizeof(double) * (size_t)h->nb_dof));
+  B2F_CUDA(h->forced_value.alloc(sizeof(double) * (size_t)h->nb_dof));
+  B2F_CUDA(h->elim_value.alloc(sizeof(double) * (size_t)h->nb_dof));
+  B2F_CUDA(h->forced_info.alloc((size_t)h->nb_dof));
+  B2F_CUDA(h->elim_info.alloc((size_t)h->nb_dof));
+  B2F_CUDA(cudaMemsetAsync(h->rhs.p, 0, sizeof(double) * (size_t)h->nb_dof, stream));
+  B2F_CUDA(cudaMemsetAsync(h->forced_value.p, 0, sizeof(double) * (size_t)h->nb_dof, stream));
+  B2F_CUDA(cudaMemsetAsync(h->elim_value.p, 0, sizeof(double) * (size_t)h->nb_dof, stream));
+  B2F_CUDA(cudaMemsetAsync(h->forced_info.p, 0, (size_t)h->nb_dof, stream));
+  B2F_CUDA(cudaMemsetAsync(h->elim_info.p, 0, (size_t)h->nb_dof, stream));
+  B2F_CUDA(cudaStreamSynchronize(stream));
+  h->ws_i64.release();
+  h->ws_tmp.release();
+  h->ws_i32a.release();
+  h->has_pattern = true;
+  return B2F_OK;
+}
+
+} // namespace b2f

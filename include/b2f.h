@@ -1,0 +1,241 @@
+/*
+ * b2f.h — C ABI of libb200fem.so: B200-native (sm_100a) finite-element bilinear-form assembly.
+ *
+ * Drop-in boundary for ArcaneFEM's femutils assembly hot path (reference: toutane/arcanefem; all
+ * file:line citations are relative to the reference root).  In the reference this path is not an FFI
+ * but a set of header-only templates compiled with each module:
+ *   femutils/BSRFormat.h              BSRMatrix<BS> / BSRFormat<NB_DOF>
+ *   femutils/ArcaneFemFunctionsGpu.h  element helpers, RHS and Dirichlet flagging kernels
+ *   femutils/HypreDoFLinearSystem.cc  _applyRowElimination / _applyForcedValuesToLhs (:319-382)
+ *   femutils/DoFLinearSystem.h        CSRFormatView hand-off (:42-76)
+ * A C ABI cannot carry a device lambda, so the reference's `Function compute_element_matrix` template
+ * parameter (BSRFormat.h:786-787,1105) becomes an operator enum + parameter block (b2f_operator); the
+ * header-only C++ shim in include/arcanefem_b200/ restores the reference's names on top of this file and
+ * include/b2f/assemble.cuh keeps a template entry point for user-written element functors.
+ *
+ * Conventions: every function returns B2F_OK (0) or a negative b2f_status; no exception crosses the
+ * boundary; b2f_last_error_string() describes the last failure on the calling thread.  All data pointers
+ * are device (or managed) pointers unless the name says host.  `stream` is a cudaStream_t passed as
+ * void*.  Calls on one handle are not thread-safe and are ordered on the stream given.  The library
+ * has no CPU fallback: without a CUDA device every compute entry point fails with B2F_ERR_CUDA.
+ */
+#ifndef B2F_H
+#define B2F_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2F_VERSION_MAJOR 0
+#define B2F_VERSION_MINOR 1
+
+typedef struct b2f_context_s* b2f_handle;
+typedef void* b2f_stream; /* cudaStream_t */
+
+typedef enum b2f_status {
+  B2F_OK = 0,
+  B2F_ERR_INVALID_ARGUMENT = -1, /* reference: ARCANE_THROW(ArgumentException), BSRFormat.h:121-125 */
+  B2F_ERR_NOT_IMPLEMENTED = -2, /* reference: NotImplementedException, BSRFormat.h:393-394 */
+  B2F_ERR_CUDA = -3,
+  B2F_ERR_STATE = -4, /* call order violated (e.g. assemble before compute_sparsity) */
+  B2F_ERR_NOT_FOUND = -5, /* reference: std::runtime_error("Value not found"), BSRFormat.h:170 */
+  B2F_ERR_OVERFLOW = -6, /* a per-rank count does not fit the reference's Int32 indices */
+  B2F_ERR_NCCL = -7
+} b2f_status;
+
+/* Value layout, femutils/BSRFormat.h:145-171 (findValueIndex) and :405. */
+typedef enum b2f_layout {
+  B2F_LAYOUT_PER_BLOCK = 0, /* order_values_per_block = true  (Aleph path): p*BS*BS + i*BS + j           */
+  B2F_LAYOUT_PER_ROW = 1 /* order_values_per_block = false (Hypre/CSR): row_index[r]*BS*BS + i*BS*k + x*BS + j */
+} b2f_layout;
+
+/* Scatter-add variant, femutils/BSRFormat.h:1105-1111. */
+typedef enum b2f_assembly_variant {
+  B2F_ASM_DEFAULT = 0, /* the library's choice (node gather) */
+  B2F_ASM_CELL_ATOMIC = 1, /* cell-wise, one fp64 atomic per entry (BSRFormat.h:786-898) */
+  B2F_ASM_CELL_ATOMIC_WARPAGG = 2, /* cell-wise, same-address adds pre-reduced inside the warp */
+  B2F_ASM_NODE_GATHER = 3 /* node-wise, atomic-free, deterministic (BSRFormat.h:937-1068) */
+} b2f_assembly_variant;
+
+typedef enum b2f_operator_kind {
+  B2F_OP_LAPLACE = 0, /* modules/poisson/FemModule.h:139-147 (tri), :177-186 (tet); BS = 1 */
+  B2F_OP_ELASTICITY = 1, /* modules/elasticity/FemModule.h:112-152 (tri, BS = 2); tet BS = 3 by extension */
+  B2F_OP_HEAT = 2 /* modules/heat/FemModule.cc:678-770 (tri, BS = 1): lambda*stiffness + mass/dt */
+} b2f_operator_kind;
+
+/* Dirichlet elimination modes stored in elimination_info (HypreDoFLinearSystem.cc:237-241,
+ * AlephDoFLinearSystem.cc ELIMINATE_ROW_COLUMN). */
+enum { B2F_ELIMINATE_NONE = 0, B2F_ELIMINATE_ROW = 1, B2F_ELIMINATE_ROW_COLUMN = 2 };
+
+/*
+ * Mesh as the reference's kernels see it: cellNode() connectivity (fixed arity, Int32 local ids),
+ * VariableNodeReal3 coordinates (array of 3 x fp64, z present even in 2D), isOwn(node) flags
+ * (femutils/BSRFormat.h:789-792).  The library never frees these pointers and reads them at every
+ * call that needs them, so they must stay valid while the handle is used.
+ */
+typedef struct b2f_mesh_view {
+  int32_t dim; /* 2 or 3 */
+  int32_t nodes_per_cell; /* 3 (Triangle3) or 4 (Tetraedron4) */
+  int64_t nb_cell;
+  int64_t nb_node;
+  const int32_t* cell_node; /* [nb_cell * nodes_per_cell] */
+  const double* coords; /* [nb_node * 3], xyz interleaved */
+  const uint8_t* node_is_own; /* [nb_node] or NULL = every node is own */
+} b2f_mesh_view;
+
+/* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
+typedef struct b2f_options {
+  int32_t block_size; /* NB_DOF: 1, 2 or 3 */
+  int32_t use_csr; /* does_linear_system_use_csr: 1 -> B2F_LAYOUT_PER_ROW, 0 -> B2F_LAYOUT_PER_BLOCK */
+  int32_t assembly_variant; /* b2f_assembly_variant; the reference's use_atomic_free=true maps to NODE_GATHER */
+  int32_t reserved;
+} b2f_options;
+
+typedef struct b2f_operator {
+  int32_t kind; /* b2f_operator_kind */
+  int32_t accumulate; /* 0: values are overwritten (zero-fill + add); 1: added to current values */
+  double lambda; /* elasticity: Lame lambda; heat: conductivity when cell_lambda == NULL */
+  double mu2; /* elasticity: 2*mu (modules/elasticity/FemModule.cc:133) */
+  double inv_dt; /* heat: 1/dt */
+  const double* cell_lambda; /* heat: per-cell conductivity [nb_cell] or NULL */
+} b2f_operator;
+
+/* BSRMatrix accessors, femutils/BSRFormat.h:312-320.  row_index has nb_row+1 entries (the reference
+ * exposes the first nb_row, :138; entry nb_row equals nb_col). */
+typedef struct b2f_bsr_view {
+  int32_t block_size;
+  int32_t layout; /* b2f_layout */
+  int64_t nb_row; /* block rows = nb_node */
+  int64_t nb_col; /* stored blocks = 2*nb_edge + nb_node (BSRFormat.h:401) */
+  int64_t nb_nz; /* scalars = BS*BS*nb_col (BSRFormat.h:402) */
+  int64_t nb_edge;
+  const int32_t* row_index;
+  const int32_t* columns;
+  const int32_t* nb_nz_per_row;
+  double* values;
+} b2f_bsr_view;
+
+/* CSRFormatView, femutils/DoFLinearSystem.h:42-76; rows has nb_row+1 entries (reference: nb_row). */
+typedef struct b2f_csr_view {
+  int64_t nb_row; /* BS * nb_node */
+  int64_t nb_value;
+  const int32_t* rows;
+  const int32_t* rows_nb_column;
+  const int32_t* columns;
+  double* values;
+} b2f_csr_view;
+
+/* Per-DoF state of the linear system the Dirichlet/RHS kernels write
+ * (femutils/HypreDoFLinearSystem.cc:224-242); dof = node*BS + i (femutils/FemDoFsOnNodes.cc:79-109). */
+typedef struct b2f_system_view {
+  int64_t nb_dof;
+  double* rhs;
+  uint8_t* forced_info;
+  double* forced_value;
+  uint8_t* elimination_info;
+  double* elimination_value;
+} b2f_system_view;
+
+/* Neumann group, femutils/ArcaneFemFunctionsGpu.h:621-677 (2D, faces = edges) and :711-768 (3D). */
+typedef struct b2f_neumann {
+  int64_t nb_face;
+  const int32_t* face_node; /* [nb_face * (dim)] node ids of each boundary face */
+  const uint8_t* face_outside; /* isSubDomainBoundaryOutside per face, or NULL = all outside */
+  int32_t has_value; /* 1: scalar `value`; 0: flux vector (value_x, value_y, value_z) . normal */
+  int32_t reserved;
+  double value;
+  double value_x, value_y, value_z;
+} b2f_neumann;
+
+typedef struct b2f_stats {
+  int64_t nb_edge;
+  int64_t nb_col;
+  int64_t nb_nz;
+  int64_t columns_not_found; /* (row,col) pairs the last assemble could not place (reference: silently skipped) */
+  int64_t workspace_bytes; /* temporary device bytes held (sort buffers); 0 after b2f_release_workspace */
+  int64_t resident_bytes; /* device bytes owned by the handle, workspace excluded */
+  int64_t gather_fallback_tiles; /* node-gather tiles that overflowed shared memory and ran on the global path */
+} b2f_stats;
+
+int b2f_version(void);
+const char* b2f_last_error_string(void);
+const char* b2f_status_string(int status);
+
+/* BSRFormat ctor + initialize (BSRFormat.h:358-363,389-409).  Sizes are not needed up front: the edge
+ * count the reference computes on the host (:370-385) is a by-product of b2f_compute_sparsity. */
+int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle* out);
+int b2f_destroy(b2f_handle h);
+/* Re-point the handle at new coordinate / ownership arrays (same connectivity). */
+int b2f_set_coords(b2f_handle h, const double* coords);
+
+/* computeSparsity (BSRFormat.h:775-781): K1-K6, canonical pattern = diagonal first, then ascending
+ * neighbour ids (what :602-744 produces when executed in key order).  Also builds the node->cell lists
+ * used by the node-gather variant.  Synchronises `stream` once (the block count must reach the host). */
+int b2f_compute_sparsity(b2f_handle h, b2f_stream stream);
+int b2f_release_workspace(b2f_handle h);
+
+/* assembleBilinear (BSRFormat.h:1105-1111). */
+int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream);
+/* resetMatrixValues (BSRFormat.h:1120-1123). */
+int b2f_reset_values(b2f_handle h, b2f_stream stream);
+
+int b2f_get_bsr(b2f_handle h, b2f_bsr_view* out);
+/* BSRMatrix::toCsr + CSRFormatView (BSRFormat.h:194-256,414-430): zero-copy alias of the BSR arrays when
+ * BS = 1; device expansion of rows/columns when BS > 1 (values alias; needs B2F_LAYOUT_PER_ROW). */
+int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream);
+int b2f_get_system(b2f_handle h, b2f_system_view* out);
+int b2f_get_stats(b2f_handle h, b2f_stats* out);
+
+/* BSRMatrix::setValue / getValue by scalar (row dof, col dof), BSRFormat.h:176-189 (host convenience,
+ * synchronous).  B2F_ERR_NOT_FOUND when the block is not in the pattern. */
+int b2f_set_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double value);
+int b2f_get_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double* value);
+/* BSRMatrix::dump (BSRFormat.h:285-307), same text format. */
+int b2f_dump(b2f_handle h, const char* filename);
+
+/* DoFLinearSystem::clearValues (HypreDoFLinearSystem.cc:184-191) + rhs.fill(0). */
+int b2f_clear_values(b2f_handle h, b2f_stream stream);
+int b2f_rhs_fill(b2f_handle h, double value, b2f_stream stream);
+/* BoundaryConditions{2D,3D}::applyConstantSourceToRhs (ArcaneFemFunctionsGpu.h:402-429,605,695). */
+int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream);
+/* BoundaryConditions{2D,3D}::applyNeumannToRhs (ArcaneFemFunctionsGpu.h:621-677,711-768). */
+int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream);
+/* applyDirichletToNodeGroupViaPenalty (ArcaneFemFunctionsGpu.h:434-456). */
+int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream);
+/* applyDirichletToNodeGroupViaRowElimination<MODE> (ArcaneFemFunctionsGpu.h:461-482). */
+int b2f_dirichlet_flag_elimination(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, int32_t mode, b2f_stream stream);
+/* _applyRowElimination + _applyForcedValuesToLhs (HypreDoFLinearSystem.cc:319-382), plus row+column
+ * elimination with the semantics of AlephDoFLinearSystem.cc:501-583, on the device-resident matrix. */
+int b2f_dirichlet_apply(b2f_handle h, b2f_stream stream);
+
+/* Device BSR SpMV check: y = A x, x and y of length BS*nb_node. */
+int b2f_spmv(b2f_handle h, const double* x, double* y, b2f_stream stream);
+
+/*
+ * Host-buffer entry point (what a caller without device-resident data uses; timed as `e2e` by bench.py):
+ * copies coordinates host->device into the handle's own staging buffer, assembles, and copies the values
+ * device->host.  Pinned host memory recommended.  values_host may be NULL (skip the read-back).
+ */
+int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords_host, double* values_host, b2f_stream stream);
+
+/*
+ * Multi-GPU (one rank per GPU, disjoint cell partition): rows of ghost nodes (node_is_own == 0) hold
+ * this rank's partial sums; b2f_ghost_exchange sends them to the owner rank over NCCL (ncclSend/ncclRecv
+ * grouped per neighbour) and adds them into the owner's rows.  `comm` is an ncclComm_t.
+ * Plan arrays are host pointers: for every ghost node its owner rank and its local id on the owner.
+ */
+int b2f_ghost_plan(b2f_handle h, int32_t rank, int32_t world, int64_t nb_ghost, const int32_t* ghost_node_host, const int32_t* ghost_owner_rank_host,
+                   const int64_t* node_global_id_host);
+int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream);
+/* NCCL bootstrap helpers so a host without its own NCCL binding can create the communicator. */
+int b2f_nccl_unique_id(void* id128_out_host);
+int b2f_nccl_comm_init(const void* id128_host, int32_t rank, int32_t world, void** comm_out);
+int b2f_nccl_comm_destroy(void* comm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2F_H */

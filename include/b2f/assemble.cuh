@@ -1,0 +1,370 @@
+// assemble.cuh — scatter-add of P1 element matrices into BSR values (sm_100a).
+//
+// Template entry point behind b2f_assemble(); also the escape hatch that keeps the reference's
+// `template <class Function> assembleBilinear(Function)` (femutils/BSRFormat.h:1105-1111) usable with a
+// user-written operator: any type satisfying the concept in element_ops.cuh can be passed to
+// b2f::launch_assemble<Op>() from a .cu file of the caller.
+//
+// Two kernels, mirroring the reference's two variants:
+//   k_cell_atomic   cell-wise (BSRFormat.h:786-898): one thread per cell, Ke blocks in registers, column slot by
+//                   binary search in the sorted row, fp64 RED per scalar; optional warp pre-reduction of
+//                   same-address adds (__match_any_sync) so a warp issues one RED per distinct block.
+//   k_node_gather   node-wise, atomic-free (BSRFormat.h:937-1068): a CTA owns ROWS consecutive block rows, whose
+//                   values are one contiguous slab.  The slab's accumulators, its column indices and the rows'
+//                   node->cell lists are staged in shared memory; one thread per row walks its cells, permutes each
+//                   cell so the row node is local vertex 0 (even permutation), computes only row 0 of Ke and adds
+//                   it into its private accumulators; the slab is then stored with coalesced vector stores — every
+//                   value is written exactly once and no zero-fill pass is needed.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "element_ops.cuh"
+
+namespace b2f {
+
+struct AssembleArgs
+{
+  const int32_t* cell_node;
+  const double* coords;
+  const uint8_t* node_is_own; // may be null
+  long long nb_cell;
+  long long nb_node;
+  const int32_t* row_index; // nb_node + 1
+  const int32_t* columns;
+  double* values;
+  const int32_t* nc_ptr; // node -> cell list offsets, nb_node + 1
+  const uint32_t* nc_list; // entries: cell * 4 + local index of the node in the cell
+  unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
+  int accumulate;
+};
+
+enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3 };
+
+// Scalar index of entry (i,j) of the x-th block of a block row that starts at block rb and holds k blocks
+// (femutils/BSRFormat.h:145-171).
+template <int BS, bool PER_BLOCK>
+__device__ __forceinline__ long long value_index(long long rb, int k, int x, int i, int j)
+{
+  if (PER_BLOCK)
+    return (rb + x) * (BS * BS) + (i * BS + j);
+  return rb * (BS * BS) + (long long)i * (BS * k) + x * BS + j;
+}
+
+// Slot of column c in a row stored "diagonal first, then ascending" (k entries).  Returns -1 if absent.
+template <class ColPtr>
+__device__ __forceinline__ int find_slot(ColPtr cols, int k, int32_t c)
+{
+  int lo = 1, hi = k;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cols[mid] < c)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  return (lo < k && cols[lo] == c) ? lo : -1;
+}
+
+template <int NV>
+__device__ __forceinline__ void load_cell_nodes(const int32_t* __restrict__ cell_node, long long cell, int32_t (&n)[NV])
+{
+  if (NV == 4) {
+    const int4 v = __ldg(reinterpret_cast<const int4*>(cell_node) + cell);
+    n[0] = v.x;
+    n[1] = v.y;
+    n[2] = v.z;
+    n[NV - 1] = v.w;
+  }
+  else {
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      n[k] = __ldg(cell_node + cell * NV + k);
+  }
+}
+
+__device__ __forceinline__ void load_xyz(const double* __restrict__ coords, int32_t node, double (&x)[3])
+{
+  const double* p = coords + 3ll * node;
+  x[0] = __ldg(p);
+  x[1] = __ldg(p + 1);
+  x[2] = __ldg(p + 2);
+}
+
+// Even permutation bringing local vertex a to position 0: tets m[k] = n[a ^ k] (double transpositions),
+// triangles m[k] = n[(a + k) % 3] (rotations).  Orientation, hence every signed quantity, is preserved.
+template <int NV>
+__device__ __forceinline__ void bring_to_front(int32_t (&n)[NV], int a)
+{
+  if (NV == 4) {
+    if (a & 1) {
+      int32_t t = n[0];
+      n[0] = n[1];
+      n[1] = t;
+      t = n[2];
+      n[2] = n[NV - 1];
+      n[NV - 1] = t;
+    }
+    if (a & 2) {
+      int32_t t = n[0];
+      n[0] = n[2];
+      n[2] = t;
+      t = n[1];
+      n[1] = n[NV - 1];
+      n[NV - 1] = t;
+    }
+  }
+  else {
+    const int32_t n0 = n[0], n1 = n[1], n2 = n[2];
+    n[0] = (a == 0) ? n0 : (a == 1 ? n1 : n2);
+    n[1] = (a == 0) ? n1 : (a == 1 ? n2 : n0);
+    n[2] = (a == 0) ? n2 : (a == 1 ? n0 : n1);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Cell-wise atomic variant
+// ---------------------------------------------------------------------------------------------------
+template <class Op, bool PER_BLOCK, bool WARPAGG>
+__global__ void __launch_bounds__(256) k_cell_atomic(AssembleArgs A, Op op)
+{
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = cell < A.nb_cell;
+  if (!WARPAGG && !valid)
+    return;
+  const unsigned lane = threadIdx.x & 31u;
+
+  int32_t n[NV];
+  double X[NV][3];
+  typename Op::Geom G;
+  if (valid) {
+    load_cell_nodes<NV>(A.cell_node, cell, n);
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      load_xyz(A.coords, n[k], X[k]);
+    G = op.prepare(X, cell);
+  }
+
+#pragma unroll
+  for (int a = 0; a < NV; ++a) {
+    bool own = valid;
+    int32_t rb = 0;
+    int k = 0;
+    if (valid) {
+      const int32_t row = n[a];
+      own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+      rb = __ldg(A.row_index + row);
+      k = __ldg(A.row_index + row + 1) - rb;
+    }
+#pragma unroll
+    for (int b = 0; b < NV; ++b) {
+      int x = -1;
+      if (own) {
+        x = (a == b) ? 0 : find_slot(A.columns + rb, k, n[b]);
+        if (x < 0)
+          atomicAdd(A.counters, 1ull);
+      }
+      double out[BS2];
+      if (own && x >= 0)
+        op.block(G, a, b, out);
+      if (!WARPAGG) {
+        if (own && x >= 0) {
+#pragma unroll
+          for (int i = 0; i < BS; ++i)
+#pragma unroll
+            for (int j = 0; j < BS; ++j)
+              atomicAdd(A.values + value_index<BS, PER_BLOCK>(rb, k, x, i, j), out[i * BS + j]);
+        }
+      }
+      else {
+        // Pre-reduce adds that target the same block inside the warp: one RED per distinct block.
+        const bool act = own && x >= 0;
+        const long long key = act ? ((long long)rb + x) : (-1ll - (long long)lane);
+        const unsigned grp = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(grp) - 1;
+        const int cnt = __reduce_max_sync(0xffffffffu, __popc(grp));
+#pragma unroll
+        for (int e = 0; e < BS2; ++e) {
+          const double v = act ? out[e] : 0.0;
+          double sum = 0.0;
+          unsigned m = grp;
+          for (int it = 0; it < cnt; ++it) {
+            const int src = m ? (__ffs(m) - 1) : (int)lane;
+            const double t = __shfl_sync(0xffffffffu, v, src);
+            if (m) {
+              sum += t;
+              m &= m - 1;
+            }
+          }
+          if (act && (int)lane == leader)
+            atomicAdd(A.values + value_index<BS, PER_BLOCK>(rb, k, x, e / BS, e % BS), sum);
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Node-wise gather variant
+// ---------------------------------------------------------------------------------------------------
+template <class Op>
+struct GatherCfg
+{
+  static constexpr int BS2 = Op::BS * Op::BS;
+  static constexpr int ROWS = (Op::BS == 1) ? 128 : 64; // block rows (= threads) per CTA
+  static constexpr int ACC_BLOCKS = ROWS * ((Op::BS == 3) ? 18 : 24); // accumulator capacity in blocks
+  static constexpr int ADJ_CAP = ROWS * 40; // staged node->cell entries
+  static constexpr size_t SMEM_BYTES = (size_t)ACC_BLOCKS * BS2 * sizeof(double) + (size_t)ACC_BLOCKS * sizeof(int32_t) + (size_t)ADJ_CAP * sizeof(uint32_t);
+};
+
+template <class Op, bool PER_BLOCK, bool SMEM>
+__device__ __forceinline__ void gather_rows(const AssembleArgs& A, const Op& op, long long row0, int nrows, int32_t vbeg, int32_t vend, int32_t abeg, int32_t aend,
+                                            double* acc_s, int32_t* cols_s, uint32_t* adj_s)
+{
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  const int t = threadIdx.x;
+  if (SMEM) {
+    const int nblk = vend - vbeg;
+    for (int q = t; q < nblk; q += blockDim.x)
+      cols_s[q] = __ldg(A.columns + vbeg + q);
+    for (int q = t; q < aend - abeg; q += blockDim.x)
+      adj_s[q] = __ldg(A.nc_list + abeg + q);
+    if (A.accumulate) {
+      for (int q = t; q < nblk * BS2; q += blockDim.x)
+        acc_s[q] = A.values[(long long)vbeg * BS2 + q];
+    }
+    else {
+      for (int q = t; q < nblk * BS2; q += blockDim.x)
+        acc_s[q] = 0.0;
+    }
+    __syncthreads();
+  }
+
+  if (t < nrows) {
+    const long long row = row0 + t;
+    const int32_t rb = __ldg(A.row_index + row);
+    const int k = __ldg(A.row_index + row + 1) - rb;
+    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+    double* acc = SMEM ? (acc_s + (size_t)(rb - vbeg) * BS2) : (A.values + (long long)rb * BS2);
+    const int32_t* cols = SMEM ? (cols_s + (rb - vbeg)) : (A.columns + rb);
+    if (!SMEM && !A.accumulate) {
+      for (int q = 0; q < k * BS2; ++q)
+        acc[q] = 0.0;
+    }
+    if (own) {
+      const int32_t qb = __ldg(A.nc_ptr + row), qe = __ldg(A.nc_ptr + row + 1);
+      double X[NV][3];
+      load_xyz(A.coords, (int32_t)row, X[0]);
+      for (int32_t q = qb; q < qe; ++q) {
+        const uint32_t e = SMEM ? adj_s[q - abeg] : __ldg(A.nc_list + q);
+        const long long cell = e >> 2;
+        int32_t n[NV];
+        load_cell_nodes<NV>(A.cell_node, cell, n);
+        bring_to_front<NV>(n, (int)(e & 3u));
+#pragma unroll
+        for (int b = 1; b < NV; ++b)
+          load_xyz(A.coords, n[b], X[b]);
+        const typename Op::Geom G = op.prepare(X, cell);
+#pragma unroll
+        for (int b = 0; b < NV; ++b) {
+          const int x = (b == 0) ? 0 : find_slot(cols, k, n[b]);
+          if (x < 0) {
+            atomicAdd(A.counters, 1ull);
+            continue;
+          }
+          double out[BS2];
+          op.block(G, 0, b, out);
+#pragma unroll
+          for (int i = 0; i < BS; ++i)
+#pragma unroll
+            for (int j = 0; j < BS; ++j)
+              acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] += out[i * BS + j];
+        }
+      }
+    }
+  }
+
+  if (SMEM) {
+    __syncthreads();
+    const long long base = (long long)vbeg * BS2;
+    const int nval = (vend - vbeg) * BS2;
+    // coalesced store of the slab; 16-byte vector stores on the aligned middle part
+    const int head = (int)((2 - (base & 1)) & 1); // values is 16B-aligned at element 0
+    if (t < head && t < nval)
+      A.values[base + t] = acc_s[t];
+    const int nvec = (nval - head) >> 1;
+    double2* dst = reinterpret_cast<double2*>(A.values + base + head);
+    for (int q = t; q < nvec; q += blockDim.x)
+      dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+    const int tail = head + 2 * nvec;
+    if (t == 0 && tail < nval)
+      A.values[base + tail] = acc_s[tail];
+  }
+}
+
+template <class Op, bool PER_BLOCK>
+__global__ void __launch_bounds__(GatherCfg<Op>::ROWS) k_node_gather(AssembleArgs A, Op op)
+{
+  using C = GatherCfg<Op>;
+  extern __shared__ __align__(16) unsigned char b2f_smem[];
+  double* acc_s = reinterpret_cast<double*>(b2f_smem);
+  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)C::ACC_BLOCKS * C::BS2);
+  uint32_t* adj_s = reinterpret_cast<uint32_t*>(cols_s + C::ACC_BLOCKS);
+
+  const long long row0 = (long long)blockIdx.x * C::ROWS;
+  const long long left = A.nb_node - row0;
+  const int nrows = left < C::ROWS ? (int)left : C::ROWS;
+  const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
+  const int32_t abeg = __ldg(A.nc_ptr + row0), aend = __ldg(A.nc_ptr + row0 + nrows);
+  const bool fits = (vend - vbeg <= C::ACC_BLOCKS) && (aend - abeg <= C::ADJ_CAP);
+  if (fits)
+    gather_rows<Op, PER_BLOCK, true>(A, op, row0, nrows, vbeg, vend, abeg, aend, acc_s, cols_s, adj_s);
+  else {
+    if (threadIdx.x == 0)
+      atomicAdd(A.counters + 1, 1ull);
+    gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, abeg, aend, acc_s, cols_s, adj_s);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Launch
+// ---------------------------------------------------------------------------------------------------
+template <class Op, bool PER_BLOCK>
+inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
+{
+  if (variant == VARIANT_NODE_GATHER) {
+    using C = GatherCfg<Op>;
+    auto kern = k_node_gather<Op, PER_BLOCK>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+    if (e != cudaSuccess)
+      return e;
+    const long long grid = (A.nb_node + C::ROWS - 1) / C::ROWS;
+    if (grid > 0)
+      kern<<<(unsigned)grid, C::ROWS, C::SMEM_BYTES, stream>>>(A, op);
+    return cudaGetLastError();
+  }
+  if (!A.accumulate) {
+    cudaError_t e = cudaMemsetAsync(A.values, 0, sizeof(double) * (size_t)nb_values, stream);
+    if (e != cudaSuccess)
+      return e;
+  }
+  const int threads = 256;
+  const long long grid = (A.nb_cell + threads - 1) / threads;
+  if (grid > 0) {
+    if (variant == VARIANT_CELL_ATOMIC_WARPAGG)
+      k_cell_atomic<Op, PER_BLOCK, true><<<(unsigned)grid, threads, 0, stream>>>(A, op);
+    else
+      k_cell_atomic<Op, PER_BLOCK, false><<<(unsigned)grid, threads, 0, stream>>>(A, op);
+  }
+  return cudaGetLastError();
+}
+
+template <class Op>
+inline cudaError_t launch_assemble(const AssembleArgs& A, const Op& op, int variant, bool per_block, long long nb_values, cudaStream_t stream)
+{
+  if (per_block)
+    return launch_assemble_layout<Op, true>(A, op, variant, nb_values, stream);
+  return launch_assemble_layout<Op, false>(A, op, variant, nb_values, stream);
+}
+
+} // namespace b2f

@@ -1,0 +1,228 @@
+// element_ops.cuh — P1 element operators evaluated in registers (sm_100a device code).
+//
+// Each operator replaces one shipped instance of the reference's element callback
+// `FixedMatrix<BS*NV,BS*NV> compute_element_matrix(CellLocalId)` (femutils/BSRFormat.h:786-787,1105;
+// entry (BS*a+i, BS*b+j) couples dof i of local node a with dof j of local node b, :823,881):
+//   LaplaceTri / LaplaceTet      modules/poisson/FemModule.h:139-147 / :177-186
+//                                (helpers femutils/ArcaneFemFunctionsGpu.h:75-83,110-122,218-252,280-392)
+//   ElasticityTri (BS=2)         modules/elasticity/FemModule.h:112-152
+//   ElasticityTet (BS=3)         tetrahedral extension (not in the reference)
+//   HeatTri                      modules/heat/FemModule.cc:678-770 ; HeatTet: 3D twin (not in the reference)
+//
+// B200-first formulation: the reference gathers the cell's vertices four times and divides every
+// cofactor by V6; here the vertices are gathered once, gradients are kept as un-normalised cofactors of
+// the edge vectors (no absolute-coordinate cancellation), and a single reciprocal scales the result:
+//   tet:  g1 = e2 x e3, g2 = e3 x e1, g3 = e1 x e2, g0 = -(g1+g2+g3), det = e1.g1
+//         V * (g_a/det).(g_b/det) = (g_a.g_b) / (6|det|)
+//   tri:  n_a = (y_{a+1}-y_{a+2}, x_{a+2}-x_{a+1}), A2 = signed 2*area
+//         A * (n_a/A2).(n_b/A2) = (n_a.n_b) / (2|A2|)
+// Results agree with the reference formulas to rounding (tests: 1e-12 relative, row-scale floor).
+//
+// Operator concept used by the assembly kernels (include/b2f/assemble.cuh):
+//   static constexpr int NV, BS;
+//   struct Geom;                                         // per-cell prepared geometry, registers only
+//   __device__ Geom prepare(const double (&X)[NV][3], long long cell) const;
+//   __device__ void block(const Geom&, int a, int b, double (&out)[BS*BS]) const;  // a, b compile-time after unrolling
+// Operators are invariant under even permutations of the cell's vertices, which the node-gather kernel
+// uses to bring the row node to local index 0.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b2f {
+
+struct TetGeom
+{
+  double g[4][3]; // un-normalised gradients (cofactors)
+  double s; // 1 / (6 |det|)
+  double vol6; // |det| = 6 * volume
+};
+
+__device__ __forceinline__ TetGeom tet_geometry(const double (&X)[4][3])
+{
+  TetGeom G;
+  const double e1x = X[1][0] - X[0][0], e1y = X[1][1] - X[0][1], e1z = X[1][2] - X[0][2];
+  const double e2x = X[2][0] - X[0][0], e2y = X[2][1] - X[0][1], e2z = X[2][2] - X[0][2];
+  const double e3x = X[3][0] - X[0][0], e3y = X[3][1] - X[0][1], e3z = X[3][2] - X[0][2];
+  G.g[1][0] = e2y * e3z - e2z * e3y;
+  G.g[1][1] = e2z * e3x - e2x * e3z;
+  G.g[1][2] = e2x * e3y - e2y * e3x;
+  G.g[2][0] = e3y * e1z - e3z * e1y;
+  G.g[2][1] = e3z * e1x - e3x * e1z;
+  G.g[2][2] = e3x * e1y - e3y * e1x;
+  G.g[3][0] = e1y * e2z - e1z * e2y;
+  G.g[3][1] = e1z * e2x - e1x * e2z;
+  G.g[3][2] = e1x * e2y - e1y * e2x;
+  G.g[0][0] = -(G.g[1][0] + G.g[2][0] + G.g[3][0]);
+  G.g[0][1] = -(G.g[1][1] + G.g[2][1] + G.g[3][1]);
+  G.g[0][2] = -(G.g[1][2] + G.g[2][2] + G.g[3][2]);
+  const double det = e1x * G.g[1][0] + e1y * G.g[1][1] + e1z * G.g[1][2];
+  G.vol6 = fabs(det);
+  G.s = 1.0 / (6.0 * G.vol6);
+  return G;
+}
+
+struct TriGeom
+{
+  double n[3][2]; // un-normalised gradients: n_a = (y_{a+1}-y_{a+2}, x_{a+2}-x_{a+1})
+  double a2; // signed 2*area
+};
+
+__device__ __forceinline__ TriGeom tri_geometry(const double (&X)[3][3])
+{
+  TriGeom G;
+  G.n[0][0] = X[1][1] - X[2][1];
+  G.n[0][1] = X[2][0] - X[1][0];
+  G.n[1][0] = X[2][1] - X[0][1];
+  G.n[1][1] = X[0][0] - X[2][0];
+  G.n[2][0] = X[0][1] - X[1][1];
+  G.n[2][1] = X[1][0] - X[0][0];
+  G.a2 = (X[1][0] - X[0][0]) * (X[2][1] - X[0][1]) - (X[2][0] - X[0][0]) * (X[1][1] - X[0][1]);
+  return G;
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct LaplaceTet
+{
+  static constexpr int NV = 4, BS = 1;
+  using Geom = TetGeom;
+  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
+  {
+    out[0] = (G.g[a][0] * G.g[b][0] + G.g[a][1] * G.g[b][1] + G.g[a][2] * G.g[b][2]) * G.s;
+  }
+};
+
+struct LaplaceTri
+{
+  static constexpr int NV = 3, BS = 1;
+  struct Geom
+  {
+    TriGeom t;
+    double s; // 1 / (2 |A2|)
+  };
+  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long) const
+  {
+    Geom G;
+    G.t = tri_geometry(X);
+    G.s = 1.0 / (2.0 * fabs(G.t.a2));
+    return G;
+  }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
+  {
+    out[0] = (G.t.n[a][0] * G.t.n[b][0] + G.t.n[a][1] * G.t.n[b][1]) * G.s;
+  }
+};
+
+// modules/elasticity/FemModule.h:112-152: Ke = [lambda*(...) + mu2*(...)] / (4*area), area = |A2|/2.
+// Block (a,b), with p = dPhi (un-normalised gradient n):
+//   [ l*px_a*px_b + m2*(px_a*px_b + .5*py_a*py_b)   l*px_a*py_b + m2*.5*py_a*px_b          ]
+//   [ l*py_a*px_b + m2*.5*px_a*py_b                  l*py_a*py_b + m2*(py_a*py_b + .5*px_a*px_b) ]
+struct ElasticityTri
+{
+  static constexpr int NV = 3, BS = 2;
+  double lambda, mu2;
+  struct Geom
+  {
+    TriGeom t;
+    double s; // 1 / (4*area) = 1 / (2 |A2|)
+  };
+  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long) const
+  {
+    Geom G;
+    G.t = tri_geometry(X);
+    G.s = 1.0 / (2.0 * fabs(G.t.a2));
+    return G;
+  }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[4]) const
+  {
+    const double pxa = G.t.n[a][0], pya = G.t.n[a][1], pxb = G.t.n[b][0], pyb = G.t.n[b][1];
+    const double xx = pxa * pxb, yy = pya * pyb, xy = pxa * pyb, yx = pya * pxb;
+    const double hm = 0.5 * mu2;
+    out[0] = (lambda * xx + mu2 * xx + hm * yy) * G.s;
+    out[1] = (lambda * xy + hm * yx) * G.s;
+    out[2] = (lambda * yx + hm * xy) * G.s;
+    out[3] = (lambda * yy + mu2 * yy + hm * xx) * G.s;
+  }
+};
+
+// Tetrahedral extension: Ke[(a,i),(b,j)] = V*(lambda*G_a^i*G_b^j + mu*G_a^j*G_b^i + mu*delta_ij*G_a.G_b), G = g/det.
+struct ElasticityTet
+{
+  static constexpr int NV = 4, BS = 3;
+  double lambda, mu2;
+  using Geom = TetGeom;
+  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[9]) const
+  {
+    const double mu = 0.5 * mu2;
+    const double ls = lambda * G.s, ms = mu * G.s;
+    const double gab = (G.g[a][0] * G.g[b][0] + G.g[a][1] * G.g[b][1] + G.g[a][2] * G.g[b][2]) * ms;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        double v = ls * (G.g[a][i] * G.g[b][j]) + ms * (G.g[a][j] * G.g[b][i]);
+        if (i == j)
+          v += gab;
+        out[i * 3 + j] = v;
+      }
+  }
+};
+
+// modules/heat/FemModule.cc:678-770: lambda_cell * (dPhi_a.dPhi_b) * 0.25/area + (area/12)*(1+delta_ab)/dt, signed area (:606-612).
+struct HeatTri
+{
+  static constexpr int NV = 3, BS = 1;
+  double lambda, inv_dt;
+  const double* cell_lambda;
+  struct Geom
+  {
+    TriGeom t;
+    double ks; // lambda * 0.25 / area
+    double m; // area / 12 / dt
+  };
+  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const
+  {
+    Geom G;
+    G.t = tri_geometry(X);
+    const double area = 0.5 * G.t.a2;
+    const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
+    G.ks = lam * 0.25 / area;
+    G.m = area * (1.0 / 12.0) * inv_dt;
+    return G;
+  }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
+  {
+    const double k = (G.t.n[a][0] * G.t.n[b][0] + G.t.n[a][1] * G.t.n[b][1]) * G.ks;
+    out[0] = k + (a == b ? 2.0 * G.m : G.m);
+  }
+};
+
+// 3D twin of the heat operator: lambda*V*(grad.grad) + (V/20)*(1+delta_ab)/dt.
+struct HeatTet
+{
+  static constexpr int NV = 4, BS = 1;
+  double lambda, inv_dt;
+  const double* cell_lambda;
+  struct Geom
+  {
+    TetGeom t;
+    double ks, m;
+  };
+  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const
+  {
+    Geom G;
+    G.t = tet_geometry(X);
+    const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
+    G.ks = lam * G.t.s;
+    G.m = G.t.vol6 * (1.0 / 120.0) * inv_dt;
+    return G;
+  }
+  __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
+  {
+    const double k = (G.t.g[a][0] * G.t.g[b][0] + G.t.g[a][1] * G.t.g[b][1] + G.t.g[a][2] * G.t.g[b][2]) * G.ks;
+    out[0] = k + (a == b ? 2.0 * G.m : G.m);
+  }
+};
+
+} // namespace b2f

@@ -1,0 +1,362 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.  Needs a B200: run with -m gpu.
+
+Bars (BASELINE.json north_star): sparsity pattern, indices and Dirichlet masks bit-exact; matrix and RHS values
+within 1e-12 relative per entry (tests/util.py states the rule, with the row-scale floor for cancelling entries).
+"""
+import numpy as np
+import pytest
+
+from tests import util
+from tests.util import MESHES, assert_values_close, assert_vec_close, op_params
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def _fem():
+    import arcanefem_b200 as fem
+    return fem
+
+
+def _setup(mesh_name, bs, use_csr, variant, node_is_own=None):
+    fem = _fem()
+    from arcanefem_b200.bsr import Mesh
+    dim, cells, coords = MESHES[mesh_name]()
+    m = Mesh.from_numpy(dim, cells, coords, node_is_own)
+    bsr = fem.BSRFormat(bs)
+    bsr.initialize(m, use_csr, assembly_variant=variant)
+    bsr.computeSparsity()
+    return bsr, m, dim, cells, coords
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+VARIANTS = [1, 2, 3]  # cell atomic, cell atomic warp-aggregated, node gather
+
+
+@pytest.mark.parametrize("mesh_name", sorted(MESHES))
+def test_sparsity_pattern_bit_exact(mesh_name):
+    from oracle import oracle as orc
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3)
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    mat = bsr.matrix()
+    assert mat.nbRow() == coords.shape[0]
+    assert mat.nbCol() == co.shape[0]
+    assert mat.nbNz() == co.shape[0]
+    np.testing.assert_array_equal(_np(mat.rowIndexWithEnd()), ri)
+    np.testing.assert_array_equal(_np(mat.columns()), co)
+    np.testing.assert_array_equal(_np(mat.nbNzPerRow()), orc.nz_per_row(ri))
+    # nnzb = 2E + Nn (femutils/BSRFormat.h:401)
+    assert mat.nbCol() == 2 * mat.nbEdge() + mat.nbRow()
+
+
+CASES = [
+    # (mesh, bs, operator)
+    ("cube1", 1, "laplace"), ("cube2", 1, "laplace"), ("cube5", 1, "laplace"), ("cube5_flat", 1, "laplace"),
+    ("cube7_shuffled", 1, "laplace"), ("cube12", 1, "laplace"),
+    ("square1", 1, "laplace"), ("square3", 1, "laplace"), ("square9_shuffled", 1, "laplace"), ("square20", 1, "laplace"),
+    ("square3", 2, "elasticity"), ("square9_shuffled", 2, "elasticity"), ("square20", 2, "elasticity"),
+    ("cube2", 3, "elasticity"), ("cube7_shuffled", 3, "elasticity"), ("cube12", 3, "elasticity"),
+    ("square9_shuffled", 1, "heat"), ("square20", 1, "heat_cell"), ("cube5", 1, "heat"), ("cube7_shuffled", 1, "heat_cell"),
+]
+
+
+def _operator(kind, params, device_cell_lambda):
+    fem = _fem()
+    if kind == "laplace":
+        return fem.Operator.laplace()
+    if kind == "elasticity":
+        return fem.Operator.elasticity(21.0e5, 0.28)
+    return fem.Operator.heat(params["lambda_"], 0.1, cell_lambda=device_cell_lambda)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("use_csr", [False, True])
+@pytest.mark.parametrize("mesh_name,bs,kind", CASES)
+def test_assembled_values_match_oracle(mesh_name, bs, kind, use_csr, variant):
+    from oracle import oracle as orc
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, use_csr, variant)
+    params = op_params(kind, nb_cell=cells.shape[0])
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    ref, nf = orc.assemble(cells, coords, ri, co, bs=bs, per_block=not use_csr, **params)
+    assert nf == 0
+    cl = params.get("cell_lambda")
+    dcl = torch.as_tensor(cl).cuda() if cl is not None else None
+    op = _operator(kind, params, dcl)
+    bsr.assembleBilinear(op)
+    torch.cuda.synchronize()
+    got = _np(bsr.matrix().values())
+    assert_values_close(got, ref, ri, bs, what=f"{mesh_name}/{kind}/bs{bs}/csr{use_csr}/v{variant}")
+    st = bsr.stats()
+    assert st["columns_not_found"] == 0
+    # assembling twice overwrites (zero-fill semantics), accumulate=True adds
+    bsr.assembleBilinear(op)
+    torch.cuda.synchronize()
+    assert_values_close(_np(bsr.matrix().values()), ref, ri, bs, what="second assembly")
+    bsr.assembleBilinear(op, accumulate=True)
+    torch.cuda.synchronize()
+    assert_values_close(_np(bsr.matrix().values()), 2.0 * ref, ri, bs, what="accumulate")
+    bsr.resetMatrixValues()
+    torch.cuda.synchronize()
+    assert not _np(bsr.matrix().values()).any()
+
+
+def test_node_gather_is_deterministic_and_symmetric():
+    bsr, m, dim, cells, coords = _setup("cube12", 1, True, 3)
+    fem = _fem()
+    bsr.assembleBilinear(fem.Operator.laplace())
+    a = _np(bsr.matrix().values()).copy()
+    bsr.assembleBilinear(fem.Operator.laplace())
+    b = _np(bsr.matrix().values())
+    np.testing.assert_array_equal(a, b)  # atomic-free: bitwise reproducible
+    import scipy.sparse as sp
+    mat = bsr.matrix()
+    A = sp.csr_matrix((a, _np(mat.columns()), _np(mat.rowIndexWithEnd())))
+    assert abs(A - A.T).max() <= 1e-12 * abs(A).max()
+    assert np.abs(A @ np.ones(A.shape[0])).max() <= 1e-12 * abs(A).max()
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("square9_shuffled", 2, "elasticity"), ("cube7_shuffled", 3, "elasticity")])
+def test_rows_of_ghost_nodes_stay_zero(mesh_name, bs, kind, variant):
+    """isOwn(row_node) rule, femutils/BSRFormat.h:815,870,974,1041."""
+    from oracle import oracle as orc
+    dim, cells, coords = MESHES[mesh_name]()
+    rng = np.random.default_rng(3)
+    own = (rng.uniform(size=coords.shape[0]) > 0.3).astype(np.uint8)
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, variant, node_is_own=own)
+    params = op_params(kind)
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    ref, _ = orc.assemble(cells, coords, ri, co, bs=bs, per_block=False, node_is_own=own, **params)
+    bsr.assembleBilinear(_operator(kind, params, None))
+    torch.cuda.synchronize()
+    got = _np(bsr.matrix().values())
+    assert_values_close(got, ref, ri, bs)
+    ghost_rows = np.nonzero(own == 0)[0]
+    for r in ghost_rows[:50]:
+        assert not got[ri[r] * bs * bs:ri[r + 1] * bs * bs].any()
+
+
+@pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("square9_shuffled", 2, "elasticity"), ("cube7_shuffled", 3, "elasticity")])
+def test_to_csr_and_spmv(mesh_name, bs, kind):
+    from oracle import oracle as orc
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, 3)
+    params = op_params(kind)
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    ref, _ = orc.assemble(cells, coords, ri, co, bs=bs, per_block=False, **params)
+    rows, nbcol, cols = orc.to_csr(bs, ri, co)
+    bsr.assembleBilinear(_operator(kind, params, None))
+    ls = _fem().DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    torch.cuda.synchronize()
+    view = ls.getCSRValues()
+    np.testing.assert_array_equal(_np(view.rowsWithEnd()), rows)
+    np.testing.assert_array_equal(_np(view.rowsNbColumn()), nbcol)
+    np.testing.assert_array_equal(_np(view.columns()), cols)
+    assert view.nbRow() == coords.shape[0] * bs and view.nbValue() == ref.shape[0]
+    assert view.values().data_ptr() == bsr.matrix().values().data_ptr()  # zero copy
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal(coords.shape[0] * bs)
+    y_ref = orc.csr_spmv(rows, cols, ref, x)
+    y = _np(bsr.spmv(torch.as_tensor(x).cuda()))
+    assert_vec_close(y, y_ref, rtol=1e-11, what="spmv")
+    # per-block layout gives the same product
+    bsr2, *_ = _setup(mesh_name, bs, False, 3)
+    bsr2.assembleBilinear(_operator(kind, params, None))
+    y2 = _np(bsr2.spmv(torch.as_tensor(x).cuda()))
+    assert_vec_close(y2, y_ref, rtol=1e-11, what="spmv per-block")
+
+
+@pytest.mark.parametrize("mesh_name", ["cube5", "cube7_shuffled", "square9_shuffled", "square20"])
+def test_rhs_source_and_neumann(mesh_name):
+    from oracle import oracle as orc
+    from arcanefem_b200 import mesh as gen
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3)
+    nn = coords.shape[0]
+    L = coords[:, 0].max()
+    faces = gen.boundary_faces(cells, coords, 0, L)
+    assert faces.shape[0] > 0
+    outside = (np.arange(faces.shape[0]) % 3 != 0).astype(np.uint8)
+    ref = np.zeros(nn)
+    orc.rhs_constant_source(cells, coords, 1, 5.5, ref)
+    orc.rhs_neumann(faces, coords, 1, ref, value=2.0)
+    orc.rhs_neumann(faces, coords, 1, ref, value=None, value_xyz=(1.5, -0.7, 0.3), face_outside=outside)
+    ls = _fem().DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    ls.clearValues()
+    bsr.applyConstantSourceToRhs(5.5)
+    dfaces = torch.as_tensor(faces).cuda()
+    bsr.applyNeumannToRhs(dfaces, value=2.0)
+    bsr.applyNeumannToRhs(dfaces, value_xyz=(1.5, -0.7, 0.3), face_outside=torch.as_tensor(outside).cuda())
+    torch.cuda.synchronize()
+    assert_vec_close(_np(ls.rhsVariable()), ref, what="rhs")
+
+
+def _dirichlet_case(mesh_name, bs, kind, mode):
+    """mode: 'penalty' | 'row' | 'rowcol' — returns (got values, got rhs, masks...) vs oracle."""
+    from oracle import oracle as orc
+    from arcanefem_b200 import mesh as gen
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, 3)
+    params = op_params(kind)
+    nn = coords.shape[0]
+    ndof = nn * bs
+    ri, co = orc.build_pattern(cells, nn)
+    vals, _ = orc.assemble(cells, coords, ri, co, bs=bs, per_block=False, **params)
+    rows, nbcol, cols = orc.to_csr(bs, ri, co)
+    axis = dim - 1
+    group = gen.boundary_nodes(coords, axis, 0.0)  # "horizontal"
+    assert group.size > 0
+    rhs = np.zeros(ndof)
+    orc.rhs_constant_source(cells, coords, bs, 5.5, rhs)
+    finfo = np.zeros(ndof, np.uint8)
+    fval = np.zeros(ndof)
+    einfo = np.zeros(ndof, np.uint8)
+    evalue = np.zeros(ndof)
+    comps = [(0, 0.5)] if bs == 1 else [(0, 0.5), (bs - 1, -0.25)]  # vectorial: one call per non-"NULL" component
+    for dof_index, g in comps:
+        if mode == "penalty":
+            orc.dirichlet_flag_penalty(bs, dof_index, g, 1.0e30, group, finfo, fval, rhs)
+        else:
+            orc.dirichlet_flag_elimination(bs, dof_index, g, 1 if mode == "row" else 2, group, einfo, evalue)
+    orc.dirichlet_apply(rows, cols, vals, einfo, evalue, finfo, fval, rhs)
+
+    ls = _fem().DoFLinearSystem()
+    bsr.assembleBilinear(_operator(kind, params, None))
+    bsr.toLinearSystem(ls)
+    ls.clearValues()
+    bsr.applyConstantSourceToRhs(5.5)
+    dgroup = torch.as_tensor(group).cuda()
+    for dof_index, g in comps:
+        if mode == "penalty":
+            bsr.applyDirichletViaPenalty(dgroup, g, 1.0e30, dof_index)
+        else:
+            bsr.applyDirichletViaRowElimination(dgroup, g, dof_index, mode=1 if mode == "row" else 2)
+    ls.applyDirichlet()
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(_np(ls.getForcedInfo()), finfo)  # masks bit-exact
+    np.testing.assert_array_equal(_np(ls.getEliminationInfo()), einfo)
+    np.testing.assert_array_equal(_np(ls.getForcedValue()), fval)
+    np.testing.assert_array_equal(_np(ls.getEliminationValue()), evalue)
+    assert_values_close(_np(bsr.matrix().values()), vals, ri, bs, what=f"dirichlet {mode} values")
+    assert_vec_close(_np(ls.rhsVariable()), rhs, what=f"dirichlet {mode} rhs")
+    return _np(bsr.matrix().values()), vals
+
+
+@pytest.mark.parametrize("mode", ["penalty", "row", "rowcol"])
+@pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("cube7_shuffled", 1, "laplace"), ("square9_shuffled", 1, "laplace"),
+                                                ("square9_shuffled", 2, "elasticity"), ("cube7_shuffled", 3, "elasticity")])
+def test_dirichlet_on_device(mesh_name, bs, kind, mode):
+    got, ref = _dirichlet_case(mesh_name, bs, kind, mode)
+    if mode == "penalty":
+        assert (got == 1.0e30).sum() == (ref == 1.0e30).sum() > 0  # exact stores of P
+
+
+def test_set_get_value_and_dump(tmp_path):
+    fem = _fem()
+    bsr, m, dim, cells, coords = _setup("square3", 2, True, 3)
+    bsr.assembleBilinear(fem.Operator.elasticity(21.0e5, 0.28))
+    mat = bsr.matrix()
+    # testlab's host-side penalty: bsr_matrix->setValue(dof, dof, Penalty), modules/testlab/FemModule.cc:677-678
+    mat.setValue(5, 5, 1.0e31)
+    assert mat.getValue(5, 5) == 1.0e31
+    v = mat.getValue(4, 5)
+    assert v == mat.getValue(5, 4) or abs(v - mat.getValue(5, 4)) <= 1e-12 * abs(v)
+    with pytest.raises(fem.B2FError) as e:
+        mat.getValue(0, 2 * (coords.shape[0] - 1))  # far corner is not a neighbour of node 0
+    assert e.value.status == -5 and "Value not found" in e.value.message
+    out = tmp_path / "m.txt"
+    bsr.dumpMatrix(out)
+    lines = out.read_text().splitlines()
+    assert lines[0] == f"size :{mat.nbNz()}"
+    assert len(lines[2].split()) == mat.nbCol() and len(lines[3].split()) == mat.nbNz()
+
+
+def test_error_conventions():
+    fem = _fem()
+    from arcanefem_b200.bsr import Mesh
+    dim, cells, coords = MESHES["square3"]()
+    m = Mesh.from_numpy(dim, cells, coords)
+    bsr = fem.BSRFormat(1)
+    bsr.initialize(m, True)
+    with pytest.raises(fem.B2FError) as e:
+        bsr.assembleBilinear(fem.Operator.laplace())  # before computeSparsity
+    assert e.value.status == -4
+    bad = fem.BSRFormat(4)
+    with pytest.raises(fem.B2FError) as e:
+        bad.initialize(m, True)
+    assert e.value.status == -2
+    m1 = Mesh(1, m.cell_node, m.coords)
+    with pytest.raises(fem.B2FError) as e:
+        fem.BSRFormat(1).initialize(m1, True)
+    assert e.value.status == -2 and "Only supports 2D and 3D" in e.value.message
+    bsr.computeSparsity()
+    with pytest.raises(fem.B2FError) as e:
+        bsr.assembleBilinear(fem.Operator.elasticity(1.0, 0.3))  # BS mismatch
+    assert e.value.status == -1
+    # node id out of range is reported, not dereferenced
+    cells_bad = cells.copy()
+    cells_bad[0, 0] = coords.shape[0] + 5
+    b2 = fem.BSRFormat(1)
+    b2.initialize(Mesh.from_numpy(dim, cells_bad, coords), True)
+    with pytest.raises(fem.B2FError) as e:
+        b2.computeSparsity()
+    assert e.value.status == -1
+    # BS > 1 CSR view needs the per-row layout
+    b3 = fem.BSRFormat(2)
+    b3.initialize(m, False)
+    b3.computeSparsity()
+    with pytest.raises(fem.B2FError) as e:
+        b3.matrix().toCsr()
+    assert e.value.status == -4
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_medium_cube_parity(variant):
+    """N = 40 (384 000 tets): oracle runs in about a second."""
+    from oracle import oracle as orc
+    from arcanefem_b200 import mesh as gen
+    from arcanefem_b200.bsr import Mesh
+    fem = _fem()
+    cells, coords = gen.cube_kuhn(40)
+    m = Mesh.from_numpy(3, cells, coords)
+    bsr = fem.BSRFormat(1)
+    bsr.initialize(m, True, assembly_variant=variant)
+    bsr.computeSparsity()
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    np.testing.assert_array_equal(_np(bsr.matrix().rowIndexWithEnd()), ri)
+    np.testing.assert_array_equal(_np(bsr.matrix().columns()), co)
+    nc, nn, e, nnzb = gen.kuhn_counts(40)
+    assert bsr.matrix().nbEdge() == e and bsr.matrix().nbCol() == nnzb
+    ref, _ = orc.assemble(cells, coords, ri, co)
+    bsr.assembleBilinear(fem.Operator.laplace())
+    torch.cuda.synchronize()
+    assert_values_close(_np(bsr.matrix().values()), ref, ri, 1)
+    assert bsr.stats()["gather_fallback_tiles"] == 0
+
+
+def test_long_rows_take_the_global_fallback_path():
+    """A fan of triangles around one hub node: one row far longer than the shared-memory tile."""
+    from oracle import oracle as orc
+    from arcanefem_b200.bsr import Mesh
+    fem = _fem()
+    K = 5000
+    ang = np.linspace(0.0, 2 * np.pi, K, endpoint=False)
+    coords = np.zeros((K + 1, 3))
+    coords[1:, 0] = np.cos(ang)
+    coords[1:, 1] = np.sin(ang)
+    cells = np.stack([np.zeros(K, np.int32), 1 + np.arange(K, dtype=np.int32), 1 + (np.arange(K, dtype=np.int32) + 1) % K], axis=1).astype(np.int32)
+    ri, co = orc.build_pattern(cells, K + 1)
+    ref, _ = orc.assemble(cells, coords, ri, co)
+    for variant in VARIANTS:
+        bsr = fem.BSRFormat(1)
+        bsr.initialize(Mesh.from_numpy(2, cells, coords), True, assembly_variant=variant)
+        bsr.computeSparsity()
+        np.testing.assert_array_equal(_np(bsr.matrix().columns()), co)
+        bsr.assembleBilinear(fem.Operator.laplace())
+        torch.cuda.synchronize()
+        assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant}")
+        if variant == 3:
+            assert bsr.stats()["gather_fallback_tiles"] >= 1
