@@ -106,7 +106,7 @@ int b2f_destroy(b2f_handle h)
 {
   if (!h)
     return B2F_OK;
-  DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+  DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
                      &h->coords_stage, &h->ghost.send_rows, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_slot };
   for (DevBuf* b : bufs)
@@ -235,7 +235,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
     out->gather_fallback_tiles = (int64_t)c[1];
   }
   out->workspace_bytes = (int64_t)(h->ws_keys_a.bytes + h->ws_keys_b.bytes + h->ws_tmp.bytes + h->ws_i32a.bytes + h->ws_i64.bytes);
-  const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+  const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                           &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage };
   for (const DevBuf* b : res)
     out->resident_bytes += (int64_t)b->bytes;

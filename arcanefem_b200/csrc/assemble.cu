@@ -22,6 +22,8 @@ namespace {
     A.values = h->values.as<double>();
     A.nc_ptr = h->nc_ptr.as<int32_t>();
     A.nc_list = h->nc_list.as<uint32_t>();
+    A.nc_slots = h->nc_slots.as<uint32_t>();
+    A.slots_ok = h->slots_ok ? 1 : 0;
     A.counters = h->counters.as<unsigned long long>();
     A.accumulate = accumulate;
     int variant = h->variant;

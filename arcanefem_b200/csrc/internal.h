@@ -77,7 +77,8 @@ struct b2f_context_s
   int64_t nb_col = 0, nb_nz = 0, nb_edge = 0, nb_dof = 0;
 
   b2f::DevBuf row_index, columns, nb_nz_per_row, values; // BSRMatrix arrays
-  b2f::DevBuf nc_ptr, nc_list; // node -> cell lists
+  b2f::DevBuf nc_ptr, nc_list, nc_slots; // node -> cell lists and the column-slot plan of the gather kernel
+  bool slots_ok = false;
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
   b2f::DevBuf counters; // 4 x u64

@@ -219,6 +219,46 @@ namespace {
     }
   }
 
+  // Plan of the slots-driven gather kernel: for every node->cell entry, the column slots of the cell's other vertices
+  // in the row of that node, in the even-permuted vertex order that puts the node first (tets: n[a^k]; triangles:
+  // n[(a+k)%3]).  10 bits per slot; rows longer than 1023 blocks clear the `ok` flag (search-based kernel is used).
+  template <int NV>
+  __global__ void __launch_bounds__(128) k_build_slots(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
+                                                       const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, long long nb_node,
+                                                       uint32_t* __restrict__ nc_slots, unsigned long long* __restrict__ counters)
+  {
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nb_node)
+      return;
+    const int32_t rb = row_index[row];
+    const int k = row_index[row + 1] - rb;
+    if (k > 1023) {
+      atomicAdd(counters + 3, 1ull);
+      return;
+    }
+    for (int32_t q = nc_ptr[row]; q < nc_ptr[row + 1]; ++q) {
+      const uint32_t e = nc_list[q];
+      const long long cell = e >> 2;
+      const int a = (int)(e & 3u);
+      uint32_t word = 0;
+#pragma unroll
+      for (int b = 1; b < NV; ++b) {
+        const int src = (NV == 4) ? (a ^ b) : ((a + b) % 3);
+        const int32_t c = cell_node[cell * NV + src];
+        int lo = 1, hi = k;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (columns[rb + mid] < c)
+            lo = mid + 1;
+          else
+            hi = mid;
+        }
+        word |= (uint32_t)(lo & 1023) << (10 * (b - 1));
+      }
+      nc_slots[q] = word;
+    }
+  }
+
   __global__ void k_narrow_offsets(const long long* __restrict__ in, long long n, int32_t* __restrict__ out)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -326,7 +366,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   h->nb_edge = (nb_col - nn) / 2;
 
   // --- K5: columns, then canonical order inside every row
-  B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)nb_col));
+  B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
   B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
   B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)nb_nz, stream)); // BSRMatrix::initialize fills 0, BSRFormat.h:136
   int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724
@@ -366,6 +406,23 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   }
   k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
   B2F_CUDA(cudaGetLastError());
+
+  // --- plan of the slots-driven gather kernel
+  B2F_CUDA(h->nc_slots.alloc(sizeof(uint32_t) * (size_t)(nb_adj + 8)));
+  B2F_CUDA(cudaMemsetAsync(counters + 3, 0, sizeof(unsigned long long), stream));
+  if (nv == 3)
+    k_build_slots<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
+                                                            h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
+  else
+    k_build_slots<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
+                                                            h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
+  B2F_CUDA(cudaGetLastError());
+  {
+    unsigned long long long_rows = 0;
+    B2F_CUDA(cudaMemcpyAsync(&long_rows, counters + 3, sizeof(long_rows), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    h->slots_ok = (long_rows == 0);
+  }
 
   // --- linear-system state (HypreDoFLinearSystem.cc:224-242)
   h->nb_dof = nn * h->bs;

@@ -34,6 +34,8 @@ struct AssembleArgs
   double* values;
   const int32_t* nc_ptr; // node -> cell list offsets, nb_node + 1
   const uint32_t* nc_list; // entries: cell * 4 + local index of the node in the cell
+  const uint32_t* nc_slots; // per node->cell entry: column slots of the cell's other vertices, 10 bits each (see k_node_gather_slots)
+  int slots_ok; // nc_slots is usable (every row has at most 1023 blocks)
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
 };
@@ -326,12 +328,186 @@ __global__ void __launch_bounds__(GatherCfg<Op>::ROWS) k_node_gather(AssembleArg
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Node-wise gather, plan-driven ("slots") kernel — the default.
+//
+// The sparsity build also emits, for every (row node, incident cell) pair, one 32-bit word holding the column slots
+// (10 bits each) of the cell's other NV-1 vertices inside the row, listed in the even-permuted order that puts the
+// row node at local vertex 0.  With it the hot loop needs neither the cell's connectivity nor a column search: the
+// neighbour ids are columns[row_begin + slot], so one staged word per pair drives NV-1 coordinate gathers, the row-0
+// entries of Ke and NV accumulator updates.  The tile's column indices and slot words are contiguous in global memory
+// and are brought into shared memory by two TMA bulk copies (cp.async.bulk -> mbarrier) while the accumulators are
+// cleared; coordinates of the next pair are prefetched into registers while the current pair is evaluated.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_global, uint32_t bytes, unsigned long long* bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(__cvta_generic_to_global(src_global)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity)
+{
+  uint32_t done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+
+template <class Op>
+struct SlotsCfg
+{
+  static constexpr int BS2 = Op::BS * Op::BS;
+  static constexpr int ROWS = (Op::BS == 1) ? 128 : 64;
+  static constexpr int ACC_BLOCKS = ROWS * ((Op::BS == 3) ? 18 : 22);
+  static constexpr int ADJ_CAP = ROWS * 32;
+  static constexpr int PAD = 8; // alignment slack of the bulk copies (source is aligned down to 16 bytes)
+  static constexpr size_t SMEM_BYTES = 16 + (size_t)ACC_BLOCKS * BS2 * sizeof(double) + (size_t)(ACC_BLOCKS + PAD) * sizeof(int32_t) + (size_t)(ADJ_CAP + PAD) * sizeof(uint32_t);
+};
+
+template <class Op, bool PER_BLOCK>
+__global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(AssembleArgs A, Op op)
+{
+  using C = SlotsCfg<Op>;
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  extern __shared__ __align__(16) unsigned char b2f_smem[];
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
+  double* acc_s = reinterpret_cast<double*>(b2f_smem + 16);
+  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)C::ACC_BLOCKS * BS2);
+  uint32_t* slots_s = reinterpret_cast<uint32_t*>(cols_s + C::ACC_BLOCKS + C::PAD);
+
+  const int t = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * C::ROWS;
+  const long long left = A.nb_node - row0;
+  const int nrows = left < C::ROWS ? (int)left : C::ROWS;
+  const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
+  const int32_t abeg = __ldg(A.nc_ptr + row0), aend = __ldg(A.nc_ptr + row0 + nrows);
+  const int32_t vbeg_al = vbeg & ~3, abeg_al = abeg & ~3; // 16-byte aligned sources
+  const int ncols_cp = ((vend - vbeg_al) + 3) & ~3, nadj_cp = ((aend - abeg_al) + 3) & ~3;
+  const bool fits = (vend - vbeg <= C::ACC_BLOCKS) && (ncols_cp <= C::ACC_BLOCKS + C::PAD) && (nadj_cp <= C::ADJ_CAP + C::PAD);
+  if (!fits) { // oversized tile (very long rows): search-based path on global memory
+    if (t == 0)
+      atomicAdd(A.counters + 1, 1ull);
+    gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, abeg, aend, nullptr, nullptr, nullptr);
+    return;
+  }
+
+  if (t == 0)
+    mbar_init(bar, 1);
+  __syncthreads();
+  if (t == 0) {
+    mbar_expect_tx(bar, (uint32_t)(ncols_cp + nadj_cp) * 4u);
+    if (ncols_cp > 0)
+      tma_load_1d(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
+    if (nadj_cp > 0)
+      tma_load_1d(slots_s, A.nc_slots + abeg_al, (uint32_t)nadj_cp * 4u, bar);
+  }
+  const int nval = (vend - vbeg) * BS2;
+  if (A.accumulate) {
+    for (int q = t; q < nval; q += C::ROWS)
+      acc_s[q] = A.values[(long long)vbeg * BS2 + q];
+  }
+  else {
+    for (int q = t; q < nval; q += C::ROWS)
+      acc_s[q] = 0.0;
+  }
+  mbar_wait(bar, 0);
+  __syncthreads();
+
+  if (t < nrows) {
+    const long long row = row0 + t;
+    const int32_t rb = __ldg(A.row_index + row);
+    const int k = __ldg(A.row_index + row + 1) - rb;
+    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+    if (own) {
+      double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
+      const int32_t* cols = cols_s + (rb - vbeg_al);
+      const int32_t qb = __ldg(A.nc_ptr + row), qe = __ldg(A.nc_ptr + row + 1);
+      const uint32_t* sl = slots_s + (qb - abeg_al);
+      const int npair = qe - qb;
+      double X[NV][3], Y[NV - 1][3];
+      load_xyz(A.coords, (int32_t)row, X[0]);
+      uint32_t w = 0, wn = 0;
+      if (npair > 0) {
+        wn = sl[0];
+#pragma unroll
+        for (int b = 1; b < NV; ++b)
+          load_xyz(A.coords, cols[(wn >> (10 * (b - 1))) & 1023u], Y[b - 1]);
+      }
+      for (int p = 0; p < npair; ++p) {
+        w = wn;
+#pragma unroll
+        for (int b = 1; b < NV; ++b)
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            X[b][d] = Y[b - 1][d];
+        if (p + 1 < npair) { // prefetch the next pair's vertices while this one is evaluated
+          wn = sl[p + 1];
+#pragma unroll
+          for (int b = 1; b < NV; ++b)
+            load_xyz(A.coords, cols[(wn >> (10 * (b - 1))) & 1023u], Y[b - 1]);
+        }
+        long long cell = 0;
+        if (Op::NEEDS_CELL)
+          cell = __ldg(A.nc_list + qb + p) >> 2;
+        const typename Op::Geom G = op.prepare(X, cell);
+#pragma unroll
+        for (int b = 0; b < NV; ++b) {
+          const int x = (b == 0) ? 0 : (int)((w >> (10 * (b - 1))) & 1023u);
+          double out[BS2];
+          op.block(G, 0, b, out);
+#pragma unroll
+          for (int i = 0; i < BS; ++i)
+#pragma unroll
+            for (int j = 0; j < BS; ++j)
+              acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] += out[i * BS + j];
+        }
+      }
+    }
+  }
+
+  __syncthreads();
+  const long long base = (long long)vbeg * BS2;
+  const int head = (int)(base & 1); // values is 16-byte aligned at element 0
+  if (t < head && t < nval)
+    A.values[base + t] = acc_s[t];
+  const int nvec = (nval - head) >> 1;
+  double2* dst = reinterpret_cast<double2*>(A.values + base + head);
+  for (int q = t; q < nvec; q += C::ROWS)
+    dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+  const int tail = head + 2 * nvec;
+  if (t == 0 && tail < nval)
+    A.values[base + tail] = acc_s[tail];
+}
+
 // ---------------------------------------------------------------------------------------------------
 // Launch
 // ---------------------------------------------------------------------------------------------------
 template <class Op, bool PER_BLOCK>
 inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
 {
+  if (variant == VARIANT_NODE_GATHER && A.slots_ok) {
+    using C = SlotsCfg<Op>;
+    auto kern = k_node_gather_slots<Op, PER_BLOCK>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+    if (e != cudaSuccess)
+      return e;
+    const long long grid = (A.nb_node + C::ROWS - 1) / C::ROWS;
+    if (grid > 0)
+      kern<<<(unsigned)grid, C::ROWS, C::SMEM_BYTES, stream>>>(A, op);
+    return cudaGetLastError();
+  }
   if (variant == VARIANT_NODE_GATHER) {
     using C = GatherCfg<Op>;
     auto kern = k_node_gather<Op, PER_BLOCK>;

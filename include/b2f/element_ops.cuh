@@ -20,6 +20,7 @@
 //
 // Operator concept used by the assembly kernels (include/b2f/assemble.cuh):
 //   static constexpr int NV, BS;
+//   static constexpr bool NEEDS_CELL;                    // prepare() reads per-cell data (the cell id must be fetched)
 //   struct Geom;                                         // per-cell prepared geometry, registers only
 //   __device__ Geom prepare(const double (&X)[NV][3], long long cell) const;
 //   __device__ void block(const Geom&, int a, int b, double (&out)[BS*BS]) const;  // a, b compile-time after unrolling
@@ -84,6 +85,7 @@ __device__ __forceinline__ TriGeom tri_geometry(const double (&X)[3][3])
 struct LaplaceTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr bool NEEDS_CELL = false;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
@@ -95,6 +97,7 @@ struct LaplaceTet
 struct LaplaceTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr bool NEEDS_CELL = false;
   struct Geom
   {
     TriGeom t;
@@ -120,6 +123,7 @@ struct LaplaceTri
 struct ElasticityTri
 {
   static constexpr int NV = 3, BS = 2;
+  static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
   struct Geom
   {
@@ -149,6 +153,7 @@ struct ElasticityTri
 struct ElasticityTet
 {
   static constexpr int NV = 4, BS = 3;
+  static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
@@ -173,6 +178,7 @@ struct ElasticityTet
 struct HeatTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr bool NEEDS_CELL = true; // per-cell conductivity
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
@@ -202,6 +208,7 @@ struct HeatTri
 struct HeatTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr bool NEEDS_CELL = true;
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
