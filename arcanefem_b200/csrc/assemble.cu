@@ -24,6 +24,10 @@ namespace {
     A.nc_list = h->nc_list.as<uint32_t>();
     A.nc_slots = h->nc_slots.as<uint32_t>();
     A.slots_ok = h->slots_ok ? 1 : 0;
+    A.tile_blocks_max128 = h->tile_extents[0];
+    A.tile_adj_max128 = h->tile_extents[1];
+    A.tile_blocks_max64 = h->tile_extents[2];
+    A.tile_adj_max64 = h->tile_extents[3];
     A.counters = h->counters.as<unsigned long long>();
     A.accumulate = accumulate;
     int variant = h->variant;

@@ -79,9 +79,10 @@ struct b2f_context_s
   b2f::DevBuf row_index, columns, nb_nz_per_row, values; // BSRMatrix arrays
   b2f::DevBuf nc_ptr, nc_list, nc_slots; // node -> cell lists and the column-slot plan of the gather kernel
   bool slots_ok = false;
+  int tile_extents[4] = { 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then for 64-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
-  b2f::DevBuf counters; // 4 x u64
+  b2f::DevBuf counters; // 8 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..5] tile extents)
   b2f::DevBuf ws_keys_a, ws_keys_b, ws_tmp, ws_i32a, ws_i64; // workspace
   b2f::DevBuf coords_stage; // b2f_assemble_host
   b2f::GhostPlan ghost;

@@ -259,6 +259,23 @@ namespace {
     }
   }
 
+  // Largest gather tile of the plan, for tiles of 128 and of 64 consecutive rows: out = {blocks128, adj128, blocks64, adj64}.
+  __global__ void k_tile_extents(const int32_t* __restrict__ row_index, const int32_t* __restrict__ nc_ptr, long long nb_node, int* __restrict__ out)
+  {
+    const long long tile = (long long)blockIdx.x * blockDim.x + threadIdx.x; // tiles of 64 rows
+    const long long r0 = tile * 64;
+    if (r0 >= nb_node)
+      return;
+    const long long r1 = r0 + 64 < nb_node ? r0 + 64 : nb_node;
+    atomicMax(out + 2, row_index[r1] - row_index[r0]);
+    atomicMax(out + 3, nc_ptr[r1] - nc_ptr[r0]);
+    if ((tile & 1) == 0) {
+      const long long r2 = r0 + 128 < nb_node ? r0 + 128 : nb_node;
+      atomicMax(out + 0, row_index[r2] - row_index[r0]);
+      atomicMax(out + 1, nc_ptr[r2] - nc_ptr[r0]);
+    }
+  }
+
   __global__ void k_narrow_offsets(const long long* __restrict__ in, long long n, int32_t* __restrict__ out)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -314,7 +331,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
 
   h->has_pattern = false;
   h->has_csr = false;
-  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 4));
+  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 8));
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
   unsigned long long* counters = h->counters.as<unsigned long long>();
 
@@ -418,8 +435,13 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
                                                             h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
   B2F_CUDA(cudaGetLastError());
   {
+    int* ext = reinterpret_cast<int*>(counters + 4);
+    B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 4, stream));
+    k_tile_extents<<<grid_for((nn + 63) / 64, 128), 128, 0, stream>>>(h->row_index.as<int32_t>(), h->nc_ptr.as<int32_t>(), nn, ext);
+    B2F_CUDA(cudaGetLastError());
     unsigned long long long_rows = 0;
     B2F_CUDA(cudaMemcpyAsync(&long_rows, counters + 3, sizeof(long_rows), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 4, cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaStreamSynchronize(stream));
     h->slots_ok = (long_rows == 0);
   }

@@ -36,6 +36,7 @@ struct AssembleArgs
   const uint32_t* nc_list; // entries: cell * 4 + local index of the node in the cell
   const uint32_t* nc_slots; // per node->cell entry: column slots of the cell's other vertices, 10 bits each (see k_node_gather_slots)
   int slots_ok; // nc_slots is usable (every row has at most 1023 blocks)
+  int tile_blocks_max128, tile_adj_max128, tile_blocks_max64, tile_adj_max64; // largest tile of the plan (128 / 64 rows per tile)
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
 };
@@ -369,23 +370,54 @@ template <class Op>
 struct SlotsCfg
 {
   static constexpr int BS2 = Op::BS * Op::BS;
-  static constexpr int ROWS = (Op::BS == 1) ? 128 : 64;
-  static constexpr int ACC_BLOCKS = ROWS * ((Op::BS == 3) ? 18 : 22);
-  static constexpr int ADJ_CAP = ROWS * 32;
+  static constexpr int ROWS = (Op::BS == 1) ? 128 : 64; // block rows (= threads) per CTA
+  static constexpr int MAX_BLOCKS_PER_ROW = (Op::BS == 3) ? 18 : 24; // caps of the shared-memory tile (per row, on average)
+  static constexpr int MAX_ADJ_PER_ROW = 40;
   static constexpr int PAD = 8; // alignment slack of the bulk copies (source is aligned down to 16 bytes)
-  static constexpr size_t SMEM_BYTES = 16 + (size_t)ACC_BLOCKS * BS2 * sizeof(double) + (size_t)(ACC_BLOCKS + PAD) * sizeof(int32_t) + (size_t)(ADJ_CAP + PAD) * sizeof(uint32_t);
+  // capacities are rounded to multiples of 4 so that every region stays 16-byte aligned
+  static size_t smem_bytes(int acc_blocks, int adj_cap)
+  {
+    return 16 + (size_t)acc_blocks * BS2 * sizeof(double) + (size_t)(acc_blocks + PAD) * sizeof(int32_t) + (size_t)(adj_cap + PAD) * sizeof(uint32_t);
+  }
 };
 
+// One (row node, cell) pair: vertices X (X[0] = the row node), slot word w -> row-0 entries of Ke into acc.
 template <class Op, bool PER_BLOCK>
-__global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(AssembleArgs A, Op op)
+__device__ __forceinline__ void gather_pair(const Op& op, const double (&X)[Op::NV][3], uint32_t w, long long cell, int k, double* __restrict__ acc)
+{
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  const typename Op::Geom G = op.prepare(X, cell);
+#pragma unroll
+  for (int b = 0; b < NV; ++b) {
+    const int x = (b == 0) ? 0 : (int)((w >> (10 * (b - 1))) & 1023u);
+    double out[BS2];
+    op.block(G, 0, b, out);
+#pragma unroll
+    for (int i = 0; i < BS; ++i)
+#pragma unroll
+      for (int j = 0; j < BS; ++j)
+        acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] += out[i * BS + j];
+  }
+}
+
+template <class Op>
+__device__ __forceinline__ void fetch_pair(const double* __restrict__ coords, const int32_t* cols, uint32_t w, double (&X)[Op::NV][3])
+{
+#pragma unroll
+  for (int b = 1; b < Op::NV; ++b)
+    load_xyz(coords, cols[(w >> (10 * (b - 1))) & 1023u], X[b]);
+}
+
+template <class Op, bool PER_BLOCK>
+__global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(AssembleArgs A, Op op, int acc_blocks, int adj_cap)
 {
   using C = SlotsCfg<Op>;
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
   double* acc_s = reinterpret_cast<double*>(b2f_smem + 16);
-  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)C::ACC_BLOCKS * BS2);
-  uint32_t* slots_s = reinterpret_cast<uint32_t*>(cols_s + C::ACC_BLOCKS + C::PAD);
+  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)acc_blocks * BS2);
+  uint32_t* slots_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
 
   const int t = threadIdx.x;
   const long long row0 = (long long)blockIdx.x * C::ROWS;
@@ -395,7 +427,7 @@ __global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(Assemb
   const int32_t abeg = __ldg(A.nc_ptr + row0), aend = __ldg(A.nc_ptr + row0 + nrows);
   const int32_t vbeg_al = vbeg & ~3, abeg_al = abeg & ~3; // 16-byte aligned sources
   const int ncols_cp = ((vend - vbeg_al) + 3) & ~3, nadj_cp = ((aend - abeg_al) + 3) & ~3;
-  const bool fits = (vend - vbeg <= C::ACC_BLOCKS) && (ncols_cp <= C::ACC_BLOCKS + C::PAD) && (nadj_cp <= C::ADJ_CAP + C::PAD);
+  const bool fits = (vend - vbeg <= acc_blocks) && (ncols_cp <= acc_blocks + C::PAD) && (nadj_cp <= adj_cap + C::PAD);
   if (!fits) { // oversized tile (very long rows): search-based path on global memory
     if (t == 0)
       atomicAdd(A.counters + 1, 1ull);
@@ -422,58 +454,50 @@ __global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(Assemb
     for (int q = t; q < nval; q += C::ROWS)
       acc_s[q] = 0.0;
   }
+  // per-row setup overlaps the bulk copies
+  long long row = row0 + t;
+  int32_t rb = 0, qb = 0;
+  int k = 0, npair = 0;
+  bool own = false;
+  double XA[NV][3], XB[NV][3];
+  if (t < nrows) {
+    rb = __ldg(A.row_index + row);
+    k = __ldg(A.row_index + row + 1) - rb;
+    own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+    qb = __ldg(A.nc_ptr + row);
+    npair = own ? (__ldg(A.nc_ptr + row + 1) - qb) : 0;
+    load_xyz(A.coords, (int32_t)row, XA[0]);
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+      XB[0][d] = XA[0][d];
+  }
   mbar_wait(bar, 0);
   __syncthreads();
 
-  if (t < nrows) {
-    const long long row = row0 + t;
-    const int32_t rb = __ldg(A.row_index + row);
-    const int k = __ldg(A.row_index + row + 1) - rb;
-    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
-    if (own) {
-      double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
-      const int32_t* cols = cols_s + (rb - vbeg_al);
-      const int32_t qb = __ldg(A.nc_ptr + row), qe = __ldg(A.nc_ptr + row + 1);
-      const uint32_t* sl = slots_s + (qb - abeg_al);
-      const int npair = qe - qb;
-      double X[NV][3], Y[NV - 1][3];
-      load_xyz(A.coords, (int32_t)row, X[0]);
-      uint32_t w = 0, wn = 0;
-      if (npair > 0) {
-        wn = sl[0];
-#pragma unroll
-        for (int b = 1; b < NV; ++b)
-          load_xyz(A.coords, cols[(wn >> (10 * (b - 1))) & 1023u], Y[b - 1]);
+  if (npair > 0) {
+    double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
+    const int32_t* cols = cols_s + (rb - vbeg_al);
+    const uint32_t* sl = slots_s + (qb - abeg_al);
+    const uint32_t* cl = A.nc_list + qb;
+    // two register sets used alternately: the vertices of pair p+1 are in flight while pair p is evaluated
+    uint32_t wA = sl[0], wB = 0;
+    fetch_pair<Op>(A.coords, cols, wA, XA);
+    int p = 0;
+    while (true) {
+      if (p + 1 < npair) {
+        wB = sl[p + 1];
+        fetch_pair<Op>(A.coords, cols, wB, XB);
       }
-      for (int p = 0; p < npair; ++p) {
-        w = wn;
-#pragma unroll
-        for (int b = 1; b < NV; ++b)
-#pragma unroll
-          for (int d = 0; d < 3; ++d)
-            X[b][d] = Y[b - 1][d];
-        if (p + 1 < npair) { // prefetch the next pair's vertices while this one is evaluated
-          wn = sl[p + 1];
-#pragma unroll
-          for (int b = 1; b < NV; ++b)
-            load_xyz(A.coords, cols[(wn >> (10 * (b - 1))) & 1023u], Y[b - 1]);
-        }
-        long long cell = 0;
-        if (Op::NEEDS_CELL)
-          cell = __ldg(A.nc_list + qb + p) >> 2;
-        const typename Op::Geom G = op.prepare(X, cell);
-#pragma unroll
-        for (int b = 0; b < NV; ++b) {
-          const int x = (b == 0) ? 0 : (int)((w >> (10 * (b - 1))) & 1023u);
-          double out[BS2];
-          op.block(G, 0, b, out);
-#pragma unroll
-          for (int i = 0; i < BS; ++i)
-#pragma unroll
-            for (int j = 0; j < BS; ++j)
-              acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] += out[i * BS + j];
-        }
+      gather_pair<Op, PER_BLOCK>(op, XA, wA, Op::NEEDS_CELL ? (long long)(__ldg(cl + p) >> 2) : 0ll, k, acc);
+      if (++p >= npair)
+        break;
+      if (p + 1 < npair) {
+        wA = sl[p + 1];
+        fetch_pair<Op>(A.coords, cols, wA, XA);
       }
+      gather_pair<Op, PER_BLOCK>(op, XB, wB, Op::NEEDS_CELL ? (long long)(__ldg(cl + p) >> 2) : 0ll, k, acc);
+      if (++p >= npair)
+        break;
     }
   }
 
@@ -500,12 +524,21 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
   if (variant == VARIANT_NODE_GATHER && A.slots_ok) {
     using C = SlotsCfg<Op>;
     auto kern = k_node_gather_slots<Op, PER_BLOCK>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+    // shared-memory tile sized to what this mesh needs (largest tile of the plan), capped: oversized tiles take the
+    // global path, so a few very long rows cannot lower the occupancy of every other tile
+    const int tb = (C::ROWS == 128) ? A.tile_blocks_max128 : A.tile_blocks_max64;
+    const int ta = (C::ROWS == 128) ? A.tile_adj_max128 : A.tile_adj_max64;
+    int acc_blocks = tb < C::ROWS * C::MAX_BLOCKS_PER_ROW ? tb : C::ROWS * C::MAX_BLOCKS_PER_ROW;
+    int adj_cap = ta < C::ROWS * C::MAX_ADJ_PER_ROW ? ta : C::ROWS * C::MAX_ADJ_PER_ROW;
+    acc_blocks = (acc_blocks + 3) & ~3;
+    adj_cap = (adj_cap + 3) & ~3;
+    const size_t smem = C::smem_bytes(acc_blocks, adj_cap);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
       return e;
     const long long grid = (A.nb_node + C::ROWS - 1) / C::ROWS;
     if (grid > 0)
-      kern<<<(unsigned)grid, C::ROWS, C::SMEM_BYTES, stream>>>(A, op);
+      kern<<<(unsigned)grid, C::ROWS, smem, stream>>>(A, op, acc_blocks, adj_cap);
     return cudaGetLastError();
   }
   if (variant == VARIANT_NODE_GATHER) {
