@@ -16,10 +16,11 @@ from .bsr import (  # noqa: F401
     ASM_CELL_ATOMIC_WARPAGG,
     ASM_DEFAULT,
     ASM_NODE_GATHER,
+    ASM_NODE_GATHER_SLOTS,
 )
 from . import mesh  # noqa: F401
 
 __all__ = [
     "B2FError", "lib_path", "load_library", "BSRFormat", "BSRMatrix", "CSRFormatView", "DoFLinearSystem", "Operator",
-    "ASM_DEFAULT", "ASM_CELL_ATOMIC", "ASM_CELL_ATOMIC_WARPAGG", "ASM_NODE_GATHER", "mesh",
+    "ASM_DEFAULT", "ASM_CELL_ATOMIC", "ASM_CELL_ATOMIC_WARPAGG", "ASM_NODE_GATHER", "ASM_NODE_GATHER_SLOTS", "mesh",
 ]

@@ -52,9 +52,14 @@ class Neumann(C.Structure):
                 ("value_z", C.c_double)]
 
 
+class PlanView(C.Structure):
+    _fields_ = [("nb_node", C.c_int64), ("nb_pair", C.c_int64), ("nb_fan_step", C.c_int64), ("nc_ptr", C.c_void_p), ("nc_list", C.c_void_p),
+                ("fan_ptr", C.c_void_p), ("fan_steps", C.c_void_p), ("fan_cell", C.c_void_p)]
+
+
 class Stats(C.Structure):
     _fields_ = [("nb_edge", C.c_int64), ("nb_col", C.c_int64), ("nb_nz", C.c_int64), ("columns_not_found", C.c_int64),
-                ("workspace_bytes", C.c_int64), ("resident_bytes", C.c_int64), ("gather_fallback_tiles", C.c_int64)]
+                ("workspace_bytes", C.c_int64), ("resident_bytes", C.c_int64), ("gather_fallback_tiles", C.c_int64), ("fan_steps", C.c_int64)]
 
 
 _H = C.c_void_p  # b2f_handle
@@ -77,6 +82,7 @@ PROTOTYPES = {
     "b2f_to_csr": (C.c_int, [_H, _P(CsrView), _S]),
     "b2f_get_system": (C.c_int, [_H, _P(SystemView)]),
     "b2f_get_stats": (C.c_int, [_H, _P(Stats)]),
+    "b2f_get_plan": (C.c_int, [_H, _P(PlanView)]),
     "b2f_set_value": (C.c_int, [_H, C.c_int64, C.c_int64, C.c_double]),
     "b2f_get_value": (C.c_int, [_H, C.c_int64, C.c_int64, _P(C.c_double)]),
     "b2f_dump": (C.c_int, [_H, C.c_char_p]),

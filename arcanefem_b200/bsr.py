@@ -22,7 +22,7 @@ import numpy as np
 from . import _lib
 from ._lib import check
 
-ASM_DEFAULT, ASM_CELL_ATOMIC, ASM_CELL_ATOMIC_WARPAGG, ASM_NODE_GATHER = 0, 1, 2, 3
+ASM_DEFAULT, ASM_CELL_ATOMIC, ASM_CELL_ATOMIC_WARPAGG, ASM_NODE_GATHER, ASM_NODE_GATHER_SLOTS = 0, 1, 2, 3, 4
 OP_LAPLACE, OP_ELASTICITY, OP_HEAT = 0, 1, 2
 ELIMINATE_NONE, ELIMINATE_ROW, ELIMINATE_ROW_COLUMN = 0, 1, 2
 
@@ -339,6 +339,17 @@ class BSRFormat:
         s = _lib.Stats()
         check(self._lib.b2f_get_stats(self._h, C.byref(s)))
         return {k: int(getattr(s, k)) for k, _ in _lib.Stats._fields_}
+
+    def plan(self):
+        """Gather plan arrays as tensors (views; "<u4" words are exposed as int32 bit patterns)."""
+        v = _lib.PlanView()
+        check(self._lib.b2f_get_plan(self._h, C.byref(v)))
+        out = {"nc_ptr": _as_tensor(v.nc_ptr, v.nb_node + 1, "<i4", self), "nc_list": _as_tensor(v.nc_list, v.nb_pair, "<i4", self)}
+        if v.fan_ptr:
+            out["fan_ptr"] = _as_tensor(v.fan_ptr, v.nb_node + 1, "<i4", self)
+            out["fan_steps"] = _as_tensor(v.fan_steps, v.nb_fan_step, "<i4", self)
+            out["fan_cell"] = _as_tensor(v.fan_cell, v.nb_fan_step, "<i4", self)
+        return out
 
     def spmv(self, x, y=None):
         torch = _torch()

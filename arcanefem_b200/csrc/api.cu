@@ -84,7 +84,7 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_OVERFLOW, "nb_node=%lld does not fit Int32 node ids", (long long)mesh->nb_node);
   if (!mesh->cell_node && mesh->nb_cell > 0)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node is null");
-  if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER)
+  if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -106,7 +106,7 @@ int b2f_destroy(b2f_handle h)
 {
   if (!h)
     return B2F_OK;
-  DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+  DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
                      &h->coords_stage, &h->ghost.send_rows, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_slot };
   for (DevBuf* b : bufs)
@@ -219,6 +219,23 @@ int b2f_get_system(b2f_handle h, b2f_system_view* out)
   return B2F_OK;
 }
 
+int b2f_get_plan(b2f_handle h, b2f_plan_view* out)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_plan: null output");
+  out->nb_node = h->mesh.nb_node;
+  out->nb_pair = h->mesh.nb_cell * h->nv;
+  out->nb_fan_step = h->fan_ok ? h->nb_fan_step : 0;
+  out->nc_ptr = h->nc_ptr.as<int32_t>();
+  out->nc_list = h->nc_list.as<uint32_t>();
+  out->fan_ptr = h->fan_ok ? h->fan_ptr.as<int32_t>() : nullptr;
+  out->fan_steps = h->fan_ok ? h->fan_steps.as<uint32_t>() : nullptr;
+  out->fan_cell = h->fan_ok ? h->fan_cell.as<uint32_t>() : nullptr;
+  return B2F_OK;
+}
+
 int b2f_get_stats(b2f_handle h, b2f_stats* out)
 {
   B2F_CHECK_HANDLE(h);
@@ -228,6 +245,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   out->nb_edge = h->nb_edge;
   out->nb_col = h->nb_col;
   out->nb_nz = h->nb_nz;
+  out->fan_steps = h->nb_fan_step;
   if (h->counters.p) {
     unsigned long long c[4] = { 0, 0, 0, 0 };
     B2F_CUDA(cudaMemcpy(c, h->counters.p, sizeof(c), cudaMemcpyDeviceToHost));
@@ -235,7 +253,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
     out->gather_fallback_tiles = (int64_t)c[1];
   }
   out->workspace_bytes = (int64_t)(h->ws_keys_a.bytes + h->ws_keys_b.bytes + h->ws_tmp.bytes + h->ws_i32a.bytes + h->ws_i64.bytes);
-  const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
+  const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                           &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage };
   for (const DevBuf* b : res)
     out->resident_bytes += (int64_t)b->bytes;

@@ -24,6 +24,10 @@ namespace {
     A.nc_list = h->nc_list.as<uint32_t>();
     A.nc_slots = h->nc_slots.as<uint32_t>();
     A.slots_ok = h->slots_ok ? 1 : 0;
+    A.fan_ptr = h->fan_ptr.as<int32_t>();
+    A.fan_steps = h->fan_steps.as<uint32_t>();
+    A.fan_cell = h->fan_cell.as<uint32_t>();
+    A.fan_ok = h->fan_ok ? 1 : 0;
     A.tile_blocks_max128 = h->tile_extents[0];
     A.tile_adj_max128 = h->tile_extents[1];
     A.tile_blocks_max64 = h->tile_extents[2];

@@ -79,6 +79,9 @@ struct b2f_context_s
   b2f::DevBuf row_index, columns, nb_nz_per_row, values; // BSRMatrix arrays
   b2f::DevBuf nc_ptr, nc_list, nc_slots; // node -> cell lists and the column-slot plan of the gather kernel
   bool slots_ok = false;
+  b2f::DevBuf fan_ptr, fan_steps, fan_cell; // fan-walk plan of the default gather kernel (one word per step, cell id per step)
+  bool fan_ok = false;
+  int64_t nb_fan_step = 0;
   int tile_extents[4] = { 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then for 64-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state

@@ -259,6 +259,228 @@ namespace {
     }
   }
 
+  // Plan of the fan-walk gather kernel (k_node_fan, include/b2f/assemble.cuh).  The cells incident to a node are visited
+  // along a path in which consecutive cells share a face through the node (a walk on the dual of the node's link), so
+  // every step brings in ONE new vertex: one coordinate gather, one accumulator load and one accumulator flush per
+  // cell instead of NV-1 of each, and one cross product carried over.  One 32-bit word per step:
+  // The window is (N, O): N the vertex that entered last, O the other one (tets only).
+  //   START  bit31 = 1 : (re)load the window; bits 0-9 slot of N, bits 10-19 slot of O (tets only)
+  //   EMIT   bit31 = 0 : bits 0-9 slot of the entering vertex C, which becomes N; bit 10 = which window vertex leaves
+  //                      afterwards (1: N, so O stays; 0: O, so the old N becomes O);
+  //                      bit 11 = the vertex order (row node, N, O, C) is an odd permutation of the cell's
+  // The walk is built greedily (next = unvisited face neighbour with the fewest unvisited neighbours, Warnsdorff's
+  // rule), restarting with a START word when it gets stuck; nearly every row is a single chain.  Rows with more than
+  // FAN_MAXC incident cells or more than 1023 blocks use one START + EMIT per cell / clear the `ok` flag.
+  constexpr int FAN_MAXC = 64;
+  constexpr unsigned FAN_START = 0x80000000u;
+
+  template <int NV, bool WRITE>
+  __global__ void __launch_bounds__(128) k_build_fan(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
+                                                     const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, long long nb_node,
+                                                     const int32_t* __restrict__ fan_ptr, int32_t* __restrict__ fan_count, uint32_t* __restrict__ fan_steps,
+                                                     uint32_t* __restrict__ fan_cell, unsigned long long* __restrict__ counters)
+  {
+    constexpr int NO = NV - 1; // other vertices of a cell
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nb_node)
+      return;
+    const int32_t rb = row_index[row];
+    const int k = row_index[row + 1] - rb;
+    const int32_t qb = nc_ptr[row];
+    const int m = nc_ptr[row + 1] - qb;
+    if (k > 1023) {
+      if (!WRITE) {
+        atomicAdd(counters + 3, 1ull);
+        fan_count[row] = 0;
+      }
+      return;
+    }
+    uint32_t* out = WRITE ? fan_steps + fan_ptr[row] : nullptr;
+    uint32_t* outc = WRITE ? fan_cell + fan_ptr[row] : nullptr;
+    int nout = 0;
+    auto slot_of = [&](int32_t c) {
+      int lo = 1, hi = k;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (columns[rb + mid] < c)
+          lo = mid + 1;
+        else
+          hi = mid;
+      }
+      return lo;
+    };
+    // parity of the vertex order (row node, w0, [w1,] c) given as positions in the cell
+    auto is_odd = [&](const int* pos) {
+      int inv = 0;
+      for (int i = 0; i < NV; ++i)
+        for (int j = i + 1; j < NV; ++j)
+          inv += pos[i] > pos[j];
+      return inv & 1;
+    };
+    if (m > FAN_MAXC) { // very high valence: no walk, every cell is its own chain
+      for (int q = 0; q < m; ++q) {
+        const uint32_t e = nc_list[qb + q];
+        const long long cell = e >> 2;
+        const int a = (int)(e & 3u);
+        int pos[NV];
+        uint32_t sl[NO];
+        pos[0] = a;
+        for (int f = 0; f < NO; ++f) {
+          pos[f + 1] = f < a ? f : f + 1;
+          sl[f] = (uint32_t)slot_of(cell_node[cell * NV + pos[f + 1]]);
+        }
+        if (WRITE) {
+          out[nout] = FAN_START | sl[0] | (NV == 4 ? (sl[1] << 10) : 0u);
+          outc[nout] = (uint32_t)cell;
+          out[nout + 1] = sl[NO - 1] | ((uint32_t)is_odd(pos) << 11);
+          outc[nout + 1] = (uint32_t)cell;
+        }
+        nout += 2;
+      }
+      if (!WRITE)
+        fan_count[row] = nout;
+      return;
+    }
+    uint16_t v[FAN_MAXC][NO]; // slots of the other vertices, in cell order
+    int8_t nb[FAN_MAXC][NO]; // neighbour across the face that omits vertex f (shares all the others), -1 if none
+    uint8_t apos[FAN_MAXC];
+    for (int i = 0; i < m; ++i) {
+      const uint32_t e = nc_list[qb + i];
+      const long long cell = e >> 2;
+      const int a = (int)(e & 3u);
+      apos[i] = (uint8_t)a;
+      for (int f = 0; f < NO; ++f) {
+        v[i][f] = (uint16_t)slot_of(cell_node[cell * NV + (f < a ? f : f + 1)]);
+        nb[i][f] = -1;
+      }
+    }
+    for (int i = 0; i < m; ++i)
+      for (int j = i + 1; j < m; ++j) {
+        int common = 0, fi = -1, fj = -1; // fi: the vertex of i not shared, fj: same for j
+        bool in_j[NO];
+        for (int g = 0; g < NO; ++g)
+          in_j[g] = false;
+        for (int f = 0; f < NO; ++f) {
+          bool hit = false;
+          for (int g = 0; g < NO; ++g)
+            if (v[i][f] == v[j][g]) {
+              hit = true;
+              in_j[g] = true;
+            }
+          if (hit)
+            ++common;
+          else
+            fi = f;
+        }
+        if (common == NO - 1) {
+          for (int g = 0; g < NO; ++g)
+            if (!in_j[g])
+              fj = g;
+          nb[i][fi] = (int8_t)j;
+          nb[j][fj] = (int8_t)i;
+        }
+      }
+    unsigned long long visited = 0ull;
+    auto unvisited_degree = [&](int i) {
+      int d = 0;
+      for (int f = 0; f < NO; ++f)
+        d += (nb[i][f] >= 0 && !((visited >> nb[i][f]) & 1ull));
+      return d;
+    };
+    // best unvisited neighbour of i: returns the omitted-vertex index f (neighbour = nb[i][f]) or -1
+    auto best_next = [&](int i) {
+      int best = -1, bd = 99;
+      for (int f = 0; f < NO; ++f) {
+        const int j = nb[i][f];
+        if (j < 0 || ((visited >> j) & 1ull))
+          continue;
+        const int d = unvisited_degree(j);
+        if (d < bd || (d == bd && j < nb[i][best])) {
+          bd = d;
+          best = f;
+        }
+      }
+      return best;
+    };
+    int cur = -1, nvis = 0;
+    uint32_t win[2] = { 0u, 0u }; // slots currently held as N, O
+    while (nvis < m) {
+      bool start = false;
+      if (cur < 0) {
+        int bd = 99;
+        for (int i = 0; i < m; ++i)
+          if (!((visited >> i) & 1ull)) {
+            const int d = unvisited_degree(i);
+            if (d < bd) {
+              bd = d;
+              cur = i;
+            }
+          }
+        start = true;
+      }
+      visited |= 1ull << cur;
+      ++nvis;
+      int fc = -1; // vertex of cur that enters as C
+      if (!start) {
+        // continuation: the window must hold every vertex of cur but one (checked, so a non-manifold link cannot
+        // desynchronise the walk: it just restarts)
+        int inwin = 0;
+        for (int f = 0; f < NO; ++f) {
+          bool hit = false;
+          for (int w = 0; w < NV - 2; ++w)
+            hit |= (v[cur][f] == win[w]);
+          if (hit)
+            ++inwin;
+          else
+            fc = f;
+        }
+        if (inwin != NO - 1)
+          start = true;
+      }
+      int fnext = best_next(cur); // vertex of cur that the next cell does not contain (dropped after this cell)
+      if (!start && fnext == fc)
+        fnext = -1;
+      if (start) {
+        // order the cell so that the dropped vertex sits in the window and C is shared with the next cell
+        fc = (fnext == NO - 1) ? 0 : NO - 1;
+        int w = 0;
+        if (fnext >= 0)
+          win[w++] = v[cur][fnext];
+        for (int f = 0; f < NO; ++f)
+          if (f != fc && f != fnext)
+            win[w++] = v[cur][f];
+        if (WRITE) {
+          out[nout] = FAN_START | win[0] | (NV == 4 ? (win[1] << 10) : 0u);
+          outc[nout] = nc_list[qb + cur] >> 2;
+        }
+        ++nout;
+      }
+      const uint32_t sc = v[cur][fc];
+      // positions in the cell of (row node, A, [B,] C)
+      int pos[NV];
+      pos[0] = apos[cur];
+      for (int w = 0; w < NV - 2; ++w)
+        for (int f = 0; f < NO; ++f)
+          if (v[cur][f] == win[w])
+            pos[1 + w] = f < apos[cur] ? f : f + 1;
+      pos[NV - 1] = fc < apos[cur] ? fc : fc + 1;
+      uint32_t drop_n = 0;
+      if (fnext >= 0 && NV == 4)
+        drop_n = (v[cur][fnext] == win[0]) ? 1u : 0u;
+      if (WRITE) {
+        out[nout] = sc | (drop_n << 10) | ((uint32_t)is_odd(pos) << 11);
+        outc[nout] = nc_list[qb + cur] >> 2;
+      }
+      ++nout;
+      if (NV == 4 && !drop_n)
+        win[1] = win[0];
+      win[0] = sc;
+      cur = fnext >= 0 ? nb[cur][fnext] : -1;
+    }
+    if (!WRITE)
+      fan_count[row] = nout;
+  }
+
   // Largest gather tile of the plan, for tiles of 128 and of 64 consecutive rows: out = {blocks128, adj128, blocks64, adj64}.
   __global__ void k_tile_extents(const int32_t* __restrict__ row_index, const int32_t* __restrict__ nc_ptr, long long nb_node, int* __restrict__ out)
   {
@@ -424,26 +646,61 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
   B2F_CUDA(cudaGetLastError());
 
-  // --- plan of the slots-driven gather kernel
-  B2F_CUDA(h->nc_slots.alloc(sizeof(uint32_t) * (size_t)(nb_adj + 8)));
+  // --- plan of the gather kernel: fan walk (default) or the column-slot words of the first-generation kernel
+  const int32_t* tile_ptr = h->nc_ptr.as<int32_t>();
   B2F_CUDA(cudaMemsetAsync(counters + 3, 0, sizeof(unsigned long long), stream));
-  if (nv == 3)
-    k_build_slots<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
-                                                            h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
-  else
-    k_build_slots<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
-                                                            h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
-  B2F_CUDA(cudaGetLastError());
+  h->fan_ok = false;
+  h->slots_ok = false;
+  if (h->variant == B2F_ASM_NODE_GATHER_SLOTS) {
+    B2F_CUDA(h->nc_slots.alloc(sizeof(uint32_t) * (size_t)(nb_adj + 8)));
+    if (nv == 3)
+      k_build_slots<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
+                                                              h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
+    else
+      k_build_slots<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, h->row_index.as<int32_t>(), h->columns.as<int32_t>(), h->nc_ptr.as<int32_t>(),
+                                                              h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
+    B2F_CUDA(cudaGetLastError());
+  }
+  else if (h->variant == B2F_ASM_NODE_GATHER) {
+    B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+    int32_t* fan_count = h->ws_i32a.as<int32_t>();
+    const int32_t* ri = h->row_index.as<int32_t>();
+    const int32_t* co = h->columns.as<int32_t>();
+    const int32_t* ncp = h->nc_ptr.as<int32_t>();
+    const uint32_t* ncl = h->nc_list.as<uint32_t>();
+    if (nv == 3)
+      k_build_fan<3, false><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, nullptr, fan_count, nullptr, nullptr, counters);
+    else
+      k_build_fan<4, false><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, nullptr, fan_count, nullptr, nullptr, counters);
+    B2F_CUDA(cudaGetLastError());
+    B2F_CUDA(h->fan_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+    long long nb_step = 0;
+    rc = scan_counts(h, fan_count, nn, h->fan_ptr.as<int32_t>(), &nb_step, stream);
+    if (rc != B2F_OK)
+      return rc;
+    h->nb_fan_step = nb_step;
+    B2F_CUDA(h->fan_steps.alloc(sizeof(uint32_t) * (size_t)(nb_step + 8)));
+    B2F_CUDA(h->fan_cell.alloc(sizeof(uint32_t) * (size_t)(nb_step + 8)));
+    if (nv == 3)
+      k_build_fan<3, true><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, h->fan_ptr.as<int32_t>(), nullptr, h->fan_steps.as<uint32_t>(),
+                                                                  h->fan_cell.as<uint32_t>(), counters);
+    else
+      k_build_fan<4, true><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, h->fan_ptr.as<int32_t>(), nullptr, h->fan_steps.as<uint32_t>(),
+                                                                  h->fan_cell.as<uint32_t>(), counters);
+    B2F_CUDA(cudaGetLastError());
+    tile_ptr = h->fan_ptr.as<int32_t>();
+  }
   {
     int* ext = reinterpret_cast<int*>(counters + 4);
     B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 4, stream));
-    k_tile_extents<<<grid_for((nn + 63) / 64, 128), 128, 0, stream>>>(h->row_index.as<int32_t>(), h->nc_ptr.as<int32_t>(), nn, ext);
+    k_tile_extents<<<grid_for((nn + 63) / 64, 128), 128, 0, stream>>>(h->row_index.as<int32_t>(), tile_ptr, nn, ext);
     B2F_CUDA(cudaGetLastError());
     unsigned long long long_rows = 0;
     B2F_CUDA(cudaMemcpyAsync(&long_rows, counters + 3, sizeof(long_rows), cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 4, cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaStreamSynchronize(stream));
-    h->slots_ok = (long_rows == 0);
+    h->slots_ok = (h->variant == B2F_ASM_NODE_GATHER_SLOTS) && (long_rows == 0);
+    h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0);
   }
 
   // --- linear-system state (HypreDoFLinearSystem.cc:224-242)

@@ -57,7 +57,8 @@ typedef enum b2f_assembly_variant {
   B2F_ASM_DEFAULT = 0, /* the library's choice (node gather) */
   B2F_ASM_CELL_ATOMIC = 1, /* cell-wise, one fp64 atomic per entry (BSRFormat.h:786-898) */
   B2F_ASM_CELL_ATOMIC_WARPAGG = 2, /* cell-wise, same-address adds pre-reduced inside the warp */
-  B2F_ASM_NODE_GATHER = 3 /* node-wise, atomic-free, deterministic (BSRFormat.h:937-1068) */
+  B2F_ASM_NODE_GATHER = 3, /* node-wise, atomic-free, deterministic (BSRFormat.h:937-1068); fan-walk plan */
+  B2F_ASM_NODE_GATHER_SLOTS = 4 /* first-generation node gather (one column-slot word per node/cell pair); kept for A/B measurements */
 } b2f_assembly_variant;
 
 typedef enum b2f_operator_kind {
@@ -150,6 +151,18 @@ typedef struct b2f_neumann {
   double value_x, value_y, value_z;
 } b2f_neumann;
 
+/* Plan of the node-gather kernels (library-internal layout, see arcanefem_b200/csrc/sparsity.cu). */
+typedef struct b2f_plan_view {
+  int64_t nb_node;
+  int64_t nb_pair; /* node/cell incidences */
+  int64_t nb_fan_step;
+  const int32_t* nc_ptr; /* [nb_node + 1] */
+  const uint32_t* nc_list; /* [nb_pair] cell * 4 + local index of the node in the cell, ascending per node */
+  const int32_t* fan_ptr; /* [nb_node + 1] or NULL when the variant has no fan plan */
+  const uint32_t* fan_steps; /* [nb_fan_step] */
+  const uint32_t* fan_cell; /* [nb_fan_step] */
+} b2f_plan_view;
+
 typedef struct b2f_stats {
   int64_t nb_edge;
   int64_t nb_col;
@@ -158,6 +171,7 @@ typedef struct b2f_stats {
   int64_t workspace_bytes; /* temporary device bytes held (sort buffers); 0 after b2f_release_workspace */
   int64_t resident_bytes; /* device bytes owned by the handle, workspace excluded */
   int64_t gather_fallback_tiles; /* node-gather tiles that overflowed shared memory and ran on the global path */
+  int64_t fan_steps; /* words of the fan-walk plan (incident node/cell pairs + chain starts) */
 } b2f_stats;
 
 int b2f_version(void);
@@ -187,6 +201,8 @@ int b2f_get_bsr(b2f_handle h, b2f_bsr_view* out);
  * BS = 1; device expansion of rows/columns when BS > 1 (values alias; needs B2F_LAYOUT_PER_ROW). */
 int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream);
 int b2f_get_system(b2f_handle h, b2f_system_view* out);
+/* Device pointers of the gather plan built by b2f_compute_sparsity (read-only; for inspection and tests). */
+int b2f_get_plan(b2f_handle h, b2f_plan_view* out);
 int b2f_get_stats(b2f_handle h, b2f_stats* out);
 
 /* BSRMatrix::setValue / getValue by scalar (row dof, col dof), BSRFormat.h:176-189 (host convenience,

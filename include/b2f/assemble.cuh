@@ -17,6 +17,7 @@
 //                   value is written exactly once and no zero-fill pass is needed.
 #pragma once
 #include <cstdint>
+#include <utility>
 #include <cuda_runtime.h>
 #include "element_ops.cuh"
 
@@ -36,12 +37,16 @@ struct AssembleArgs
   const uint32_t* nc_list; // entries: cell * 4 + local index of the node in the cell
   const uint32_t* nc_slots; // per node->cell entry: column slots of the cell's other vertices, 10 bits each (see k_node_gather_slots)
   int slots_ok; // nc_slots is usable (every row has at most 1023 blocks)
+  const int32_t* fan_ptr; // node -> fan-walk step offsets, nb_node + 1
+  const uint32_t* fan_steps; // one word per step (see k_node_fan)
+  const uint32_t* fan_cell; // cell id of every step (read by operators with per-cell data only)
+  int fan_ok; // the fan plan is usable
   int tile_blocks_max128, tile_adj_max128, tile_blocks_max64, tile_adj_max64; // largest tile of the plan (128 / 64 rows per tile)
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
 };
 
-enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3 };
+enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };
 
 // Scalar index of entry (i,j) of the x-th block of a block row that starts at block rb and holds k blocks
 // (femutils/BSRFormat.h:145-171).
@@ -516,12 +521,336 @@ __global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(Assemb
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Node-wise gather, fan-walk kernel — the default.
+//
+// ncu of the slots kernel on the 50M-tet cube (profiles/r01_gather_slots.txt) shows the L1 data pipe saturated
+// (l1tex__data_pipe_lsu_wavefronts 96.6 %): 9 scattered coordinate gathers + 8 shared-memory accumulator accesses per
+// (row node, cell) pair.  The fan plan (sparsity.cu, k_build_fan) orders the cells around a node so that consecutive
+// cells share a face through the node.  A thread then keeps a window of the shared vertices (tets: A, B with
+// n = eA x eB; triangles: A) in registers together with their accumulators, and every step
+//   * gathers ONE new vertex C (coordinates prefetched one step ahead) and loads its accumulator,
+//   * builds the cell's un-normalised gradients from the carried cross product: gA = eB x eC, gB = eC x eA, gC = n,
+//   * adds row 0 of Ke into the three register accumulators + the register diagonal,
+//   * flushes the accumulator of the vertex that leaves the window (plain store: it was loaded on entry) and replaces
+//     that vertex by C in place (n <- -gA or -gB).
+// Per cell: 3 gathers + 1 LDS + 1 STS of accumulators instead of 9 + 4 + 4, and 12 fewer fp64 operations.
+// ---------------------------------------------------------------------------------------------------
+constexpr unsigned FAN_START = 0x80000000u;
+
+// Operator entry points of the fan kernel, selected by arity (only the matching one is instantiated).
+template <class Op>
+__device__ __forceinline__ auto tet_finish(const Op& op, const TetGeom& T, long long cell, bool odd) -> decltype(op.finish(T, cell, odd))
+{
+  return op.finish(T, cell, odd);
+}
+template <class Op>
+__device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3], const double (&XA)[3], const double (&XC)[3], long long cell, bool odd)
+  -> decltype(op.prepare_oriented(std::declval<const double (&)[3][3]>(), cell, odd))
+{
+  const double X[3][3] = { { X0[0], X0[1], X0[2] }, { XA[0], XA[1], XA[2] }, { XC[0], XC[1], XC[2] } };
+  return op.prepare_oriented(X, cell, odd);
+}
+
+template <int BS, bool PER_BLOCK>
+__device__ __forceinline__ void load_block(const double* __restrict__ acc, int k, int x, double (&out)[BS * BS])
+{
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+#pragma unroll
+    for (int j = 0; j < BS; ++j)
+      out[i * BS + j] = acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)];
+}
+
+template <int BS, bool PER_BLOCK>
+__device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int x, const double (&v)[BS * BS])
+{
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+#pragma unroll
+    for (int j = 0; j < BS; ++j)
+      acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] = v[i * BS + j];
+}
+
+// One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
+// receive the vertex that enters; the caller alternates two register sets between the roles N and C, so the "C becomes
+// N" renaming costs no instruction.  Tets carry m = +-(eN x eO); flip tells the sign (m = -(eN x eO) when set).
+template <class Op, bool PER_BLOCK>
+__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], double* __restrict__ acc, const int32_t* __restrict__ cols,
+                                         int k, uint32_t wc, const double (&Xc)[3], long long cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
+                                         double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], bool& flip, double (&eC)[3],
+                                         double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
+{
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  sC = (int)(wc & 1023u);
+  if (wc & FAN_START) {
+    // flush the whole window before loading anything: a vertex of the new window may still be held by the old one
+    if (sN)
+      store_block<BS, PER_BLOCK>(acc, k, sN, accN);
+    if constexpr (NV == 4) {
+      if (sO)
+        store_block<BS, PER_BLOCK>(acc, k, sO, accO);
+    }
+    load_block<BS, PER_BLOCK>(acc, k, sC, accC);
+    if constexpr (NV == 4) {
+      sO = (int)((wc >> 10) & 1023u);
+      load_block<BS, PER_BLOCK>(acc, k, sO, accO);
+      double XB[3];
+      load_xyz(coords, cols[sO], XB);
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        eC[d] = Xc[d] - X0[d];
+        eO[d] = XB[d] - X0[d];
+      }
+      m[0] = eC[1] * eO[2] - eC[2] * eO[1];
+      m[1] = eC[2] * eO[0] - eC[0] * eO[2];
+      m[2] = eC[0] * eO[1] - eC[1] * eO[0];
+      flip = false;
+    }
+    else {
+#pragma unroll
+      for (int d = 0; d < 3; ++d)
+        eC[d] = Xc[d]; // triangles keep the vertex itself
+    }
+    return;
+  }
+  const bool odd = (wc >> 11) & 1u;
+  load_block<BS, PER_BLOCK>(acc, k, sC, accC);
+  double out[BS2];
+  if constexpr (NV == 4) {
+    const bool dropN = (wc >> 10) & 1u;
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+      eC[d] = Xc[d] - X0[d];
+    // local vertices (0, 1, 2, 3) = (row node, N, O, C): g1 = eO x eC, g2 = eC x eN, g3 = eN x eO
+    TetGeom T;
+    T.g[1][0] = eO[1] * eC[2] - eO[2] * eC[1];
+    T.g[1][1] = eO[2] * eC[0] - eO[0] * eC[2];
+    T.g[1][2] = eO[0] * eC[1] - eO[1] * eC[0];
+    T.g[2][0] = eC[1] * eN[2] - eC[2] * eN[1];
+    T.g[2][1] = eC[2] * eN[0] - eC[0] * eN[2];
+    T.g[2][2] = eC[0] * eN[1] - eC[1] * eN[0];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      // conditional sign flip on the integer pipe (the fp64 pipe is the busy one)
+      const long long bits = __double_as_longlong(m[d]) ^ (flip ? (long long)0x8000000000000000ull : 0ll);
+      T.g[NV - 1][d] = __longlong_as_double(bits);
+      T.g[0][d] = -(T.g[1][d] + T.g[2][d] + T.g[NV - 1][d]);
+    }
+    const double det = eC[0] * T.g[NV - 1][0] + eC[1] * T.g[NV - 1][1] + eC[2] * T.g[NV - 1][2];
+    T.vol6 = fabs(det);
+    T.s = 1.0 / (6.0 * T.vol6);
+    const auto G = tet_finish(op, T, cell, odd);
+    op.block(G, 0, 1, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accN[e] += out[e];
+    op.block(G, 0, 2, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accO[e] += out[e];
+    op.block(G, 0, NV - 1, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accC[e] += out[e];
+    op.block(G, 0, 0, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      diag[e] += out[e];
+    // one vertex leaves: its accumulator is flushed (plain store: it was loaded on entry).  C becomes N (renaming by
+    // the caller); the vertex that stays becomes / remains O.  New m: (eC x eN) = g2 if N stays, (eC x eO) = -g1 if O stays.
+    double leave[BS2];
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      leave[e] = dropN ? accN[e] : accO[e];
+    store_block<BS, PER_BLOCK>(acc, k, dropN ? sN : sO, leave);
+    if (!dropN) {
+      sO = sN;
+#pragma unroll
+      for (int e = 0; e < BS2; ++e)
+        accO[e] = accN[e];
+    }
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      eO[d] = dropN ? eO[d] : eN[d];
+      m[d] = dropN ? T.g[1][d] : T.g[2][d];
+    }
+    flip = dropN;
+  }
+  else {
+    const auto G = tri_prepare(op, X0, eN, Xc, cell, odd);
+    op.block(G, 0, 1, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accN[e] += out[e];
+    op.block(G, 0, 2, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accC[e] += out[e];
+    op.block(G, 0, 0, out);
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      diag[e] += out[e];
+    store_block<BS, PER_BLOCK>(acc, k, sN, accN);
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+      eC[d] = Xc[d];
+  }
+}
+
+template <class Op, bool PER_BLOCK>
+__global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
+{
+  using C = SlotsCfg<Op>;
+  constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  extern __shared__ __align__(16) unsigned char b2f_smem[];
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
+  double* acc_s = reinterpret_cast<double*>(b2f_smem + 16);
+  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)acc_blocks * BS2);
+  uint32_t* steps_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
+
+  const int t = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * C::ROWS;
+  const long long left = A.nb_node - row0;
+  const int nrows = left < C::ROWS ? (int)left : C::ROWS;
+  const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
+  const int32_t abeg = __ldg(A.fan_ptr + row0), aend = __ldg(A.fan_ptr + row0 + nrows);
+  const int32_t vbeg_al = vbeg & ~3, abeg_al = abeg & ~3; // 16-byte aligned sources
+  const int ncols_cp = ((vend - vbeg_al) + 3) & ~3, nstep_cp = ((aend - abeg_al) + 3) & ~3;
+  const bool fits = (vend - vbeg <= acc_blocks) && (ncols_cp <= acc_blocks + C::PAD) && (nstep_cp <= step_cap + C::PAD);
+  if (!fits) { // oversized tile (very long rows): search-based path on global memory
+    if (t == 0)
+      atomicAdd(A.counters + 1, 1ull);
+    gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, __ldg(A.nc_ptr + row0), __ldg(A.nc_ptr + row0 + nrows), nullptr, nullptr, nullptr);
+    return;
+  }
+
+  if (t == 0)
+    mbar_init(bar, 1);
+  __syncthreads();
+  if (t == 0) {
+    mbar_expect_tx(bar, (uint32_t)(ncols_cp + nstep_cp) * 4u);
+    if (ncols_cp > 0)
+      tma_load_1d(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
+    if (nstep_cp > 0)
+      tma_load_1d(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
+  }
+  const int nval = (vend - vbeg) * BS2;
+  if (A.accumulate) {
+    for (int q = t; q < nval; q += C::ROWS)
+      acc_s[q] = A.values[(long long)vbeg * BS2 + q];
+  }
+  else {
+    for (int q = t; q < nval; q += C::ROWS)
+      acc_s[q] = 0.0;
+  }
+  // per-row setup overlaps the bulk copies
+  const long long row = row0 + t;
+  int32_t rb = 0, qb = 0;
+  int k = 0, nstep = 0;
+  double X0[3] = { 0.0, 0.0, 0.0 };
+  if (t < nrows) {
+    rb = __ldg(A.row_index + row);
+    k = __ldg(A.row_index + row + 1) - rb;
+    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+    qb = __ldg(A.fan_ptr + row);
+    nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
+    load_xyz(A.coords, (int32_t)row, X0);
+  }
+  mbar_wait(bar, 0);
+  __syncthreads();
+
+  if (nstep > 0) {
+    double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
+    const int32_t* cols = cols_s + (rb - vbeg_al);
+    const uint32_t* st = steps_s + (qb - abeg_al);
+    const uint32_t* cl = A.fan_cell + qb;
+    double diag[BS2];
+    load_block<BS, PER_BLOCK>(acc, k, 0, diag);
+    // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
+    double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
+    int sP = 0, sQ = 0, sO = 0;
+    bool flip = false;
+    double XP[3], XQ[3]; // coordinates of the entering vertex, prefetched one step ahead
+    uint32_t wP = st[0], wQ = 0;
+    load_xyz(A.coords, cols[wP & 1023u], XP);
+    int p = 0;
+    bool newest_is_Q = false;
+    while (true) {
+      // step p: P enters (Q is the newest)
+      if (p + 1 < nstep) {
+        wQ = st[p + 1];
+        load_xyz(A.coords, cols[wQ & 1023u], XQ);
+      }
+      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wP, XP, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, flip, eP, accP, sP,
+                              diag);
+      newest_is_Q = false;
+      if (++p >= nstep)
+        break;
+      // step p: Q enters (P is the newest)
+      if (p + 1 < nstep) {
+        wP = st[p + 1];
+        load_xyz(A.coords, cols[wP & 1023u], XP);
+      }
+      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wQ, XQ, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, flip, eQ, accQ, sQ,
+                              diag);
+      newest_is_Q = true;
+      if (++p >= nstep)
+        break;
+    }
+    if (newest_is_Q) {
+      if (sQ)
+        store_block<BS, PER_BLOCK>(acc, k, sQ, accQ);
+    }
+    else {
+      if (sP)
+        store_block<BS, PER_BLOCK>(acc, k, sP, accP);
+    }
+    if constexpr (NV == 4) {
+      if (sO)
+        store_block<BS, PER_BLOCK>(acc, k, sO, accO);
+    }
+    store_block<BS, PER_BLOCK>(acc, k, 0, diag);
+  }
+
+  __syncthreads();
+  const long long base = (long long)vbeg * BS2;
+  const int head = (int)(base & 1); // values is 16-byte aligned at element 0
+  if (t < head && t < nval)
+    A.values[base + t] = acc_s[t];
+  const int nvec = (nval - head) >> 1;
+  double2* dst = reinterpret_cast<double2*>(A.values + base + head);
+  for (int q = t; q < nvec; q += C::ROWS)
+    dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+  const int tail = head + 2 * nvec;
+  if (t == 0 && tail < nval)
+    A.values[base + tail] = acc_s[tail];
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Launch
 // ---------------------------------------------------------------------------------------------------
 template <class Op, bool PER_BLOCK>
 inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
 {
-  if (variant == VARIANT_NODE_GATHER && A.slots_ok) {
+  if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
+    using C = SlotsCfg<Op>;
+    auto kern = k_node_fan<Op, PER_BLOCK>;
+    const int tb = (C::ROWS == 128) ? A.tile_blocks_max128 : A.tile_blocks_max64;
+    const int ta = (C::ROWS == 128) ? A.tile_adj_max128 : A.tile_adj_max64;
+    int acc_blocks = tb < C::ROWS * C::MAX_BLOCKS_PER_ROW ? tb : C::ROWS * C::MAX_BLOCKS_PER_ROW;
+    int step_cap = ta < C::ROWS * C::MAX_ADJ_PER_ROW ? ta : C::ROWS * C::MAX_ADJ_PER_ROW;
+    acc_blocks = (acc_blocks + 3) & ~3;
+    step_cap = (step_cap + 3) & ~3;
+    const size_t smem = C::smem_bytes(acc_blocks, step_cap);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess)
+      return e;
+    const long long grid = (A.nb_node + C::ROWS - 1) / C::ROWS;
+    if (grid > 0)
+      kern<<<(unsigned)grid, C::ROWS, smem, stream>>>(A, op, acc_blocks, step_cap);
+    return cudaGetLastError();
+  }
+  if (variant == VARIANT_NODE_GATHER_SLOTS && A.slots_ok) {
     using C = SlotsCfg<Op>;
     auto kern = k_node_gather_slots<Op, PER_BLOCK>;
     // shared-memory tile sized to what this mesh needs (largest tile of the plan), capped: oversized tiles take the
@@ -541,7 +870,7 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
       kern<<<(unsigned)grid, C::ROWS, smem, stream>>>(A, op, acc_blocks, adj_cap);
     return cudaGetLastError();
   }
-  if (variant == VARIANT_NODE_GATHER) {
+  if (variant == VARIANT_NODE_GATHER || variant == VARIANT_NODE_GATHER_SLOTS) {
     using C = GatherCfg<Op>;
     auto kern = k_node_gather<Op, PER_BLOCK>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);

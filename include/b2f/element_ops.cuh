@@ -24,6 +24,9 @@
 //   struct Geom;                                         // per-cell prepared geometry, registers only
 //   __device__ Geom prepare(const double (&X)[NV][3], long long cell) const;
 //   __device__ void block(const Geom&, int a, int b, double (&out)[BS*BS]) const;  // a, b compile-time after unrolling
+//   tets:      __device__ Geom finish(const TetGeom&, long long cell, bool odd) const;   // geometry already built (fan kernel)
+//   triangles: __device__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool odd) const;
+//              odd = the vertices are listed in an odd permutation of the cell's own order
 // Operators are invariant under even permutations of the cell's vertices, which the node-gather kernel
 // uses to bring the row node to local index 0.
 #pragma once
@@ -88,6 +91,7 @@ struct LaplaceTet
   static constexpr bool NEEDS_CELL = false;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, long long, bool) const { return T; }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
   {
     out[0] = (G.g[a][0] * G.g[b][0] + G.g[a][1] * G.g[b][1] + G.g[a][2] * G.g[b][2]) * G.s;
@@ -110,6 +114,7 @@ struct LaplaceTri
     G.s = 1.0 / (2.0 * fabs(G.t.a2));
     return G;
   }
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool) const { return prepare(X, cell); }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
   {
     out[0] = (G.t.n[a][0] * G.t.n[b][0] + G.t.n[a][1] * G.t.n[b][1]) * G.s;
@@ -137,6 +142,7 @@ struct ElasticityTri
     G.s = 1.0 / (2.0 * fabs(G.t.a2));
     return G;
   }
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool) const { return prepare(X, cell); }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[4]) const
   {
     const double pxa = G.t.n[a][0], pya = G.t.n[a][1], pxb = G.t.n[b][0], pyb = G.t.n[b][1];
@@ -157,6 +163,7 @@ struct ElasticityTet
   double lambda, mu2;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, long long, bool) const { return T; }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[9]) const
   {
     const double mu = 0.5 * mu2;
@@ -187,11 +194,13 @@ struct HeatTri
     double ks; // lambda * 0.25 / area
     double m; // area / 12 / dt
   };
-  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const
+  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const { return prepare_oriented(X, cell, false); }
+  // odd: X lists the cell's vertices in an odd permutation of the cell's own order (the signed area flips back)
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool odd) const
   {
     Geom G;
     G.t = tri_geometry(X);
-    const double area = 0.5 * G.t.a2;
+    const double area = odd ? -0.5 * G.t.a2 : 0.5 * G.t.a2;
     const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
     G.ks = lam * 0.25 / area;
     G.m = area * (1.0 / 12.0) * inv_dt;
@@ -216,10 +225,11 @@ struct HeatTet
     TetGeom t;
     double ks, m;
   };
-  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const
+  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const { return finish(tet_geometry(X), cell, false); }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, long long cell, bool) const
   {
     Geom G;
-    G.t = tet_geometry(X);
+    G.t = T;
     const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
     G.ks = lam * G.t.s;
     G.m = G.t.vol6 * (1.0 / 120.0) * inv_dt;

@@ -34,7 +34,7 @@ def _np(t):
     return t.detach().cpu().numpy()
 
 
-VARIANTS = [1, 2, 3]  # cell atomic, cell atomic warp-aggregated, node gather
+VARIANTS = [1, 2, 3, 4]  # cell atomic, cell atomic warp-aggregated, node gather (fan walk), node gather (slot words)
 
 
 @pytest.mark.parametrize("mesh_name", sorted(MESHES))
@@ -61,6 +61,9 @@ CASES = [
     ("square3", 2, "elasticity"), ("square9_shuffled", 2, "elasticity"), ("square20", 2, "elasticity"),
     ("cube2", 3, "elasticity"), ("cube7_shuffled", 3, "elasticity"), ("cube12", 3, "elasticity"),
     ("square9_shuffled", 1, "heat"), ("square20", 1, "heat_cell"), ("cube5", 1, "heat"), ("cube7_shuffled", 1, "heat_cell"),
+    # negatively oriented cells (the reference takes |det| for tets and the signed area for the heat triangle)
+    ("cube4_mixed_orientation", 1, "laplace"), ("cube4_mixed_orientation", 3, "elasticity"), ("cube4_mixed_orientation", 1, "heat_cell"),
+    ("square7_mixed_orientation", 1, "laplace"), ("square7_mixed_orientation", 2, "elasticity"), ("square7_mixed_orientation", 1, "heat_cell"),
 ]
 
 
@@ -334,7 +337,12 @@ def test_medium_cube_parity(variant):
     bsr.assembleBilinear(fem.Operator.laplace())
     torch.cuda.synchronize()
     assert_values_close(_np(bsr.matrix().values()), ref, ri, 1)
-    assert bsr.stats()["gather_fallback_tiles"] == 0
+    st = bsr.stats()
+    assert st["gather_fallback_tiles"] == 0
+    if variant == 3:
+        # fan plan: one chain start per row on this mesh (every node link is a disc or a sphere), so
+        # steps = node/cell pairs + rows
+        assert st["fan_steps"] == 4 * nc + nn
 
 
 @pytest.mark.parametrize("K", [500, 3000, 5000])
@@ -361,3 +369,54 @@ def test_long_rows_take_the_global_fallback_path(K):
         assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant}")
         if variant == 3 and K >= 3000:
             assert bsr.stats()["gather_fallback_tiles"] >= 1
+
+
+def emulate_fan_plan(cells, ri, co, plan):
+    """Replay the fan-walk plan on the host: returns, per row, the list of (cell, (row, N, O, C) node ids, odd) it emits."""
+    nv = cells.shape[1]
+    fan_ptr = plan["fan_ptr"]
+    steps = plan["fan_steps"].view(np.uint32)
+    fcell = plan["fan_cell"].view(np.uint32)
+    out = []
+    for row in range(ri.shape[0] - 1):
+        cols = co[ri[row]:ri[row + 1]]
+        n = o = None
+        emitted = []
+        for q in range(fan_ptr[row], fan_ptr[row + 1]):
+            w = int(steps[q])
+            if w & 0x80000000:
+                n = int(cols[w & 1023])
+                o = int(cols[(w >> 10) & 1023]) if nv == 4 else None
+                continue
+            c = int(cols[w & 1023])
+            assert n is not None
+            verts = (row, n, o, c) if nv == 4 else (row, n, c)
+            emitted.append((int(fcell[q]), verts, (w >> 11) & 1))
+            if nv == 4:
+                if not (w >> 10) & 1:  # O leaves: the old N becomes O
+                    o = n
+            n = c
+        out.append(emitted)
+    return out
+
+
+@pytest.mark.parametrize("mesh_name", sorted(MESHES))
+def test_fan_plan_visits_every_incident_cell_once(mesh_name):
+    """The plan is a cover of every node's incident cells by face-adjacent walks; the orientation bit is the parity of
+    the emitted vertex order relative to the cell's own."""
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3)
+    plan = {k: _np(v) for k, v in bsr.plan().items()}
+    mat = bsr.matrix()
+    ri, co = _np(mat.rowIndexWithEnd()), _np(mat.columns())
+    rows = emulate_fan_plan(cells, ri, co, plan)
+    incident = [[] for _ in range(coords.shape[0])]
+    for c, vs in enumerate(cells):
+        for v in vs:
+            incident[int(v)].append(c)
+    for row, emitted in enumerate(rows):
+        assert sorted(e[0] for e in emitted) == sorted(incident[row]), f"row {row}"
+        for cell, verts, odd in emitted:
+            assert sorted(verts) == sorted(int(v) for v in cells[cell]), f"row {row} cell {cell}: {verts} vs {cells[cell]}"
+            perm = [list(cells[cell]).index(v) for v in verts]
+            inv = sum(1 for i in range(len(perm)) for j in range(i + 1, len(perm)) if perm[i] > perm[j])
+            assert (inv & 1) == odd, f"row {row} cell {cell}"

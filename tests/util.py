@@ -41,7 +41,22 @@ def assert_vec_close(got, ref, rtol=RTOL, what="vector"):
     assert (d <= tol).all(), f"{what}: max |d| {d.max():.3e} (scale {scale:.3e})"
 
 
+def _mixed_orientation(dim, cells, coords, seed=11):
+    """Swap two vertices of about half of the cells: negatively oriented cells, as a reader may deliver them."""
+    rng = np.random.default_rng(seed)
+    flip = rng.uniform(size=cells.shape[0]) < 0.5
+    cells = cells.copy()
+    a, b = (1, 2) if dim == 2 else (2, 3)
+    cells[flip, a], cells[flip, b] = cells[flip, b].copy(), cells[flip, a].copy()
+    # and rotate some others (even permutation) so that the row node sits at every local position
+    rot = rng.uniform(size=cells.shape[0]) < 0.5
+    cells[rot] = np.roll(cells[rot], 1, axis=1) if dim == 2 else cells[rot][:, [1, 0, 3, 2]]
+    return dim, np.ascontiguousarray(cells), coords
+
+
 MESHES = {
+    "cube4_mixed_orientation": lambda: _mixed_orientation(3, *gen.cube_kuhn(4, shuffle_cells=3)),
+    "square7_mixed_orientation": lambda: _mixed_orientation(2, *gen.square(7, shuffle_cells=3)),
     "cube1": lambda: (3,) + gen.cube_kuhn(1, perturb=0.0),
     "cube2": lambda: (3,) + gen.cube_kuhn(2),
     "cube5": lambda: (3,) + gen.cube_kuhn(5),
