@@ -6,7 +6,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def lib_path():
-    return os.path.join(_HERE, "lib", "libb200fem.so")
+    """In-tree library; B2F_LIBRARY selects another build of the same library (kernel tuning experiments)."""
+    return os.environ.get("B2F_LIBRARY") or os.path.join(_HERE, "lib", "libb200fem.so")
 
 
 class B2FError(RuntimeError):

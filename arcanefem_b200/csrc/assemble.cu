@@ -28,10 +28,8 @@ namespace {
     A.fan_steps = h->fan_steps.as<uint32_t>();
     A.fan_cell = h->fan_cell.as<uint32_t>();
     A.fan_ok = h->fan_ok ? 1 : 0;
-    A.tile_blocks_max128 = h->tile_extents[0];
-    A.tile_adj_max128 = h->tile_extents[1];
-    A.tile_blocks_max64 = h->tile_extents[2];
-    A.tile_adj_max64 = h->tile_extents[3];
+    for (int i = 0; i < 6; ++i)
+      A.tile_extents[i] = h->tile_extents[i];
     A.counters = h->counters.as<unsigned long long>();
     A.accumulate = accumulate;
     int variant = h->variant;

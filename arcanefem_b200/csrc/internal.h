@@ -82,10 +82,10 @@ struct b2f_context_s
   b2f::DevBuf fan_ptr, fan_steps, fan_cell; // fan-walk plan of the default gather kernel (one word per step, cell id per step)
   bool fan_ok = false;
   int64_t nb_fan_step = 0;
-  int tile_extents[4] = { 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then for 64-row tiles
+  int tile_extents[6] = { 0, 0, 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then 64-row, then 32-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
-  b2f::DevBuf counters; // 8 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..5] tile extents)
+  b2f::DevBuf counters; // 8 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..6] tile extents)
   b2f::DevBuf ws_keys_a, ws_keys_b, ws_tmp, ws_i32a, ws_i64; // workspace
   b2f::DevBuf coords_stage; // b2f_assemble_host
   b2f::GhostPlan ghost;

@@ -481,20 +481,21 @@ namespace {
       fan_count[row] = nout;
   }
 
-  // Largest gather tile of the plan, for tiles of 128 and of 64 consecutive rows: out = {blocks128, adj128, blocks64, adj64}.
+  // Largest gather tile of the plan for tiles of 128, 64 and 32 consecutive rows: out = {blocks128, adj128, blocks64, adj64, blocks32, adj32}.
   __global__ void k_tile_extents(const int32_t* __restrict__ row_index, const int32_t* __restrict__ nc_ptr, long long nb_node, int* __restrict__ out)
   {
-    const long long tile = (long long)blockIdx.x * blockDim.x + threadIdx.x; // tiles of 64 rows
-    const long long r0 = tile * 64;
+    const long long tile = (long long)blockIdx.x * blockDim.x + threadIdx.x; // tiles of 32 rows
+    const long long r0 = tile * 32;
     if (r0 >= nb_node)
       return;
-    const long long r1 = r0 + 64 < nb_node ? r0 + 64 : nb_node;
-    atomicMax(out + 2, row_index[r1] - row_index[r0]);
-    atomicMax(out + 3, nc_ptr[r1] - nc_ptr[r0]);
-    if ((tile & 1) == 0) {
-      const long long r2 = r0 + 128 < nb_node ? r0 + 128 : nb_node;
-      atomicMax(out + 0, row_index[r2] - row_index[r0]);
-      atomicMax(out + 1, nc_ptr[r2] - nc_ptr[r0]);
+#pragma unroll
+    for (int lvl = 0; lvl < 3; ++lvl) { // 32, 64, 128 rows
+      const int rows = 32 << lvl;
+      if ((tile & ((1 << lvl) - 1)) != 0)
+        continue;
+      const long long r1 = r0 + rows < nb_node ? r0 + rows : nb_node;
+      atomicMax(out + 2 * (2 - lvl), row_index[r1] - row_index[r0]);
+      atomicMax(out + 2 * (2 - lvl) + 1, nc_ptr[r1] - nc_ptr[r0]);
     }
   }
 
@@ -692,12 +693,12 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   }
   {
     int* ext = reinterpret_cast<int*>(counters + 4);
-    B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 4, stream));
-    k_tile_extents<<<grid_for((nn + 63) / 64, 128), 128, 0, stream>>>(h->row_index.as<int32_t>(), tile_ptr, nn, ext);
+    B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 6, stream));
+    k_tile_extents<<<grid_for((nn + 31) / 32, 128), 128, 0, stream>>>(h->row_index.as<int32_t>(), tile_ptr, nn, ext);
     B2F_CUDA(cudaGetLastError());
     unsigned long long long_rows = 0;
     B2F_CUDA(cudaMemcpyAsync(&long_rows, counters + 3, sizeof(long_rows), cudaMemcpyDeviceToHost, stream));
-    B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 4, cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 6, cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaStreamSynchronize(stream));
     h->slots_ok = (h->variant == B2F_ASM_NODE_GATHER_SLOTS) && (long_rows == 0);
     h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0);

@@ -10,7 +10,6 @@ File layout followed: $MeshFormat / $PhysicalNames / $Entities / $Nodes / $Eleme
 specification (size_t = 8 bytes, int = 4 bytes, double = 8 bytes, native little endian when the header's "one" reads 1).
 """
 import io
-import struct
 from dataclasses import dataclass, field
 from typing import Dict, List, Tuple
 
@@ -84,11 +83,12 @@ class _Reader:
             raise ValueError(f"MSH: expected {text!r}, found {got!r}")
 
     def raw(self, fmt, count=1):
-        size = struct.calcsize(fmt) * count
+        dt = np.dtype(fmt)
+        size = dt.itemsize * count
         buf = self.b.read(size)
         if len(buf) != size:
             raise ValueError("MSH: truncated binary section")
-        return np.frombuffer(buf, dtype=np.dtype(fmt), count=count)
+        return np.frombuffer(buf, dtype=dt, count=count)
 
     def skip_section(self, name):
         end = f"$End{name}".encode()

@@ -41,7 +41,7 @@ struct AssembleArgs
   const uint32_t* fan_steps; // one word per step (see k_node_fan)
   const uint32_t* fan_cell; // cell id of every step (read by operators with per-cell data only)
   int fan_ok; // the fan plan is usable
-  int tile_blocks_max128, tile_adj_max128, tile_blocks_max64, tile_adj_max64; // largest tile of the plan (128 / 64 rows per tile)
+  int tile_extents[6]; // largest tile of the plan: {blocks, steps or pairs} for 128-, 64- and 32-row tiles
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
 };
@@ -363,6 +363,17 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_glob
                "l"(__cvta_generic_to_global(src_global)), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+#ifndef B2F_FAN_PREFETCH
+#define B2F_FAN_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p)
+{
+#if B2F_FAN_PREFETCH == 2
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#elif B2F_FAN_PREFETCH == 1
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity)
 {
   uint32_t done;
@@ -572,11 +583,11 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 }
 
 // One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
-// receive the vertex that enters; the caller alternates two register sets between the roles N and C, so the "C becomes
+// receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = +-(eN x eO); flip tells the sign (m = -(eN x eO) when set).
 template <class Op, bool PER_BLOCK>
 __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], double* __restrict__ acc, const int32_t* __restrict__ cols,
-                                         int k, uint32_t wc, const double (&Xc)[3], long long cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
+                                         int k, uint32_t wc, long long cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], bool& flip, double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
 {
@@ -597,19 +608,12 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       double XB[3];
       load_xyz(coords, cols[sO], XB);
 #pragma unroll
-      for (int d = 0; d < 3; ++d) {
-        eC[d] = Xc[d] - X0[d];
+      for (int d = 0; d < 3; ++d)
         eO[d] = XB[d] - X0[d];
-      }
       m[0] = eC[1] * eO[2] - eC[2] * eO[1];
       m[1] = eC[2] * eO[0] - eC[0] * eO[2];
       m[2] = eC[0] * eO[1] - eC[1] * eO[0];
       flip = false;
-    }
-    else {
-#pragma unroll
-      for (int d = 0; d < 3; ++d)
-        eC[d] = Xc[d]; // triangles keep the vertex itself
     }
     return;
   }
@@ -618,9 +622,6 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
   double out[BS2];
   if constexpr (NV == 4) {
     const bool dropN = (wc >> 10) & 1u;
-#pragma unroll
-    for (int d = 0; d < 3; ++d)
-      eC[d] = Xc[d] - X0[d];
     // local vertices (0, 1, 2, 3) = (row node, N, O, C): g1 = eO x eC, g2 = eC x eN, g3 = eN x eO
     TetGeom T;
     T.g[1][0] = eO[1] * eC[2] - eO[2] * eC[1];
@@ -638,7 +639,7 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     }
     const double det = eC[0] * T.g[NV - 1][0] + eC[1] * T.g[NV - 1][1] + eC[2] * T.g[NV - 1][2];
     T.vol6 = fabs(det);
-    T.s = 1.0 / (6.0 * T.vol6);
+    T.s = fast_rcp(6.0 * T.vol6);
     const auto G = tet_finish(op, T, cell, odd);
     op.block(G, 0, 1, out);
 #pragma unroll
@@ -677,7 +678,7 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     flip = dropN;
   }
   else {
-    const auto G = tri_prepare(op, X0, eN, Xc, cell, odd);
+    const auto G = tri_prepare(op, X0, eN, eC, cell, odd);
     op.block(G, 0, 1, out);
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
@@ -691,16 +692,28 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     for (int e = 0; e < BS2; ++e)
       diag[e] += out[e];
     store_block<BS, PER_BLOCK>(acc, k, sN, accN);
-#pragma unroll
-    for (int d = 0; d < 3; ++d)
-      eC[d] = Xc[d];
   }
 }
 
-template <class Op, bool PER_BLOCK>
-__global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
+#ifndef B2F_FAN_ROWS
+#define B2F_FAN_ROWS 128
+#endif
+template <class Op>
+struct FanCfg : SlotsCfg<Op>
 {
-  using C = SlotsCfg<Op>;
+  static constexpr int ROWS = (Op::BS == 1) ? B2F_FAN_ROWS : 64; // block rows (= threads) per CTA
+  static_assert(ROWS == 128 || ROWS == 64 || ROWS == 32, "tile extents exist for 128, 64 and 32 rows");
+};
+#ifndef B2F_FAN_MINBLOCKS
+#define B2F_FAN_MINBLOCKS 1
+#endif
+#ifndef B2F_FAN_CARVEOUT
+#define B2F_FAN_CARVEOUT -1
+#endif
+template <class Op, bool PER_BLOCK>
+__global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBLOCKS : 1)) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
+{
+  using C = FanCfg<Op>;
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
@@ -764,35 +777,48 @@ __global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_fan(AssembleArgs A,
     const int32_t* cols = cols_s + (rb - vbeg_al);
     const uint32_t* st = steps_s + (qb - abeg_al);
     const uint32_t* cl = A.fan_cell + qb;
+    // bring the coordinates of every neighbour of the row towards the SM now, in one round trip, instead of meeting
+    // the misses one by one along the walk
+    for (int x = 1; x < k; ++x)
+      prefetch_l2(A.coords + 3ll * cols[x]);
     double diag[BS2];
     load_block<BS, PER_BLOCK>(acc, k, 0, diag);
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
     bool flip = false;
-    double XP[3], XQ[3]; // coordinates of the entering vertex, prefetched one step ahead
-    uint32_t wP = st[0], wQ = 0;
-    load_xyz(A.coords, cols[wP & 1023u], XP);
+    double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
+    uint32_t w = st[0];
+    load_xyz(A.coords, cols[w & 1023u], Xn);
     int p = 0;
     bool newest_is_Q = false;
+    // The prefetched coordinates are consumed (edge vector) BEFORE the next prefetch is issued into the same registers:
+    // the consumer then never waits on a scoreboard that the new loads have just re-armed.
+    auto enter = [&](double(&e)[3]) {
+#pragma unroll
+      for (int d = 0; d < 3; ++d)
+        e[d] = (NV == 4) ? Xn[d] - X0[d] : Xn[d];
+    };
     while (true) {
       // step p: P enters (Q is the newest)
+      uint32_t wc = w;
+      enter(eP);
       if (p + 1 < nstep) {
-        wQ = st[p + 1];
-        load_xyz(A.coords, cols[wQ & 1023u], XQ);
+        w = st[p + 1];
+        load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wP, XP, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, flip, eP, accP, sP,
-                              diag);
+      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, flip, eP, accP, sP, diag);
       newest_is_Q = false;
       if (++p >= nstep)
         break;
       // step p: Q enters (P is the newest)
+      wc = w;
+      enter(eQ);
       if (p + 1 < nstep) {
-        wP = st[p + 1];
-        load_xyz(A.coords, cols[wP & 1023u], XP);
+        w = st[p + 1];
+        load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wQ, XQ, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, flip, eQ, accQ, sQ,
-                              diag);
+      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, flip, eQ, accQ, sQ, diag);
       newest_is_Q = true;
       if (++p >= nstep)
         break;
@@ -833,10 +859,15 @@ template <class Op, bool PER_BLOCK>
 inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
 {
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
-    using C = SlotsCfg<Op>;
+    using C = FanCfg<Op>;
     auto kern = k_node_fan<Op, PER_BLOCK>;
-    const int tb = (C::ROWS == 128) ? A.tile_blocks_max128 : A.tile_blocks_max64;
-    const int ta = (C::ROWS == 128) ? A.tile_adj_max128 : A.tile_adj_max64;
+    if (B2F_FAN_CARVEOUT >= 0) {
+      cudaError_t ec = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, B2F_FAN_CARVEOUT);
+      if (ec != cudaSuccess)
+        return ec;
+    }
+    constexpr int lvl = (C::ROWS == 128) ? 0 : (C::ROWS == 64 ? 1 : 2);
+    const int tb = A.tile_extents[2 * lvl], ta = A.tile_extents[2 * lvl + 1];
     int acc_blocks = tb < C::ROWS * C::MAX_BLOCKS_PER_ROW ? tb : C::ROWS * C::MAX_BLOCKS_PER_ROW;
     int step_cap = ta < C::ROWS * C::MAX_ADJ_PER_ROW ? ta : C::ROWS * C::MAX_ADJ_PER_ROW;
     acc_blocks = (acc_blocks + 3) & ~3;
@@ -855,8 +886,8 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     auto kern = k_node_gather_slots<Op, PER_BLOCK>;
     // shared-memory tile sized to what this mesh needs (largest tile of the plan), capped: oversized tiles take the
     // global path, so a few very long rows cannot lower the occupancy of every other tile
-    const int tb = (C::ROWS == 128) ? A.tile_blocks_max128 : A.tile_blocks_max64;
-    const int ta = (C::ROWS == 128) ? A.tile_adj_max128 : A.tile_adj_max64;
+    constexpr int lvl = (C::ROWS == 128) ? 0 : (C::ROWS == 64 ? 1 : 2);
+    const int tb = A.tile_extents[2 * lvl], ta = A.tile_extents[2 * lvl + 1];
     int acc_blocks = tb < C::ROWS * C::MAX_BLOCKS_PER_ROW ? tb : C::ROWS * C::MAX_BLOCKS_PER_ROW;
     int adj_cap = ta < C::ROWS * C::MAX_ADJ_PER_ROW ? ta : C::ROWS * C::MAX_ADJ_PER_ROW;
     acc_blocks = (acc_blocks + 3) & ~3;

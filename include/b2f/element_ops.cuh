@@ -34,6 +34,18 @@
 
 namespace b2f {
 
+// 1/x to full double precision for normal x > 0: hardware seed (MUFU.RCP64H) + two Newton steps, without the range
+// checks and slow path of the compiler's division (cells with a measure outside the normal range are degenerate anyway).
+__device__ __forceinline__ double fast_rcp(double x)
+{
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+}
+
 struct TetGeom
 {
   double g[4][3]; // un-normalised gradients (cofactors)
@@ -61,7 +73,7 @@ __device__ __forceinline__ TetGeom tet_geometry(const double (&X)[4][3])
   G.g[0][2] = -(G.g[1][2] + G.g[2][2] + G.g[3][2]);
   const double det = e1x * G.g[1][0] + e1y * G.g[1][1] + e1z * G.g[1][2];
   G.vol6 = fabs(det);
-  G.s = 1.0 / (6.0 * G.vol6);
+  G.s = fast_rcp(6.0 * G.vol6);
   return G;
 }
 
