@@ -1,0 +1,94 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz from the reference's own case data (run in the build container, where
+/root/reference exists; the GPU box and the test-suite only read the committed .npz files).
+
+Each fixture = one reference test case (an .arc case file + its mesh + its result file):
+  mesh       meshes/msh/<name>.msh read by arcanefem_b200.msh (MSH 4.1 binary)
+  parameters copied by hand from the cited .arc file
+  expected   the reference's result file (`uid value` per line, femutils/FemUtils.cc:100-170), which the reference's own
+             ctest compares the solved field against with a relative epsilon (1e-4 poisson/testlab)
+No reference source code is copied: only test DATA (mesh connectivity/coordinates and expected nodal values).
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from arcanefem_b200.msh import read_msh  # noqa: E402
+
+REF = "/root/reference"
+
+# name -> (mesh, result file, parameters); citations = the .arc the parameters come from
+CASES = {
+    # modules/poisson/inputs/circle.2D.bsr.hypre.arc
+    "poisson_circle_2D": dict(mesh="circle_cut", result="modules/poisson/check/poisson_test_ref_circle_2D.txt", f=5.5,
+                              dirichlet=[("horizontal", 0.5)], penalty=1.0e30, eps=1.0e-4),
+    # modules/poisson/inputs/circle.neumann.2D.bsr.hypre.arc
+    "poisson_circle_neumann_2D": dict(mesh="circle_cut", result="modules/poisson/check/poisson_test_ref_circle_neumann_2D.txt", f=5.5,
+                                      dirichlet=[("horizontal", 0.5)], neumann=[("curved", (-0.35, 1.65, 0.0))], penalty=1.0e30, eps=1.0e-4),
+    # modules/poisson/inputs/perforatedSquare.pointDirichlet.2D.bsr.hypre.arc
+    "poisson_point_dirichlet_2D": dict(mesh="plancher", result="modules/poisson/check/poisson_test_point_dirichlet_2D.txt", f=0.0,
+                                       dirichlet=[("topLeftCorner", 50.0), ("topRightCorner", 20.0), ("botLeftCorner", 20.0), ("botRightCorner", 50.0)],
+                                       penalty=1.0e30, eps=1.0e-4),
+    # modules/testlab/inputs/Test.sphere.3D.bsr.hypre.arc
+    "testlab_sphere_3D": dict(mesh="sphere_cut", result="modules/testlab/tests/poisson_test_ref_sphere_3D.txt", f=5.5,
+                              dirichlet=[("horizontal", 0.5)], penalty=1.0e31, eps=1.0e-4),
+    # modules/poisson/inputs/sphere.neumann.3D.bsr.hypre.arc
+    "poisson_sphere_neumann_3D": dict(mesh="sphere_cut", result="modules/poisson/check/poisson_test_ref_sphere_neumann_3D.txt", f=5.5,
+                                      dirichlet=[("horizontal", 0.5)], neumann=[("curved", (0.35, 1.65, 3.75))], penalty=1.0e30, eps=1.0e-4),
+    # modules/testlab/inputs/Test.L-shape.2D.bsr.hypre.arc
+    "testlab_Lshape_2D": dict(mesh="L-shape", result="modules/testlab/tests/poisson_test_ref_L-shape_2D.txt", f=-5.5,
+                              dirichlet=[("boundary", 0.5)], penalty=1.0e30, eps=1.0e-4),
+    # modules/testlab/inputs/Test.L-shape.3D.arc
+    "testlab_Lshape_3D": dict(mesh="L-shape-3D", result="modules/testlab/tests/poisson_test_ref_L-shape_3D.txt", f=5.5,
+                              dirichlet=[("bot", 50.0), ("bc", 10.0)], penalty=1.0e30, eps=1.0e-4),
+}
+
+
+def orient_outward(faces, cells, coords):
+    """Order the nodes of every boundary face so that the reference's normal formula
+    (2D: (y1-y0, x0-x1); 3D: (p1-p0)x(p2-p0), femutils/ArcaneFemFunctionsGpu.h:137-197) points out of the adjacent cell —
+    the state Arcane reaches with isSubDomainBoundaryOutside() == true."""
+    faces = faces.copy()
+    key = {}
+    for c, vs in enumerate(cells):
+        for i in range(len(vs)):
+            sub = tuple(sorted(int(v) for j, v in enumerate(vs) if j != i))
+            key[sub] = (c, int(vs[i]))
+    for f in range(faces.shape[0]):
+        c, opp = key[tuple(sorted(int(v) for v in faces[f]))]
+        p = coords[faces[f]]
+        if faces.shape[1] == 2:
+            n = np.array([p[1, 1] - p[0, 1], p[0, 0] - p[1, 0], 0.0])
+        else:
+            n = np.cross(p[1] - p[0], p[2] - p[0])
+        if np.dot(n, coords[opp] - p[0]) > 0:  # points towards the cell: flip
+            faces[f, 0], faces[f, 1] = faces[f, 1], faces[f, 0]
+    return faces
+
+
+def main():
+    for name, case in CASES.items():
+        m = read_msh(os.path.join(REF, "meshes", "msh", case["mesh"] + ".msh"))
+        cells, coords = m.cells(), m.coords
+        exp = np.loadtxt(os.path.join(REF, case["result"]))
+        out = dict(dim=np.int32(m.dim), cells=cells, coords=coords, node_uid=m.node_tags, expected_uid=exp[:, 0].astype(np.int64), expected_value=exp[:, 1],
+                   f=np.float64(case["f"]), penalty=np.float64(case["penalty"]), eps=np.float64(case["eps"]))
+        for i, (group, value) in enumerate(case["dirichlet"]):
+            out[f"dirichlet{i}_nodes"] = m.group_nodes(group)
+            out[f"dirichlet{i}_value"] = np.float64(value)
+        out["nb_dirichlet"] = np.int32(len(case["dirichlet"]))
+        for i, (group, q) in enumerate(case.get("neumann", [])):
+            out[f"neumann{i}_faces"] = orient_outward(m.group_elements(group), cells, coords)
+            out[f"neumann{i}_flux"] = np.array(q, dtype=np.float64)
+        out["nb_neumann"] = np.int32(len(case.get("neumann", [])))
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, **out)
+        print(name, cells.shape, coords.shape, exp.shape, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,75 @@
+"""Pins the oracle on the reference's own golden data: every fixture under tests/golden/ is one reference ctest case
+(mesh + parameters of the cited .arc + the reference's expected nodal solution, see tests/golden/make_golden.py).
+
+The reference holds no matrix-level vectors for this path; its tests assemble, apply the boundary conditions, solve with
+Hypre/PETSc and compare the nodal field with a relative epsilon of 1e-4 (femutils/FemUtils.cc:84-170).  Here the oracle
+assembles matrix and RHS, a sparse direct solve (scipy) stands in for the third-party solver, and the same comparison
+rule is applied.  A wrong element matrix, pattern, source/Neumann term or Dirichlet rule fails these tests.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spl
+
+from oracle import oracle as orc
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+
+
+def load_case(path):
+    z = np.load(path)
+    case = {k: z[k] for k in z.files}
+    case["name"] = os.path.splitext(os.path.basename(path))[0]
+    return case
+
+
+def check_against_reference(case, u):
+    """femutils/FemUtils.cc:84-90,146-163: |ref - v| / (|ref| + |v|) compared with epsilon (Arcane isNearlyEqualWithEpsilon),
+    values below min_value on both sides are skipped."""
+    uid_to_lid = {int(t): i for i, t in enumerate(case["node_uid"])}
+    eps, min_value = float(case["eps"]), 1.0e-16
+    bad = []
+    for uid, ref in zip(case["expected_uid"], case["expected_value"]):
+        v = u[uid_to_lid[int(uid)]]
+        if abs(ref) < min_value and abs(v) < min_value:
+            continue
+        if abs(ref - v) / (abs(ref) + abs(v)) > eps:
+            bad.append((int(uid), float(ref), float(v)))
+    assert not bad, f"{case['name']}: {len(bad)} nodes differ from the reference result file, e.g. {bad[:3]}"
+
+
+def oracle_system(case):
+    """Matrix, RHS after the reference's call sequence (modules/poisson/FemModule.cc:100-191): bilinear operator, source,
+    Neumann, Dirichlet by penalty, then the solve() prelude (_applyForcedValuesToLhs)."""
+    cells, coords = case["cells"], case["coords"]
+    nn = coords.shape[0]
+    ri, co = orc.build_pattern(cells, nn)
+    vals, nf = orc.assemble(cells, coords, ri, co, per_block=False)
+    assert nf == 0
+    rows, nbcol, cols = orc.to_csr(1, ri, co)
+    rhs = np.zeros(nn)
+    orc.rhs_constant_source(cells, coords, 1, float(case["f"]), rhs)
+    for i in range(int(case["nb_neumann"])):
+        orc.rhs_neumann(case[f"neumann{i}_faces"], coords, 1, rhs, value_xyz=tuple(case[f"neumann{i}_flux"]))
+    finfo, fval = np.zeros(nn, np.uint8), np.zeros(nn)
+    einfo, ev = np.zeros(nn, np.uint8), np.zeros(nn)
+    for i in range(int(case["nb_dirichlet"])):
+        orc.dirichlet_flag_penalty(1, 0, float(case[f"dirichlet{i}_value"]), float(case["penalty"]), case[f"dirichlet{i}_nodes"], finfo, fval, rhs)
+    orc.dirichlet_apply(rows, cols, vals, einfo, ev, finfo, fval, rhs)
+    return ri, co, vals, rhs, (rows, cols)
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_oracle_reproduces_reference_solution(path):
+    case = load_case(path)
+    ri, co, vals, rhs, (rows, cols) = oracle_system(case)
+    A = sp.csr_matrix((vals, cols, rows))
+    u = spl.spsolve(A.tocsc(), rhs)
+    check_against_reference(case, u)
+
+
+def test_golden_fixtures_present():
+    assert len(GOLDEN) >= 7
