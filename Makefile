@@ -12,7 +12,7 @@ all: $(LIB) oracle
 
 $(LIB): $(OBJ)
 	@mkdir -p $(dir $@)
-	$(NVCC) $(ARCH) -shared -ccbin $(HOSTCXX) -o $@ $(OBJ) $(LDLIBS_NCCL)
+	$(NVCC) $(ARCH) -shared -ccbin $(HOSTCXX) -o $@ $(OBJ) -ldl
 
 build/%.o: arcanefem_b200/csrc/%.cu $(HDR)
 	@mkdir -p build

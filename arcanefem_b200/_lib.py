@@ -19,7 +19,7 @@ class B2FError(RuntimeError):
 
 class MeshView(C.Structure):
     _fields_ = [("dim", C.c_int32), ("nodes_per_cell", C.c_int32), ("nb_cell", C.c_int64), ("nb_node", C.c_int64),
-                ("cell_node", C.c_void_p), ("coords", C.c_void_p), ("node_is_own", C.c_void_p)]
+                ("cell_node", C.c_void_p), ("coords", C.c_void_p), ("node_is_own", C.c_void_p), ("cell_is_own", C.c_void_p)]
 
 
 class Options(C.Structure):
@@ -96,7 +96,7 @@ PROTOTYPES = {
     "b2f_dirichlet_apply": (C.c_int, [_H, _S]),
     "b2f_spmv": (C.c_int, [_H, C.c_void_p, C.c_void_p, _S]),
     "b2f_assemble_host": (C.c_int, [_H, _P(OperatorDesc), C.c_void_p, C.c_void_p, _S]),
-    "b2f_ghost_plan": (C.c_int, [_H, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2f_ghost_plan": (C.c_int, [_H, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, _S]),
     "b2f_ghost_exchange": (C.c_int, [_H, C.c_void_p, _S]),
     "b2f_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "b2f_nccl_comm_init": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _P(C.c_void_p)]),

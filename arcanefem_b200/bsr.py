@@ -61,6 +61,7 @@ class Mesh:
     cell_node: "object"  # torch.int32 cuda [nb_cell, dim+1]
     coords: "object"  # torch.float64 cuda [nb_node, 3]
     node_is_own: Optional["object"] = None  # torch.uint8 cuda [nb_node] or None
+    cell_is_own: Optional["object"] = None  # torch.uint8 cuda [nb_cell] or None (0 = ghost cell: pattern only)
 
     @property
     def nb_cell(self):
@@ -71,12 +72,13 @@ class Mesh:
         return int(self.coords.shape[0])
 
     @staticmethod
-    def from_numpy(dim, cell_node, coords, node_is_own=None, device="cuda"):
+    def from_numpy(dim, cell_node, coords, node_is_own=None, device="cuda", cell_is_own=None):
         torch = _torch()
         cn = torch.as_tensor(np.ascontiguousarray(cell_node, dtype=np.int32)).to(device)
         xy = torch.as_tensor(np.ascontiguousarray(coords, dtype=np.float64)).to(device)
         own = None if node_is_own is None else torch.as_tensor(np.ascontiguousarray(node_is_own, dtype=np.uint8)).to(device)
-        return Mesh(dim, cn, xy, own)
+        cown = None if cell_is_own is None else torch.as_tensor(np.ascontiguousarray(cell_is_own, dtype=np.uint8)).to(device)
+        return Mesh(dim, cn, xy, own, cown)
 
 
 class Operator:
@@ -294,6 +296,7 @@ class BSRFormat:
         mv.cell_node = C.c_void_p(mesh.cell_node.data_ptr())
         mv.coords = C.c_void_p(mesh.coords.data_ptr())
         mv.node_is_own = C.c_void_p(mesh.node_is_own.data_ptr()) if mesh.node_is_own is not None else None
+        mv.cell_is_own = C.c_void_p(mesh.cell_is_own.data_ptr()) if mesh.cell_is_own is not None else None
         opt = _lib.Options()
         opt.block_size = self._nb_dof
         opt.use_csr = 1 if does_linear_system_use_csr else 0

@@ -108,7 +108,7 @@ int b2f_destroy(b2f_handle h)
     return B2F_OK;
   DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
-                     &h->coords_stage, &h->ghost.send_rows, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_slot };
+                     &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals };
   for (DevBuf* b : bufs)
     b->release();
   delete h;
@@ -226,7 +226,7 @@ int b2f_get_plan(b2f_handle h, b2f_plan_view* out)
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_plan: null output");
   out->nb_node = h->mesh.nb_node;
-  out->nb_pair = h->mesh.nb_cell * h->nv;
+  out->nb_pair = h->nb_pair;
   out->nb_fan_step = h->fan_ok ? h->nb_fan_step : 0;
   out->nc_ptr = h->nc_ptr.as<int32_t>();
   out->nc_list = h->nc_list.as<uint32_t>();
@@ -431,12 +431,14 @@ int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords
   return B2F_OK;
 }
 
-int b2f_ghost_plan(b2f_handle h, int32_t rank, int32_t world, int64_t nb_ghost, const int32_t* ghost_node_host, const int32_t* ghost_owner_rank_host,
-                   const int64_t* node_global_id_host)
+int b2f_ghost_plan(b2f_handle h, void* nccl_comm, int32_t rank, int32_t world, const int32_t* node_owner_rank_host, const int64_t* node_global_id_host,
+                   b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
-  return ghost_plan(h, rank, world, nb_ghost, ghost_node_host, ghost_owner_rank_host, node_global_id_host);
+  if (h->mesh.node_is_own)
+    return fail(B2F_ERR_STATE, "b2f_ghost_plan: the exchange mode assembles every local row; mesh.node_is_own must be NULL");
+  return ghost_plan(h, nccl_comm, rank, world, node_owner_rank_host, node_global_id_host, (cudaStream_t)stream);
 }
 
 int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream)

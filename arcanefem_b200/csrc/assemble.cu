@@ -15,6 +15,7 @@ namespace {
     A.cell_node = h->mesh.cell_node;
     A.coords = h->mesh.coords;
     A.node_is_own = h->mesh.node_is_own;
+    A.cell_is_own = h->mesh.cell_is_own;
     A.nb_cell = h->mesh.nb_cell;
     A.nb_node = h->mesh.nb_node;
     A.row_index = h->row_index.as<int32_t>();

@@ -55,11 +55,11 @@ struct GhostPlan
 {
   bool ready = false;
   int rank = 0, world = 1;
-  // per peer: rows this rank sends (its ghost rows owned by peer) / receives (its own rows that are ghosts on peer)
-  std::vector<int64_t> send_blocks, recv_blocks; // number of blocks exchanged with each peer
-  std::vector<int64_t> send_off, recv_off; // offsets (in blocks) into the packed buffers
-  DevBuf send_rows, send_vals, recv_vals, recv_slot; // device: row ids to pack; packed values; target value slots
-  int64_t total_send = 0, total_recv = 0;
+  // per peer: rows / blocks this rank sends (its ghost rows owned by the peer) and receives (its own rows that are ghosts on the peer)
+  std::vector<int64_t> send_rows_n, recv_rows_n, send_blocks, recv_blocks;
+  std::vector<int64_t> send_off, recv_off; // offsets (in blocks) of every peer's part of the packed buffers
+  DevBuf send_index, recv_index, send_vals, recv_vals; // value index per exchanged scalar; packed values
+  int64_t total_send = 0, total_recv = 0; // scalars
 };
 
 } // namespace b2f
@@ -82,6 +82,7 @@ struct b2f_context_s
   b2f::DevBuf fan_ptr, fan_steps, fan_cell; // fan-walk plan of the default gather kernel (one word per step, cell id per step)
   bool fan_ok = false;
   int64_t nb_fan_step = 0;
+  int64_t nb_pair = 0; // node/cell incidences of the assembled cells
   int tile_extents[6] = { 0, 0, 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then 64-row, then 32-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
@@ -110,6 +111,6 @@ int dirichlet_apply(b2f_context_s* h, cudaStream_t s);
 int to_csr(b2f_context_s* h, cudaStream_t s);
 int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
 // ghost.cu
-int ghost_plan(b2f_context_s* h, int rank, int world, int64_t nb_ghost, const int32_t* ghost_node, const int32_t* ghost_owner, const int64_t* node_gid);
+int ghost_plan(b2f_context_s* h, void* comm, int rank, int world, const int32_t* node_owner, const int64_t* node_gid, cudaStream_t s);
 int ghost_exchange(b2f_context_s* h, void* comm, cudaStream_t s);
 } // namespace b2f

@@ -198,19 +198,21 @@ namespace {
       out[i] = row_index[i + 1] - row_index[i];
   }
 
-  __global__ void __launch_bounds__(256) k_count_node_cells(const int32_t* __restrict__ cell_node, long long n_entries, int32_t* __restrict__ cnt)
+  // node -> cell lists hold the cells that are assembled: ghost cells (cell_is_own == 0) only contribute to the pattern
+  __global__ void __launch_bounds__(256) k_count_node_cells(const int32_t* __restrict__ cell_node, const uint8_t* __restrict__ cell_is_own, int nv, long long n_entries,
+                                                            int32_t* __restrict__ cnt)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n_entries)
+    if (i < n_entries && (cell_is_own == nullptr || cell_is_own[i / nv] != 0))
       atomicAdd(cnt + cell_node[i], 1);
   }
 
   template <int NV>
-  __global__ void __launch_bounds__(256) k_fill_node_cells(const int32_t* __restrict__ cell_node, long long nb_cell, const int32_t* __restrict__ nc_ptr,
-                                                           int32_t* __restrict__ cursor, uint32_t* __restrict__ nc_list)
+  __global__ void __launch_bounds__(256) k_fill_node_cells(const int32_t* __restrict__ cell_node, const uint8_t* __restrict__ cell_is_own, long long nb_cell,
+                                                           const int32_t* __restrict__ nc_ptr, int32_t* __restrict__ cursor, uint32_t* __restrict__ nc_list)
   {
     const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (cell >= nb_cell)
+    if (cell >= nb_cell || (cell_is_own != nullptr && cell_is_own[cell] == 0))
       return;
 #pragma unroll
     for (int a = 0; a < NV; ++a) {
@@ -629,20 +631,21 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   int32_t* cnt = deg;
   B2F_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
   if (nc > 0)
-    k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, nc * nv, cnt);
+    k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nv, nc * nv, cnt);
   B2F_CUDA(cudaGetLastError());
   B2F_CUDA(h->nc_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
   long long nb_adj = 0;
   rc = scan_counts(h, cnt, nn, h->nc_ptr.as<int32_t>(), &nb_adj, stream);
   if (rc != B2F_OK)
     return rc;
+  h->nb_pair = nb_adj;
   B2F_CUDA(h->nc_list.alloc(sizeof(uint32_t) * (size_t)nb_adj));
   B2F_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
   if (nc > 0) {
     if (nv == 3)
-      k_fill_node_cells<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+      k_fill_node_cells<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
     else
-      k_fill_node_cells<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+      k_fill_node_cells<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
   }
   k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
   B2F_CUDA(cudaGetLastError());

@@ -1,0 +1,158 @@
+"""Multi-GPU host side: Arcane-style slab decomposition of the synthetic Kuhn cube and the NCCL ghost-row exchange.
+
+One process per GPU (torch.distributed supplies rank/world and carries the NCCL unique id to the other ranks; the exchange
+itself runs inside libb200fem.so on its own ncclComm_t, include/b2f.h b2f_ghost_plan / b2f_ghost_exchange).
+
+Decomposition (what Arcane hands to every rank, femutils/BSRFormat.h:807-815, femutils/FemDoFsOnNodes.cc:79-128): the local
+mesh holds the rank's own cells plus the layer of ghost cells touching its own nodes; a node is owned by the lowest rank
+whose own cells touch it.  For z-slabs of `n_hex` hex layers per rank this gives: own nodes = planes r*n+1 .. (r+1)*n
+(plus plane 0 on rank 0), ghost nodes = the bottom plane r*n (owner r-1) and the plane (r+1)*n+1 of the ghost-cell layer
+on top (owner r+1).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from . import mesh as gen
+from ._lib import check
+
+
+def plane_coords(n_hex, nz_total, k, L=1.0, perturb=0.25, seed=1234):
+    """Coordinates of the (n_hex+1)^2 nodes of global z-plane k (same values on every rank that holds the plane)."""
+    n1 = n_hex + 1
+    h = L / n_hex
+    ax = np.arange(n1, dtype=np.float64) * h
+    y, x = np.meshgrid(ax, ax, indexing="ij")
+    c = np.stack([x.ravel(), y.ravel(), np.full(n1 * n1, k * h)], axis=1)
+    if perturb and 0 < k < nz_total:
+        rng = np.random.default_rng(seed + 7919 * k)
+        jit = rng.uniform(-perturb * h, perturb * h, size=c.shape)
+        idx = np.arange(n1)
+        interior = ((idx[:, None] > 0) & (idx[:, None] < n_hex) & (idx[None, :] > 0) & (idx[None, :] < n_hex)).ravel()
+        c[interior] += jit[interior]
+    return c
+
+
+def global_mesh(n_hex, world, L=1.0, perturb=0.25, seed=1234):
+    """The undecomposed mesh (cells, coords) of the same cube, global lexicographic node ids (tests only: small sizes)."""
+    n1 = n_hex + 1
+    nz_total = n_hex * world
+    coords = np.concatenate([plane_coords(n_hex, nz_total, k, L, perturb, seed) for k in range(nz_total + 1)], axis=0)
+    hi = np.arange(n_hex, dtype=np.int64)
+    kk, jj, ii = np.meshgrid(np.arange(nz_total, dtype=np.int64), hi, hi, indexing="ij")
+    base = (ii + n1 * (jj + n1 * kk)).ravel()
+    corner = np.array([dx + n1 * (dy + n1 * dz) for dz in (0, 1) for dy in (0, 1) for dx in (0, 1)], dtype=np.int64)
+    cells = (base[:, None, None] + corner[gen.kuhn_table()][None, :, :]).reshape(-1, 4).astype(np.int32)
+    return np.ascontiguousarray(cells), np.ascontiguousarray(coords)
+
+
+def slab_partition(n_hex, rank, world, L=1.0, perturb=0.25, seed=1234):
+    """Local mesh of `rank` for the global cube of n_hex x n_hex x (n_hex*world) hexes split into z-slabs.
+
+    Returns dict(cells int32 [nc,4], coords [nn,3], cell_is_own uint8 [nc], node_owner int32 [nn], node_gid int64 [nn],
+    nb_own_cell, z0 = first local plane)."""
+    n1 = n_hex + 1
+    plane = n1 * n1
+    nz_total = n_hex * world
+    lay0, lay1 = rank * n_hex, (rank + 1) * n_hex  # own hex layers [lay0, lay1)
+    ghost_top = 1 if rank < world - 1 else 0
+    z0, z1 = lay0, lay1 + ghost_top  # local planes z0 .. z1 inclusive
+    coords = np.concatenate([plane_coords(n_hex, nz_total, k, L, perturb, seed) for k in range(z0, z1 + 1)], axis=0)
+    # cells of the local layers, local lexicographic node ids
+    hi = np.arange(n_hex, dtype=np.int64)
+    nlay = z1 - z0
+    kk, jj, ii = np.meshgrid(np.arange(nlay, dtype=np.int64), hi, hi, indexing="ij")
+    base = (ii + n1 * (jj + n1 * kk)).ravel()
+    corner = np.array([dx + n1 * (dy + n1 * dz) for dz in (0, 1) for dy in (0, 1) for dx in (0, 1)], dtype=np.int64)
+    off = corner[gen.kuhn_table()]
+    cells = (base[:, None, None] + off[None, :, :]).reshape(-1, 4).astype(np.int32)
+    cell_layer = np.repeat(kk.ravel(), 6) + z0
+    cell_is_own = (cell_layer < lay1).astype(np.uint8)
+    node_plane = np.repeat(np.arange(z0, z1 + 1, dtype=np.int64), plane)
+    # owner = lowest rank whose own cells touch the node: plane k belongs to the slab below when it is a slab boundary
+    node_owner = np.clip((node_plane - 1) // n_hex, 0, world - 1).astype(np.int32)
+    node_gid = (np.arange(coords.shape[0], dtype=np.int64) + z0 * plane)
+    return dict(cells=np.ascontiguousarray(cells), coords=np.ascontiguousarray(coords), cell_is_own=cell_is_own, node_owner=node_owner, node_gid=node_gid,
+                nb_own_cell=int(cell_is_own.sum()), z0=z0, plane=plane)
+
+
+def exchange_reference(part, ri, co, vals, rank, world, dist):
+    """Host mirror of b2f_ghost_exchange on numpy arrays (BS = 1), used by the CPU tests with the gloo backend: every ghost
+    row with a non-zero partial sum goes to its owner as (global row, global col, value) triplets; the owner adds them and
+    the ghost row is zeroed."""
+    import torch
+    gid, owner = part["node_gid"], part["node_owner"]
+    out = vals.copy()
+    send = {p: [] for p in range(world) if p != rank}
+    for r in np.nonzero(owner != rank)[0]:
+        seg = slice(ri[r], ri[r + 1])
+        trip = np.stack([np.full(ri[r + 1] - ri[r], gid[r], dtype=np.float64), gid[co[seg]].astype(np.float64), out[seg]], axis=1)
+        send[int(owner[r])].append(trip)
+        out[seg] = 0.0
+    lid_of = {int(g): i for i, g in enumerate(gid)}
+    for p in range(world):
+        if p == rank:
+            continue
+        mine = np.concatenate(send[p], axis=0) if send[p] else np.zeros((0, 3))
+        n_mine = torch.tensor([mine.shape[0]], dtype=torch.int64)
+        n_theirs = torch.zeros(1, dtype=torch.int64)
+        # lower rank sends first: deadlock-free pairwise exchange
+        if rank < p:
+            dist.send(n_mine, p)
+            dist.recv(n_theirs, p)
+        else:
+            dist.recv(n_theirs, p)
+            dist.send(n_mine, p)
+        theirs = torch.zeros((int(n_theirs.item()), 3), dtype=torch.float64)
+        tm = torch.as_tensor(mine.copy())
+        if rank < p:
+            if tm.numel():
+                dist.send(tm, p)
+            if theirs.numel():
+                dist.recv(theirs, p)
+        else:
+            if theirs.numel():
+                dist.recv(theirs, p)
+            if tm.numel():
+                dist.send(tm, p)
+        for g_row, g_col, v in theirs.numpy():
+            r, c = lid_of[int(g_row)], lid_of[int(g_col)]
+            assert owner[r] == rank, "ghost row sent to a rank that does not own it"
+            row = co[ri[r]:ri[r + 1]]
+            x = int(np.nonzero(row == c)[0][0])
+            out[ri[r] + x] += v
+    return out
+
+
+class GhostExchange:
+    """NCCL ghost-row exchange bound to one BSRFormat (one rank = one GPU)."""
+
+    def __init__(self, bsr, rank, world, node_owner, node_gid):
+        import torch
+        import torch.distributed as dist
+        self._lib = _lib.load_library()
+        self._bsr = bsr
+        self._comm = C.c_void_p()
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_ubyte * 128)()
+            check(self._lib.b2f_nccl_unique_id(buf))
+            ident = torch.tensor(list(buf), dtype=torch.uint8)
+        ident = ident.cuda()
+        dist.broadcast(ident, 0)
+        raw = bytes(ident.cpu().tolist())
+        check(self._lib.b2f_nccl_comm_init(C.c_char_p(raw), int(rank), int(world), C.byref(self._comm)))
+        owner = np.ascontiguousarray(node_owner, dtype=np.int32)
+        gid = np.ascontiguousarray(node_gid, dtype=np.int64)
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(self._lib.b2f_ghost_plan(bsr._h, self._comm, int(rank), int(world), owner.ctypes.data_as(C.c_void_p), gid.ctypes.data_as(C.c_void_p), stream))
+
+    def run(self):
+        import torch
+        check(self._lib.b2f_ghost_exchange(self._bsr._h, self._comm, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+    def close(self):
+        if self._comm:
+            self._lib.b2f_nccl_comm_destroy(self._comm)
+            self._comm = C.c_void_p()

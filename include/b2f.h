@@ -85,6 +85,7 @@ typedef struct b2f_mesh_view {
   const int32_t* cell_node; /* [nb_cell * nodes_per_cell] */
   const double* coords; /* [nb_node * 3], xyz interleaved */
   const uint8_t* node_is_own; /* [nb_node] or NULL = every node is own */
+  const uint8_t* cell_is_own; /* [nb_cell] or NULL = every cell is assembled; 0 = ghost cell: pattern only (multi-GPU exchange mode) */
 } b2f_mesh_view;
 
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
@@ -238,13 +239,16 @@ int b2f_spmv(b2f_handle h, const double* x, double* y, b2f_stream stream);
 int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords_host, double* values_host, b2f_stream stream);
 
 /*
- * Multi-GPU (one rank per GPU, disjoint cell partition): rows of ghost nodes (node_is_own == 0) hold
- * this rank's partial sums; b2f_ghost_exchange sends them to the owner rank over NCCL (ncclSend/ncclRecv
- * grouped per neighbour) and adds them into the owner's rows.  `comm` is an ncclComm_t.
- * Plan arrays are host pointers: for every ghost node its owner rank and its local id on the owner.
+ * Multi-GPU (one rank per GPU, Arcane-style decomposition: the local mesh holds the rank's own cells plus the ghost-cell
+ * layer, b2f_mesh_view::cell_is_own marks the former).  Only own cells are assembled, into all local rows; rows of
+ * ghost nodes then hold this rank's partial sums.  b2f_ghost_exchange sends them to the owner rank over NCCL
+ * (grouped ncclSend/ncclRecv per neighbour), adds them into the owner's rows and zeroes the ghost rows, so owner rows
+ * equal the reference's (which computes the ghost layer redundantly instead, femutils/BSRFormat.h:807-815).
+ * `comm` is an ncclComm_t.  Plan inputs are host arrays over the local nodes: owner rank and global id
+ * (Arcane: Node::owner(), uniqueId()).  mesh.node_is_own must be NULL in this mode.
  */
-int b2f_ghost_plan(b2f_handle h, int32_t rank, int32_t world, int64_t nb_ghost, const int32_t* ghost_node_host, const int32_t* ghost_owner_rank_host,
-                   const int64_t* node_global_id_host);
+int b2f_ghost_plan(b2f_handle h, void* nccl_comm, int32_t rank, int32_t world, const int32_t* node_owner_rank_host, const int64_t* node_global_id_host,
+                   b2f_stream stream);
 int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream);
 /* NCCL bootstrap helpers so a host without its own NCCL binding can create the communicator. */
 int b2f_nccl_unique_id(void* id128_out_host);

@@ -28,6 +28,7 @@ struct AssembleArgs
   const int32_t* cell_node;
   const double* coords;
   const uint8_t* node_is_own; // may be null
+  const uint8_t* cell_is_own; // may be null; 0 = ghost cell (pattern only, not assembled)
   long long nb_cell;
   long long nb_node;
   const int32_t* row_index; // nb_node + 1
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(256) k_cell_atomic(AssembleArgs A, Op op)
 {
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool valid = cell < A.nb_cell;
+  const bool valid = cell < A.nb_cell && (A.cell_is_own == nullptr || A.cell_is_own[cell] != 0);
   if (!WARPAGG && !valid)
     return;
   const unsigned lane = threadIdx.x & 31u;

@@ -1,0 +1,82 @@
+"""Two ranks on two GPUs: slab decomposition, device assembly of the own cells, NCCL ghost-row exchange inside
+libb200fem.so; owner rows must equal the undecomposed oracle assembly (skipped on a single-GPU box)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n_hex, variant, q):
+    try:
+        import torch.distributed as dist
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        import arcanefem_b200 as fem
+        from arcanefem_b200 import multigpu as mg
+        from arcanefem_b200.bsr import Mesh
+        from oracle import oracle as orc
+        part = mg.slab_partition(n_hex, rank, world)
+        cells, coords = part["cells"], part["coords"]
+        bsr = fem.BSRFormat(1)
+        bsr.initialize(Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"]), True, assembly_variant=variant)
+        bsr.computeSparsity()
+        ex = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"])
+        for _ in range(2):  # twice: the exchange must be repeatable (ghost rows re-assembled, then zeroed again)
+            bsr.assembleBilinear(fem.Operator.laplace())
+            ex.run()
+        torch.cuda.synchronize()
+        mat = bsr.matrix()
+        ri, co, vals = mat.rowIndexWithEnd().cpu().numpy(), mat.columns().cpu().numpy(), mat.values().cpu().numpy()
+        gcells, gcoords = mg.global_mesh(n_hex, world)
+        gri, gco = orc.build_pattern(gcells, gcoords.shape[0])
+        gvals, _ = orc.assemble(gcells, gcoords, gri, gco)
+        gid = part["node_gid"]
+        worst = 0.0
+        for r in range(coords.shape[0]):
+            seg = slice(ri[r], ri[r + 1])
+            if part["node_owner"][r] != rank:
+                assert not vals[seg].any(), "ghost rows must end up zero"
+                continue
+            gseg = slice(gri[gid[r]], gri[gid[r] + 1])
+            np.testing.assert_array_equal(gid[co[seg]], gco[gseg])
+            worst = max(worst, np.abs(vals[seg] - gvals[gseg]).max() / np.abs(gvals[gseg]).max())
+        assert worst <= 1e-12, worst
+        ex.close()
+        q.put((rank, "ok"))
+        dist.destroy_process_group()
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+
+
+@pytest.mark.parametrize("variant", [1, 3])
+def test_two_gpu_ghost_exchange_matches_global_assembly(variant):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, 6, variant, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in res:
+        assert msg == "ok", f"rank {rank}: {msg}"

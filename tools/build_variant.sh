@@ -15,5 +15,5 @@ for f in arcanefem_b200/csrc/*.cu; do
   fi
 done
 wait
-$NVCC $ARCH -shared -ccbin /usr/bin/g++ -o arcanefem_b200/lib/libb200fem_$NAME.so build/var_$NAME/*.o
+$NVCC $ARCH -shared -ccbin /usr/bin/g++ -o arcanefem_b200/lib/libb200fem_$NAME.so build/var_$NAME/*.o -ldl
 echo built arcanefem_b200/lib/libb200fem_$NAME.so
