@@ -25,6 +25,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# dram__bytes_read.sum + dram__bytes_write.sum of k_node_fan<LaplaceTet> at N=203, one ncu --set full capture (profiles/r01_fan_ncu.txt)
+NCU_TRAFFIC_BYTES = 2.591e9
+NCU_TRAFFIC_NOTE = "ncu --set full, k_node_fan<LaplaceTet,0>, N=203: dram read 1.614 GB + write 0.977 GB per launch (profiles/r01_fan_ncu.txt)"
 METRIC = "bsr_assembly_gnnz_per_s"
 UNIT = "GNNZ/s"
 
@@ -95,22 +98,6 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def slab_mesh(n_hex, rank, world, perturb=0.25):
-    """Rank's slab of the (n_hex x n_hex x n_hex*world) Kuhn cube: local cells/coords, own flags and ghost plan."""
-    from arcanefem_b200 import mesh as gen
-    cells, coords = gen.cube_kuhn(n_hex, perturb=perturb, seed=1234 + rank)
-    coords[:, 2] += rank * 1.0
-    n1 = n_hex + 1
-    plane = n1 * n1
-    own = np.ones(coords.shape[0], dtype=np.uint8)
-    if world > 1:
-        # the interface planes must coincide on both sides: remove the jitter there (they are boundary planes of the
-        # local cube already, so cube_kuhn left them unperturbed)
-        if rank > 0:
-            own[:plane] = 0  # bottom plane is owned by rank-1 (lowest rank touching a node owns it)
-    return cells, coords, own, plane
-
-
 def run_b200(args):
     import torch
     import arcanefem_b200 as fem
@@ -128,16 +115,23 @@ def run_b200(args):
 
     n = args.n
     t0 = time.time()
-    cells, coords, own, plane = slab_mesh(n, rank, world)
+    from arcanefem_b200 import multigpu as mg
+    part = mg.slab_partition(n, rank, world)  # world == 1: the plain cube, every cell and node own
+    cells, coords = part["cells"], part["coords"]
     gen_s = time.time() - t0
     nc, nn = cells.shape[0], coords.shape[0]
-    mesh = Mesh.from_numpy(3, cells, coords)
+    mesh = Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"] if world > 1 else None)
     bsr = fem.BSRFormat(1)
     bsr.initialize(mesh, True, assembly_variant=args.variant)
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     bsr.computeSparsity()
+    ev1.record()
+    torch.cuda.synchronize()
+    sparsity_cold_ms = ev0.elapsed_time(ev1)
+    ev0.record()
+    bsr.computeSparsity()  # second build: no module load / local-memory set-up inside the timed region
     ev1.record()
     torch.cuda.synchronize()
     sparsity_ms = ev0.elapsed_time(ev1)
@@ -148,8 +142,7 @@ def run_b200(args):
 
     exchange = None
     if world > 1:
-        from arcanefem_b200.multigpu import GhostExchange
-        exchange = GhostExchange(bsr, rank, world, plane, n)
+        exchange = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"])
 
     def step():
         bsr.assembleBilinear(op)
@@ -182,9 +175,8 @@ def run_b200(args):
     # nonzeros the whole job produced = rows owned by some rank (ghost copies are not counted twice)
     own_nnz = nnz
     if world > 1:
-        ri = mat.rowIndexWithEnd()
-        ghost_blocks = int(ri[plane].item()) if rank > 0 else 0
-        t = torch.tensor([nnz - ghost_blocks], device="cuda", dtype=torch.float64)
+        own_rows = torch.as_tensor(part["node_owner"] == rank).cuda()
+        t = mat.nbNzPerRow()[own_rows].sum().to(torch.float64).reshape(1)
         dist.all_reduce(t)
         own_nnz = int(t.item())
     value = own_nnz / (ms_step * 1e-3) / 1e9
@@ -193,13 +185,25 @@ def run_b200(args):
     coords_host = torch.as_tensor(coords).pin_memory()
     values_host = torch.empty(nnz, dtype=torch.float64).pin_memory()
     e2e_steps = max(2, min(args.steps, 5))
-    bsr.assembleBilinearHost(op, coords_host, values_host)
+    coords_dev = mesh.coords
+
+    def e2e_step():
+        if exchange is None:
+            bsr.assembleBilinearHost(op, coords_host, values_host)  # C ABI b2f_assemble_host; synchronises before returning
+        else:
+            coords_dev.copy_(coords_host, non_blocking=True)
+            bsr.assembleBilinear(op)
+            exchange.run()
+            values_host.copy_(mat.values(), non_blocking=True)
+            torch.cuda.synchronize()
+
+    e2e_step()
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        bsr.assembleBilinearHost(op, coords_host, values_host)  # synchronises the stream before returning
+        e2e_step()
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
     if dist is not None:
@@ -217,7 +221,10 @@ def run_b200(args):
     peak, peak_src = measured_peak()
     b_alg = algorithmic_bytes(4, nc, nn, nnzb, 1)
     achieved = b_alg / (ms_step * 1e-3) / 1e9
-    variant_names = {0: "node_gather", 1: "cell_atomic", 2: "cell_atomic_warpagg", 3: "node_gather"}
+    variant_names = {0: "node_gather_fan", 1: "cell_atomic", 2: "cell_atomic_warpagg", 3: "node_gather_fan", 4: "node_gather_slots"}
+    kernel_names = {0: "k_node_fan<LaplaceTet>", 1: "memset + k_cell_atomic<LaplaceTet>", 2: "memset + k_cell_atomic<LaplaceTet,warpagg>", 3: "k_node_fan<LaplaceTet>",
+                    4: "k_node_gather_slots<LaplaceTet>"}
+    # our kernels per step: the assembly kernel (+ pack and add kernels of the ghost exchange; NCCL's own kernels not counted)
     launches_per_step = 1 + (2 if exchange is not None else 0)
 
     # --- CPU baseline: oracle port of the reference's legacy loop on this box's host cores (bounded sample)
@@ -229,14 +236,17 @@ def run_b200(args):
         "config": {"workload": f"Poisson 3D P1 tets, structured Kuhn cube {n}^3 hexes per GPU ({nc} cells, {nn} nodes, {nnzb} nnz per GPU), BSR 1x1 values assembly",
                    "variant": variant_names.get(args.variant, str(args.variant)), "n_hex": n, "cells_per_gpu": nc, "nnz_per_gpu": nnz, "nnz_job": own_nnz,
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
-                   "parallelism": "1 rank per GPU, z-slab domain decomposition, NCCL ghost-row exchange" if world > 1 else "single GPU",
-                   "sparsity_build_ms": round(sparsity_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum},
-        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                   "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
+                   "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum},
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": b_alg, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "kernel": "k_node_gather<LaplaceTet>" if args.variant in (0, 3) else "k_cell_atomic<LaplaceTet>"},
+                     "kernel": kernel_names.get(args.variant, "?"),
+                     "traffic_source": NCU_TRAFFIC_NOTE if args.variant in (0, 3) and n == 203 and world == 1 else None},
         "cpu_baseline": cpu,
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(coords_host.numel() * 8), "d2h_bytes_per_step": int(values_host.numel() * 8),
-                "ms_per_step": round(e2e_s * 1e3, 3), "api": "b2f_assemble_host (pinned host coordinates in, values out)"},
+                "ms_per_step": round(e2e_s * 1e3, 3),
+                "api": "b2f_assemble_host (pinned host coordinates in, values out)" if exchange is None else
+                       "pinned coordinates H2D + BSRFormat.assembleBilinear + b2f_ghost_exchange + values D2H, per rank, max over ranks"},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
     }
@@ -284,7 +294,9 @@ def run_reference(args):
     from arcanefem_b200 import mesh as gen
     from oracle import oracle as orc
     n = args.n
-    cells, coords = gen.cube_kuhn(n, perturb=0.25, seed=1234)
+    from arcanefem_b200 import multigpu as mg
+    part = mg.slab_partition(n, 0, 1)  # the same mesh as rank 0 of the b200 arm at N = 1
+    cells, coords = part["cells"], part["coords"]
     nc, nn = cells.shape[0], coords.shape[0]
     threads = orc.num_threads()
     ri, co = orc.build_pattern(cells, nn)  # untimed: the metric is the values assembly on an existing pattern
