@@ -375,6 +375,11 @@ __device__ __forceinline__ void prefetch_l2(const void* p)
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 #endif
 }
+// L2 prefetch of a contiguous range (no destination, no completion tracking); size in bytes, multiple of 16
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes)
+{
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity)
 {
   uint32_t done;
@@ -585,11 +590,11 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 
 // One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
-// N" renaming costs no instruction.  Tets carry m = +-(eN x eO); flip tells the sign (m = -(eN x eO) when set).
-template <class Op, bool PER_BLOCK>
+// N" renaming costs no instruction.  Tets carry m = eN x eO.
+template <class Op, bool PER_BLOCK, bool SKIP_DIAG>
 __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], double* __restrict__ acc, const int32_t* __restrict__ cols,
                                          int k, uint32_t wc, long long cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
-                                         double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], bool& flip, double (&eC)[3],
+                                         double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
 {
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
@@ -614,7 +619,6 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       m[0] = eC[1] * eO[2] - eC[2] * eO[1];
       m[1] = eC[2] * eO[0] - eC[0] * eO[2];
       m[2] = eC[0] * eO[1] - eC[1] * eO[0];
-      flip = false;
     }
     return;
   }
@@ -623,22 +627,24 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
   double out[BS2];
   if constexpr (NV == 4) {
     const bool dropN = (wc >> 10) & 1u;
-    // local vertices (0, 1, 2, 3) = (row node, N, O, C): g1 = eO x eC, g2 = eC x eN, g3 = eN x eO
+    // local vertices (0, 1, 2, 3) = (row node, N, O, C): g1 = eO x eC, g2 = eC x eN, g3 = eN x eO = m (carried).
+    // h = -g1 = eC x eO is what the next step carries when O stays, so it is the product that is formed; the negations
+    // below fold into operand modifiers of the consumers.
+    double h[3];
+    h[0] = eC[1] * eO[2] - eC[2] * eO[1];
+    h[1] = eC[2] * eO[0] - eC[0] * eO[2];
+    h[2] = eC[0] * eO[1] - eC[1] * eO[0];
     TetGeom T;
-    T.g[1][0] = eO[1] * eC[2] - eO[2] * eC[1];
-    T.g[1][1] = eO[2] * eC[0] - eO[0] * eC[2];
-    T.g[1][2] = eO[0] * eC[1] - eO[1] * eC[0];
     T.g[2][0] = eC[1] * eN[2] - eC[2] * eN[1];
     T.g[2][1] = eC[2] * eN[0] - eC[0] * eN[2];
     T.g[2][2] = eC[0] * eN[1] - eC[1] * eN[0];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      // conditional sign flip on the integer pipe (the fp64 pipe is the busy one)
-      const long long bits = __double_as_longlong(m[d]) ^ (flip ? (long long)0x8000000000000000ull : 0ll);
-      T.g[NV - 1][d] = __longlong_as_double(bits);
-      T.g[0][d] = -(T.g[1][d] + T.g[2][d] + T.g[NV - 1][d]);
+      T.g[1][d] = -h[d];
+      T.g[NV - 1][d] = m[d];
+      T.g[0][d] = h[d] - T.g[2][d] - m[d];
     }
-    const double det = eC[0] * T.g[NV - 1][0] + eC[1] * T.g[NV - 1][1] + eC[2] * T.g[NV - 1][2];
+    const double det = eC[0] * m[0] + eC[1] * m[1] + eC[2] * m[2];
     T.vol6 = fabs(det);
     T.s = fast_rcp(6.0 * T.vol6);
     const auto G = tet_finish(op, T, cell, odd);
@@ -654,10 +660,12 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
       accC[e] += out[e];
-    op.block(G, 0, 0, out);
+    if constexpr (!SKIP_DIAG) {
+      op.block(G, 0, 0, out);
 #pragma unroll
-    for (int e = 0; e < BS2; ++e)
-      diag[e] += out[e];
+      for (int e = 0; e < BS2; ++e)
+        diag[e] += out[e];
+    }
     // one vertex leaves: its accumulator is flushed (plain store: it was loaded on entry).  C becomes N (renaming by
     // the caller); the vertex that stays becomes / remains O.  New m: (eC x eN) = g2 if N stays, (eC x eO) = -g1 if O stays.
     double leave[BS2];
@@ -674,9 +682,8 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
       eO[d] = dropN ? eO[d] : eN[d];
-      m[d] = dropN ? T.g[1][d] : T.g[2][d];
+      m[d] = dropN ? h[d] : T.g[2][d]; // new window (C, O'): eC x eO = h if O stays, eC x eN = g2 if N stays
     }
-    flip = dropN;
   }
   else {
     const auto G = tri_prepare(op, X0, eN, eC, cell, odd);
@@ -688,10 +695,12 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
       accC[e] += out[e];
-    op.block(G, 0, 0, out);
+    if constexpr (!SKIP_DIAG) {
+      op.block(G, 0, 0, out);
 #pragma unroll
-    for (int e = 0; e < BS2; ++e)
-      diag[e] += out[e];
+      for (int e = 0; e < BS2; ++e)
+        diag[e] += out[e];
+    }
     store_block<BS, PER_BLOCK>(acc, k, sN, accN);
   }
 }
@@ -705,13 +714,18 @@ struct FanCfg : SlotsCfg<Op>
   static constexpr int ROWS = (Op::BS == 1) ? B2F_FAN_ROWS : 64; // block rows (= threads) per CTA
   static_assert(ROWS == 128 || ROWS == 64 || ROWS == 32, "tile extents exist for 128, 64 and 32 rows");
 };
+#ifndef B2F_FAN_TILE_AHEAD
+#define B2F_FAN_TILE_AHEAD 0
+#endif
 #ifndef B2F_FAN_MINBLOCKS
-#define B2F_FAN_MINBLOCKS 1
+#define B2F_FAN_MINBLOCKS 6
 #endif
 #ifndef B2F_FAN_CARVEOUT
 #define B2F_FAN_CARVEOUT -1
 #endif
-template <class Op, bool PER_BLOCK>
+// DIAG_BY_ROW_SUM (operators whose element matrices have zero row sums, BS = 1, overwrite mode): the diagonal entry is
+// not accumulated along the walk but formed at the end as minus the sum of the row's off-diagonal entries.
+template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM>
 __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBLOCKS : 1)) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
 {
   using C = FanCfg<Op>;
@@ -770,6 +784,21 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
     load_xyz(A.coords, (int32_t)row, X0);
   }
+#if B2F_FAN_TILE_AHEAD > 0
+  // Streaming data of the tile that will start when this one retires (about one wave of CTAs ahead) is pulled into L2
+  // now, so that tile's dependent prologue loads (extents -> bulk copies -> first gathers) pay L2 instead of DRAM latency.
+  if (t == 32) {
+    const long long fr0 = row0 + (long long)B2F_FAN_TILE_AHEAD * C::ROWS;
+    if (fr0 < A.nb_node) {
+      const long long fr1 = (fr0 + C::ROWS < A.nb_node) ? fr0 + C::ROWS : A.nb_node;
+      const int32_t fv0 = __ldg(A.row_index + fr0) & ~3, fv1 = __ldg(A.row_index + fr1);
+      const int32_t fa0 = __ldg(A.fan_ptr + fr0) & ~3, fa1 = __ldg(A.fan_ptr + fr1);
+      bulk_prefetch_l2(A.columns + fv0, (uint32_t)(((fv1 - fv0) + 3) & ~3) * 4u);
+      bulk_prefetch_l2(A.fan_steps + fa0, (uint32_t)(((fa1 - fa0) + 3) & ~3) * 4u);
+      bulk_prefetch_l2(A.coords + 3 * (fr0 & ~1ll), (uint32_t)((((fr1 - (fr0 & ~1ll)) * 24) + 15) & ~15ll));
+    }
+  }
+#endif
   mbar_wait(bar, 0);
   __syncthreads();
 
@@ -787,7 +816,6 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
-    bool flip = false;
     double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
     uint32_t w = st[0];
     load_xyz(A.coords, cols[w & 1023u], Xn);
@@ -808,7 +836,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, flip, eP, accP, sP, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag);
       newest_is_Q = false;
       if (++p >= nstep)
         break;
@@ -819,7 +847,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, flip, eQ, accQ, sQ, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag);
       newest_is_Q = true;
       if (++p >= nstep)
         break;
@@ -835,6 +863,12 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
     if constexpr (NV == 4) {
       if (sO)
         store_block<BS, PER_BLOCK>(acc, k, sO, accO);
+    }
+    if constexpr (DIAG_BY_ROW_SUM) {
+      double sum = 0.0;
+      for (int x = 1; x < k; ++x)
+        sum += acc[x];
+      diag[0] = -sum;
     }
     store_block<BS, PER_BLOCK>(acc, k, 0, diag);
   }
@@ -861,7 +895,8 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
 {
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
     using C = FanCfg<Op>;
-    auto kern = k_node_fan<Op, PER_BLOCK>;
+    constexpr bool CAN_ROW_SUM = Op::ROW_SUM_ZERO && Op::BS == 1;
+    auto kern = (CAN_ROW_SUM && !A.accumulate) ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM> : k_node_fan<Op, PER_BLOCK, false>;
     if (B2F_FAN_CARVEOUT >= 0) {
       cudaError_t ec = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, B2F_FAN_CARVEOUT);
       if (ec != cudaSuccess)

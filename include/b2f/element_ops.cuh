@@ -20,6 +20,7 @@
 //
 // Operator concept used by the assembly kernels (include/b2f/assemble.cuh):
 //   static constexpr int NV, BS;
+//   static constexpr bool ROW_SUM_ZERO;                  // rows of every element matrix sum to zero (BS = 1 only)
 //   static constexpr bool NEEDS_CELL;                    // prepare() reads per-cell data (the cell id must be fetched)
 //   struct Geom;                                         // per-cell prepared geometry, registers only
 //   __device__ Geom prepare(const double (&X)[NV][3], long long cell) const;
@@ -100,6 +101,7 @@ __device__ __forceinline__ TriGeom tri_geometry(const double (&X)[3][3])
 struct LaplaceTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
@@ -113,6 +115,7 @@ struct LaplaceTet
 struct LaplaceTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   struct Geom
   {
@@ -140,6 +143,7 @@ struct LaplaceTri
 struct ElasticityTri
 {
   static constexpr int NV = 3, BS = 2;
+  static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
   struct Geom
@@ -171,6 +175,7 @@ struct ElasticityTri
 struct ElasticityTet
 {
   static constexpr int NV = 4, BS = 3;
+  static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
   using Geom = TetGeom;
@@ -197,6 +202,7 @@ struct ElasticityTet
 struct HeatTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true; // per-cell conductivity
   double lambda, inv_dt;
   const double* cell_lambda;
@@ -229,6 +235,7 @@ struct HeatTri
 struct HeatTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true;
   double lambda, inv_dt;
   const double* cell_lambda;
