@@ -556,12 +556,12 @@ constexpr unsigned FAN_START = 0x80000000u;
 
 // Operator entry points of the fan kernel, selected by arity (only the matching one is instantiated).
 template <class Op>
-__device__ __forceinline__ auto tet_finish(const Op& op, const TetGeom& T, long long cell, bool odd) -> decltype(op.finish(T, cell, odd))
+__device__ __forceinline__ auto tet_finish(const Op& op, const TetGeom& T, double cell, bool odd) -> decltype(op.finish(T, cell, odd))
 {
   return op.finish(T, cell, odd);
 }
 template <class Op>
-__device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3], const double (&XA)[3], const double (&XC)[3], long long cell, bool odd)
+__device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3], const double (&XA)[3], const double (&XC)[3], double cell, bool odd)
   -> decltype(op.prepare_oriented(std::declval<const double (&)[3][3]>(), cell, odd))
 {
   const double X[3][3] = { { X0[0], X0[1], X0[2] }, { XA[0], XA[1], XA[2] }, { XC[0], XC[1], XC[2] } };
@@ -593,7 +593,7 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
 template <class Op, bool PER_BLOCK, bool SKIP_DIAG>
 __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], double* __restrict__ acc, const int32_t* __restrict__ cols,
-                                         int k, uint32_t wc, long long cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
+                                         int k, uint32_t wc, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
 {
@@ -717,16 +717,13 @@ struct FanCfg : SlotsCfg<Op>
 #ifndef B2F_FAN_TILE_AHEAD
 #define B2F_FAN_TILE_AHEAD 0
 #endif
-#ifndef B2F_FAN_MINBLOCKS
-#define B2F_FAN_MINBLOCKS 6
-#endif
 #ifndef B2F_FAN_CARVEOUT
 #define B2F_FAN_CARVEOUT -1
 #endif
 // DIAG_BY_ROW_SUM (operators whose element matrices have zero row sums, BS = 1, overwrite mode): the diagonal entry is
 // not accumulated along the walk but formed at the end as minus the sum of the row's off-diagonal entries.
 template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM>
-__global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBLOCKS : 1)) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
+__global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
 {
   using C = FanCfg<Op>;
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
@@ -823,6 +820,25 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
     bool newest_is_Q = false;
     // The prefetched coordinates are consumed (edge vector) BEFORE the next prefetch is issued into the same registers:
     // the consumer then never waits on a scoreboard that the new loads have just re-armed.
+    // per-cell datum of the operator (heat conductivity): cell id fetched two steps ahead, its value one step ahead
+    double cv = 0.0, cvn = 0.0;
+    uint32_t cidn = 0;
+    if constexpr (Op::NEEDS_CELL) {
+      cv = op.cell_value((long long)__ldg(cl));
+      if (nstep > 1)
+        cvn = op.cell_value((long long)__ldg(cl + 1));
+      if (nstep > 2)
+        cidn = __ldg(cl + 2);
+    }
+    auto next_cell = [&](int pp) { // called after step pp
+      if constexpr (Op::NEEDS_CELL) {
+        cv = cvn;
+        if (pp + 2 < nstep)
+          cvn = op.cell_value((long long)cidn);
+        if (pp + 3 < nstep)
+          cidn = __ldg(cl + pp + 3);
+      }
+    };
     auto enter = [&](double(&e)[3]) {
 #pragma unroll
       for (int d = 0; d < 3; ++d)
@@ -836,7 +852,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag);
+      next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
         break;
@@ -847,7 +864,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, (Op::BS == 1 ? B2F_FAN_MINBL
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, Op::NEEDS_CELL ? (long long)__ldg(cl + p) : 0ll, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag);
+      next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
         break;

@@ -20,18 +20,24 @@
 //
 // Operator concept used by the assembly kernels (include/b2f/assemble.cuh):
 //   static constexpr int NV, BS;
+//   static constexpr int FAN_WARPS_PER_SM;               // resident warps per SM the fan kernel is compiled for
 //   static constexpr bool ROW_SUM_ZERO;                  // rows of every element matrix sum to zero (BS = 1 only)
 //   static constexpr bool NEEDS_CELL;                    // prepare() reads per-cell data (the cell id must be fetched)
 //   struct Geom;                                         // per-cell prepared geometry, registers only
 //   __device__ Geom prepare(const double (&X)[NV][3], long long cell) const;
 //   __device__ void block(const Geom&, int a, int b, double (&out)[BS*BS]) const;  // a, b compile-time after unrolling
-//   tets:      __device__ Geom finish(const TetGeom&, long long cell, bool odd) const;   // geometry already built (fan kernel)
-//   triangles: __device__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool odd) const;
+//   __device__ double cell_value(long long cell) const;  // the per-cell datum (prefetched by the fan kernel), 0 if none
+//   tets:      __device__ Geom finish(const TetGeom&, double cell_value, bool odd) const;   // geometry already built (fan kernel)
+//   triangles: __device__ Geom prepare_oriented(const double (&X)[3][3], double cell_value, bool odd) const;
 //              odd = the vertices are listed in an odd permutation of the cell's own order
 // Operators are invariant under even permutations of the cell's vertices, which the node-gather kernel
 // uses to bring the row node to local index 0.
 #pragma once
 #include <cuda_runtime.h>
+
+#ifndef B2F_FAN_WARPS
+#define B2F_FAN_WARPS 24
+#endif
 
 namespace b2f {
 
@@ -101,11 +107,13 @@ __device__ __forceinline__ TriGeom tri_geometry(const double (&X)[3][3])
 struct LaplaceTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr int FAN_WARPS_PER_SM = B2F_FAN_WARPS; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
-  __device__ __forceinline__ Geom finish(const TetGeom& T, long long, bool) const { return T; }
+  __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, double, bool) const { return T; }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
   {
     out[0] = (G.g[a][0] * G.g[b][0] + G.g[a][1] * G.g[b][1] + G.g[a][2] * G.g[b][2]) * G.s;
@@ -115,6 +123,7 @@ struct LaplaceTet
 struct LaplaceTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr int FAN_WARPS_PER_SM = B2F_FAN_WARPS; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   struct Geom
@@ -129,7 +138,8 @@ struct LaplaceTri
     G.s = 1.0 / (2.0 * fabs(G.t.a2));
     return G;
   }
-  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool) const { return prepare(X, cell); }
+  __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], double, bool) const { return prepare(X, 0); }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[1]) const
   {
     out[0] = (G.t.n[a][0] * G.t.n[b][0] + G.t.n[a][1] * G.t.n[b][1]) * G.s;
@@ -143,6 +153,7 @@ struct LaplaceTri
 struct ElasticityTri
 {
   static constexpr int NV = 3, BS = 2;
+  static constexpr int FAN_WARPS_PER_SM = 16; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
@@ -158,7 +169,8 @@ struct ElasticityTri
     G.s = 1.0 / (2.0 * fabs(G.t.a2));
     return G;
   }
-  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool) const { return prepare(X, cell); }
+  __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], double, bool) const { return prepare(X, 0); }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[4]) const
   {
     const double pxa = G.t.n[a][0], pya = G.t.n[a][1], pxb = G.t.n[b][0], pyb = G.t.n[b][1];
@@ -175,12 +187,14 @@ struct ElasticityTri
 struct ElasticityTet
 {
   static constexpr int NV = 4, BS = 3;
+  static constexpr int FAN_WARPS_PER_SM = 4; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
   double lambda, mu2;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
-  __device__ __forceinline__ Geom finish(const TetGeom& T, long long, bool) const { return T; }
+  __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, double, bool) const { return T; }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[9]) const
   {
     const double mu = 0.5 * mu2;
@@ -202,6 +216,7 @@ struct ElasticityTet
 struct HeatTri
 {
   static constexpr int NV = 3, BS = 1;
+  static constexpr int FAN_WARPS_PER_SM = 24; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true; // per-cell conductivity
   double lambda, inv_dt;
@@ -212,14 +227,14 @@ struct HeatTri
     double ks; // lambda * 0.25 / area
     double m; // area / 12 / dt
   };
-  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const { return prepare_oriented(X, cell, false); }
+  __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
+  __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const { return prepare_oriented(X, cell_value(cell), false); }
   // odd: X lists the cell's vertices in an odd permutation of the cell's own order (the signed area flips back)
-  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], long long cell, bool odd) const
+  __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], double lam, bool odd) const
   {
     Geom G;
     G.t = tri_geometry(X);
     const double area = odd ? -0.5 * G.t.a2 : 0.5 * G.t.a2;
-    const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
     G.ks = lam * 0.25 / area;
     G.m = area * (1.0 / 12.0) * inv_dt;
     return G;
@@ -235,6 +250,7 @@ struct HeatTri
 struct HeatTet
 {
   static constexpr int NV = 4, BS = 1;
+  static constexpr int FAN_WARPS_PER_SM = 20; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true;
   double lambda, inv_dt;
@@ -244,12 +260,12 @@ struct HeatTet
     TetGeom t;
     double ks, m;
   };
-  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const { return finish(tet_geometry(X), cell, false); }
-  __device__ __forceinline__ Geom finish(const TetGeom& T, long long cell, bool) const
+  __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
+  __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const { return finish(tet_geometry(X), cell_value(cell), false); }
+  __device__ __forceinline__ Geom finish(const TetGeom& T, double lam, bool) const
   {
     Geom G;
     G.t = T;
-    const double lam = cell_lambda ? __ldg(cell_lambda + cell) : lambda;
     G.ks = lam * G.t.s;
     G.m = G.t.vol6 * (1.0 / 120.0) * inv_dt;
     return G;

@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""Secondary workloads of BASELINE.json (configs #3 and #4) on one GPU — the headline metric stays in bench.py.
+
+  elasticity3d  config #3: linear elasticity 3D P1 tets, BSR 3x3, N=149 (19.8M tets), step = values assembly + Dirichlet
+                row elimination on the plane z=0 (flag + apply)
+  heat3d/heat2d config #4: heat, mass + stiffness re-assembled every time step on a fixed pattern (repeated-assembly throughput)
+  poisson2d     2D twin of the headline (square, 2 triangles per quad)
+Prints one JSON line per workload: GNNZ/s, ms/step, algorithmic GB/s and the fraction of the measured HBM peak.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def run(workload, n, steps, warmup, variant):
+    import torch
+    import arcanefem_b200 as fem
+    from arcanefem_b200 import mesh as gen
+    from arcanefem_b200.bsr import Mesh
+    if workload == "elasticity3d":
+        dim, bs, (cells, coords), op = 3, 3, gen.cube_kuhn(n), fem.Operator.elasticity(21.0e5, 0.28)
+    elif workload == "heat3d":
+        dim, bs, (cells, coords), op = 3, 1, gen.cube_kuhn(n), None
+    elif workload == "heat2d":
+        dim, bs, (cells, coords), op = 2, 1, gen.square(n), None
+    elif workload == "poisson2d":
+        dim, bs, (cells, coords), op = 2, 1, gen.square(n), fem.Operator.laplace()
+    else:
+        raise SystemExit(f"unknown workload {workload}")
+    nc, nn, nv = cells.shape[0], coords.shape[0], cells.shape[1]
+    keep = []
+    if op is None:
+        lam = torch.as_tensor(np.random.default_rng(5).uniform(0.5, 2.0, size=nc)).cuda()
+        keep.append(lam)
+        op = fem.Operator.heat(1.75, 0.1, cell_lambda=lam)
+    bsr = fem.BSRFormat(bs)
+    bsr.initialize(Mesh.from_numpy(dim, cells, coords), True, assembly_variant=variant)
+    bsr.computeSparsity()
+    mat = bsr.matrix()
+    nnzb, nnz = mat.nbCol(), mat.nbNz()
+    ls = fem.DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    group = torch.as_tensor(gen.boundary_nodes(coords, dim - 1, 0.0)).cuda()
+
+    def step():
+        bsr.assembleBilinear(op)
+        if workload == "elasticity3d":
+            ls.clearValues()
+            for comp in range(bs):
+                bsr.applyDirichletViaRowElimination(group, 0.0, dof_index=comp)
+            ls.applyDirichlet()
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    b_alg = 4 * nv * nc + 24 * nn + 4 * (nn + 1) + 4 * nnzb + 8 * bs * bs * nnzb
+    if workload.startswith("heat"):
+        b_alg += 8 * nc  # per-cell conductivity
+    gbs = b_alg / (ms * 1e-3) / 1e9
+    st = bsr.stats()
+    return {"workload": workload, "n": n, "cells": nc, "nodes": nn, "block_size": bs, "nnz": nnz, "ms_per_step": round(ms, 4), "gnnz_per_s": round(nnz / (ms * 1e-3) / 1e9, 2),
+            "algorithmic_bytes": b_alg, "achieved_gbs": round(gbs, 1), "frac_of_measured_hbm_peak": round(gbs / peak(), 4), "steps": steps, "variant": variant,
+            "gather_fallback_tiles": st["gather_fallback_tiles"], "columns_not_found": st["columns_not_found"],
+            "checksum": float(mat.values().abs().sum().item())}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workloads", default="elasticity3d,heat3d,heat2d,poisson2d")
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--variant", type=int, default=3)
+    args = ap.parse_args()
+    sizes = {"elasticity3d": 149, "heat3d": 203, "heat2d": 5000, "poisson2d": 5000}
+    for w in args.workloads.split(","):
+        print(json.dumps(run(w, sizes[w], args.steps, args.warmup, args.variant)), flush=True)
+
+
+if __name__ == "__main__":
+    main()
