@@ -81,6 +81,7 @@ PROTOTYPES = {
     "b2f_reset_values": (C.c_int, [_H, _S]),
     "b2f_get_bsr": (C.c_int, [_H, _P(BsrView)]),
     "b2f_to_csr": (C.c_int, [_H, _P(CsrView), _S]),
+    "b2f_csr_global_numbering": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, _S]),
     "b2f_get_system": (C.c_int, [_H, _P(SystemView)]),
     "b2f_get_stats": (C.c_int, [_H, _P(Stats)]),
     "b2f_get_plan": (C.c_int, [_H, _P(PlanView)]),
@@ -92,6 +93,7 @@ PROTOTYPES = {
     "b2f_rhs_constant_source": (C.c_int, [_H, C.c_double, _S]),
     "b2f_rhs_neumann": (C.c_int, [_H, _P(Neumann), _S]),
     "b2f_dirichlet_flag_penalty": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double, _S]),
+    "b2f_dirichlet_flag_weak_penalty": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double, _S]),
     "b2f_dirichlet_flag_elimination": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_int32, _S]),
     "b2f_dirichlet_apply": (C.c_int, [_H, _S]),
     "b2f_spmv": (C.c_int, [_H, C.c_void_p, C.c_void_p, _S]),

@@ -343,6 +343,16 @@ class BSRFormat:
         check(self._lib.b2f_get_stats(self._h, C.byref(s)))
         return {k: int(getattr(s, k)) for k, _ in _lib.Stats._fields_}
 
+    def csrGlobalNumbering(self, dof_number):
+        """(rows_global, cols_global) of the CSR view for the device int32 numbering array `dof_number` [nb_dof]."""
+        torch = _torch()
+        v = _lib.CsrView()
+        check(self._lib.b2f_to_csr(self._h, C.byref(v), _stream()))
+        rows = torch.empty(int(v.nb_row), dtype=torch.int32, device="cuda")
+        cols = torch.empty(int(v.nb_value), dtype=torch.int32, device="cuda")
+        check(self._lib.b2f_csr_global_numbering(self._h, C.c_void_p(dof_number.data_ptr()), C.c_void_p(rows.data_ptr()), C.c_void_p(cols.data_ptr()), _stream()))
+        return rows, cols
+
     def plan(self):
         """Gather plan arrays as tensors (views; "<u4" words are exposed as int32 bit patterns)."""
         v = _lib.PlanView()
@@ -379,6 +389,10 @@ class BSRFormat:
     def applyDirichletViaPenalty(self, node_ids, value, penalty, dof_index=0):
         check(self._lib.b2f_dirichlet_flag_penalty(self._h, C.c_void_p(node_ids.data_ptr()), int(node_ids.numel()), int(dof_index), float(value),
                                                    float(penalty), _stream()))
+
+    def applyDirichletViaWeakPenalty(self, node_ids, value, penalty, dof_index=0):
+        check(self._lib.b2f_dirichlet_flag_weak_penalty(self._h, C.c_void_p(node_ids.data_ptr()), int(node_ids.numel()), int(dof_index), float(value),
+                                                        float(penalty), _stream()))
 
     def applyDirichletViaRowElimination(self, node_ids, value, dof_index=0, mode=ELIMINATE_ROW):
         check(self._lib.b2f_dirichlet_flag_elimination(self._h, C.c_void_p(node_ids.data_ptr()), int(node_ids.numel()), int(dof_index), float(value),

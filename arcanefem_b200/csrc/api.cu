@@ -204,6 +204,15 @@ int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream)
   return B2F_OK;
 }
 
+int b2f_csr_global_numbering(b2f_handle h, const int32_t* dof_number, int32_t* rows_global_out, int32_t* cols_global_out, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!dof_number)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_csr_global_numbering: null numbering");
+  return csr_global_numbering(h, dof_number, rows_global_out, cols_global_out, (cudaStream_t)stream);
+}
+
 int b2f_get_system(b2f_handle h, b2f_system_view* out)
 {
   B2F_CHECK_HANDLE(h);
@@ -381,7 +390,16 @@ int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n,
   B2F_NEED_PATTERN(h);
   if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_penalty: bad arguments (dof_index=%d, n=%lld)", dof_index, (long long)n);
-  return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, (cudaStream_t)stream);
+  return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, 0, (cudaStream_t)stream);
+}
+
+int b2f_dirichlet_flag_weak_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_weak_penalty: bad arguments (dof_index=%d, n=%lld)", dof_index, (long long)n);
+  return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, 1, (cudaStream_t)stream);
 }
 
 int b2f_dirichlet_flag_elimination(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, int32_t mode, b2f_stream stream)

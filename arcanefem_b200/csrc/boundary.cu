@@ -110,7 +110,7 @@ namespace {
         atomicAdd(rhs + (long long)n[k] * bs, contrib);
   }
 
-  __global__ void k_flag_penalty(const int32_t* __restrict__ ids, long long n, const uint8_t* __restrict__ own, int bs, int dof_index, double value, double penalty,
+  __global__ void k_flag_penalty(const int32_t* __restrict__ ids, long long n, const uint8_t* __restrict__ own, int bs, int dof_index, double value, double penalty, int weak,
                                  uint8_t* __restrict__ forced_info, double* __restrict__ forced_value, double* __restrict__ rhs)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -120,7 +120,7 @@ namespace {
     if (own != nullptr && !own[node])
       return;
     const long long dof = (long long)node * bs + dof_index;
-    forced_info[dof] = 1;
+    forced_info[dof] = weak ? 2 : 1; // 2: WeakPenalty, a_ii += P (modules/testlab/FemModule.cc:687-717)
     forced_value[dof] = penalty;
     rhs[dof] = penalty * value;
   }
@@ -222,8 +222,10 @@ namespace {
       }
       S.rhs[r] = S.elim_value[r];
     }
-    if (forced)
-      S.values[value_index<BS, PER_BLOCK>(rb, k, 0, ir, ir)] = S.forced_value[r]; // the diagonal block is slot 0
+    if (forced) { // the diagonal block is slot 0
+      double* d = S.values + value_index<BS, PER_BLOCK>(rb, k, 0, ir, ir);
+      *d = (S.forced_info[r] == 2) ? *d + S.forced_value[r] : S.forced_value[r];
+    }
   }
 
   template <int BS, bool PER_BLOCK>
@@ -293,11 +295,11 @@ int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s)
   return B2F_OK;
 }
 
-int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, cudaStream_t s)
+int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, int weak, cudaStream_t s)
 {
   if (n == 0)
     return B2F_OK;
-  k_flag_penalty<<<grid_for(n, 256), 256, 0, s>>>(ids, n, h->mesh.node_is_own, h->bs, dof_index, value, penalty, h->forced_info.as<uint8_t>(), h->forced_value.as<double>(),
+  k_flag_penalty<<<grid_for(n, 256), 256, 0, s>>>(ids, n, h->mesh.node_is_own, h->bs, dof_index, value, penalty, weak, h->forced_info.as<uint8_t>(), h->forced_value.as<double>(),
                                                   h->rhs.as<double>());
   B2F_CUDA(cudaGetLastError());
   return B2F_OK;

@@ -86,6 +86,45 @@ int to_csr(b2f_context_s* h, cudaStream_t s)
   return B2F_OK;
 }
 
+// Local -> global numbering of the CSR view on device.  The reference does this on the host, one entry at a time, right
+// before HYPRE_IJMatrixSetValues (femutils/HypreDoFLinearSystem.cc:474-519: rows_index[i] = numbering[dof],
+// columns[q] = numbering[local column]).
+namespace {
+  __global__ void __launch_bounds__(256) k_renumber(const int32_t* __restrict__ in, long long n, const int32_t* __restrict__ numbering, long long nb_dof, int32_t* __restrict__ out,
+                                                    unsigned long long* __restrict__ errors)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+      return;
+    const int32_t c = in ? in[i] : (int32_t)i;
+    if (c < 0 || c >= nb_dof) {
+      atomicAdd(errors, 1ull);
+      out[i] = -1;
+      return;
+    }
+    out[i] = numbering[c];
+  }
+} // namespace
+
+int csr_global_numbering(b2f_context_s* h, const int32_t* dof_number, int32_t* rows_global, int32_t* cols_global, cudaStream_t s)
+{
+  if (!h->has_csr) {
+    int rc = to_csr(h, s);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  const long long nd = h->nb_dof, nnz = h->nb_nz;
+  const int32_t* cols = h->bs == 1 ? h->columns.as<int32_t>() : h->csr_cols.as<int32_t>();
+  unsigned long long* err = h->counters.as<unsigned long long>() + 2;
+  B2F_CUDA(cudaMemsetAsync(err, 0, sizeof(unsigned long long), s));
+  if (rows_global && nd > 0)
+    k_renumber<<<grid_for(nd, 256), 256, 0, s>>>(nullptr, nd, dof_number, nd, rows_global, err);
+  if (cols_global && nnz > 0)
+    k_renumber<<<grid_for(nnz, 256), 256, 0, s>>>(cols, nnz, dof_number, nd, cols_global, err);
+  B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
 int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s)
 {
   const long long nn = h->mesh.nb_node, nrow = nn * h->bs;

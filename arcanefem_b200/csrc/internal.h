@@ -104,11 +104,12 @@ int rhs_fill(b2f_context_s* h, double v, cudaStream_t s);
 int clear_values(b2f_context_s* h, cudaStream_t s);
 int rhs_constant_source(b2f_context_s* h, double qdot, cudaStream_t s);
 int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s);
-int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, cudaStream_t s);
+int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, int weak, cudaStream_t s);
 int dirichlet_flag_elimination(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, int mode, cudaStream_t s);
 int dirichlet_apply(b2f_context_s* h, cudaStream_t s);
 // convert.cu
 int to_csr(b2f_context_s* h, cudaStream_t s);
+int csr_global_numbering(b2f_context_s* h, const int32_t* dof_number, int32_t* rows_global, int32_t* cols_global, cudaStream_t s);
 int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
 // ghost.cu
 int ghost_plan(b2f_context_s* h, void* comm, int rank, int world, const int32_t* node_owner, const int64_t* node_gid, cudaStream_t s);

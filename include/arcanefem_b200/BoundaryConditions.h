@@ -18,6 +18,11 @@ namespace BoundaryConditions {
   {
     check(b2f_dirichlet_flag_penalty(ls.handle(), g.ids, g.n, 0, value, penalty, stream));
   }
+  // WeakPenalty of modules/testlab/FemModule.cc:687-717 (a_ii += P; the reference has it on the CPU only)
+  inline void applyDirichletViaWeakPenalty(DoFLinearSystem& ls, const NodeGroup& g, Real value, Real penalty, b2f_stream stream = nullptr)
+  {
+    check(b2f_dirichlet_flag_weak_penalty(ls.handle(), g.ids, g.n, 0, value, penalty, stream));
+  }
   // vectorial variant :513-545: one call per component whose value string is not "NULL"
   inline void applyDirichletViaPenaltyVectorial(DoFLinearSystem& ls, const NodeGroup& g, int component, Real value, Real penalty, b2f_stream stream = nullptr)
   {

@@ -201,6 +201,12 @@ int b2f_get_bsr(b2f_handle h, b2f_bsr_view* out);
 /* BSRMatrix::toCsr + CSRFormatView (BSRFormat.h:194-256,414-430): zero-copy alias of the BSR arrays when
  * BS = 1; device expansion of rows/columns when BS > 1 (values alias; needs B2F_LAYOUT_PER_ROW). */
 int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream);
+/* Hand-off helper for a distributed solver (femutils/HypreDoFLinearSystem.cc:474-519, done there in host loops over
+ * every row and every entry): rows_global_out[i] = dof_number[i] for the nb_dof local rows and
+ * cols_global_out[q] = dof_number[csr.columns[q]] for the nb_value entries of the CSR view, on the device.
+ * dof_number is the device array of the global matrix numbering of the local dofs (own: first_own_row + own index,
+ * ghosts: the owner's number, :264-303).  Either output may be NULL. */
+int b2f_csr_global_numbering(b2f_handle h, const int32_t* dof_number, int32_t* rows_global_out, int32_t* cols_global_out, b2f_stream stream);
 int b2f_get_system(b2f_handle h, b2f_system_view* out);
 /* Device pointers of the gather plan built by b2f_compute_sparsity (read-only; for inspection and tests). */
 int b2f_get_plan(b2f_handle h, b2f_plan_view* out);
@@ -222,6 +228,8 @@ int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream);
 int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream);
 /* applyDirichletToNodeGroupViaPenalty (ArcaneFemFunctionsGpu.h:434-456). */
 int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream);
+/* WeakPenalty (modules/testlab/FemModule.cc:687-717; CPU-only in the reference): a_ii += P at b2f_dirichlet_apply, rhs_i = P*g. */
+int b2f_dirichlet_flag_weak_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream);
 /* applyDirichletToNodeGroupViaRowElimination<MODE> (ArcaneFemFunctionsGpu.h:461-482). */
 int b2f_dirichlet_flag_elimination(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, int32_t mode, b2f_stream stream);
 /* _applyRowElimination + _applyForcedValuesToLhs (HypreDoFLinearSystem.cc:319-382), plus row+column

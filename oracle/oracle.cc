@@ -600,7 +600,7 @@ void orc_rhs_neumann(int nvf, int bs, int has_value, double value, double vx, do
 // Row elimination flag: :461-482 (mode 1 = ELIMINATE_ROW; 2 = ELIMINATE_ROW_COLUMN,
 // femutils/AlephDoFLinearSystem.cc semantics).
 // ---------------------------------------------------------------------------
-void orc_dirichlet_flag_penalty(int bs, int dof_index, double value, double penalty, int64_t n, const int32_t* node_ids, const uint8_t* node_is_own,
+void orc_dirichlet_flag_penalty(int bs, int dof_index, double value, double penalty, int weak, int64_t n, const int32_t* node_ids, const uint8_t* node_is_own,
                                 uint8_t* forced_info, double* forced_value, double* rhs)
 {
   for (int64_t k = 0; k < n; ++k) {
@@ -608,7 +608,7 @@ void orc_dirichlet_flag_penalty(int bs, int dof_index, double value, double pena
     if (node_is_own && !node_is_own[node])
       continue;
     int64_t dof = (int64_t)node * bs + dof_index;
-    forced_info[dof] = 1;
+    forced_info[dof] = weak ? 2 : 1; // weak: modules/testlab/FemModule.cc:687-717 (a_ii += P)
     forced_value[dof] = penalty;
     rhs[dof] = penalty * value;
   }
@@ -684,7 +684,7 @@ void orc_dirichlet_apply(int64_t nb_dof, const int32_t* rows, const int32_t* col
     if (forced_info[d]) {
       for (int32_t q = rows[d]; q < rows[d + 1]; ++q)
         if (columns[q] == d) {
-          values[q] = forced_value[d];
+          values[q] = (forced_info[d] == 2) ? values[q] + forced_value[d] : forced_value[d]; // 2: WeakPenalty
           break;
         }
     }

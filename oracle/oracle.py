@@ -120,9 +120,9 @@ def rhs_neumann(face_node, coords, bs, rhs, value=None, value_xyz=(0.0, 0.0, 0.0
     return rhs
 
 
-def dirichlet_flag_penalty(bs, dof_index, value, penalty, node_ids, forced_info, forced_value, rhs, node_is_own=None):
+def dirichlet_flag_penalty(bs, dof_index, value, penalty, node_ids, forced_info, forced_value, rhs, node_is_own=None, weak=False):
     node_ids = np.ascontiguousarray(node_ids, dtype=np.int32)
-    lib().orc_dirichlet_flag_penalty(C.c_int(bs), C.c_int(dof_index), C.c_double(value), C.c_double(penalty), C.c_int64(node_ids.shape[0]), _p(node_ids),
+    lib().orc_dirichlet_flag_penalty(C.c_int(bs), C.c_int(dof_index), C.c_double(value), C.c_double(penalty), C.c_int(1 if weak else 0), C.c_int64(node_ids.shape[0]), _p(node_ids),
                                      _p(node_is_own), _p(forced_info), _p(forced_value), _p(rhs))
 
 

@@ -220,8 +220,8 @@ def _dirichlet_case(mesh_name, bs, kind, mode):
     evalue = np.zeros(ndof)
     comps = [(0, 0.5)] if bs == 1 else [(0, 0.5), (bs - 1, -0.25)]  # vectorial: one call per non-"NULL" component
     for dof_index, g in comps:
-        if mode == "penalty":
-            orc.dirichlet_flag_penalty(bs, dof_index, g, 1.0e30, group, finfo, fval, rhs)
+        if mode in ("penalty", "weak"):
+            orc.dirichlet_flag_penalty(bs, dof_index, g, 1.0e30 if mode == "penalty" else 1.0e8, group, finfo, fval, rhs, weak=(mode == "weak"))
         else:
             orc.dirichlet_flag_elimination(bs, dof_index, g, 1 if mode == "row" else 2, group, einfo, evalue)
     orc.dirichlet_apply(rows, cols, vals, einfo, evalue, finfo, fval, rhs)
@@ -235,6 +235,8 @@ def _dirichlet_case(mesh_name, bs, kind, mode):
     for dof_index, g in comps:
         if mode == "penalty":
             bsr.applyDirichletViaPenalty(dgroup, g, 1.0e30, dof_index)
+        elif mode == "weak":
+            bsr.applyDirichletViaWeakPenalty(dgroup, g, 1.0e8, dof_index)
         else:
             bsr.applyDirichletViaRowElimination(dgroup, g, dof_index, mode=1 if mode == "row" else 2)
     ls.applyDirichlet()
@@ -248,7 +250,7 @@ def _dirichlet_case(mesh_name, bs, kind, mode):
     return _np(bsr.matrix().values()), vals
 
 
-@pytest.mark.parametrize("mode", ["penalty", "row", "rowcol"])
+@pytest.mark.parametrize("mode", ["penalty", "weak", "row", "rowcol"])
 @pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("cube7_shuffled", 1, "laplace"), ("square9_shuffled", 1, "laplace"),
                                                 ("square9_shuffled", 2, "elasticity"), ("cube7_shuffled", 3, "elasticity")])
 def test_dirichlet_on_device(mesh_name, bs, kind, mode):
@@ -420,3 +422,17 @@ def test_fan_plan_visits_every_incident_cell_once(mesh_name):
             perm = [list(cells[cell]).index(v) for v in verts]
             inv = sum(1 for i in range(len(perm)) for j in range(i + 1, len(perm)) if perm[i] > perm[j])
             assert (inv & 1) == odd, f"row {row} cell {cell}"
+
+
+@pytest.mark.parametrize("mesh_name,bs", [("cube5", 1), ("square9_shuffled", 2), ("cube7_shuffled", 3)])
+def test_csr_global_numbering_on_device(mesh_name, bs):
+    """Device replacement of the host renumbering loops of femutils/HypreDoFLinearSystem.cc:474-519."""
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, 3)
+    csr = bsr.matrix().toCsr()
+    ndof = coords.shape[0] * bs
+    rng = np.random.default_rng(9)
+    numbering = (rng.permutation(ndof) + 1000).astype(np.int32)
+    rows, cols = bsr.csrGlobalNumbering(torch.as_tensor(numbering).cuda())
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(_np(rows), numbering)
+    np.testing.assert_array_equal(_np(cols), numbering[_np(csr.columns())])
