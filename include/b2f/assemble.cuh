@@ -568,6 +568,64 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
   return op.prepare_oriented(X, cell, odd);
 }
 
+#ifndef B2F_FAN_ASM_SMEM
+#define B2F_FAN_ASM_SMEM 1
+#endif
+// Shared-memory accessors on 32-bit shared-window addresses (B2F_FAN_ASM_SMEM): the walk keeps three byte addresses in
+// registers instead of re-deriving 64-bit generic pointers from the dynamic-smem base at every step.  The read-only arrays
+// (columns, step words) use plain asm (free to schedule); the accumulators use volatile asm, which keeps their loads and
+// stores in program order with respect to each other.
+struct SmemI32
+{
+  uint32_t a;
+  __device__ __forceinline__ int32_t operator[](int i) const
+  {
+    int32_t v;
+    asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a + 4u * (uint32_t)i));
+    return v;
+  }
+};
+struct SmemU32
+{
+  uint32_t a;
+  __device__ __forceinline__ uint32_t operator[](int i) const
+  {
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a + 4u * (uint32_t)i));
+    return v;
+  }
+};
+struct SmemF64
+{
+  uint32_t a;
+  __device__ __forceinline__ double ld(int i) const
+  {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a + 8u * (uint32_t)i));
+    return v;
+  }
+  __device__ __forceinline__ double operator[](int i) const { return ld(i); }
+  __device__ __forceinline__ void st(int i, double v) const { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a + 8u * (uint32_t)i), "d"(v)); }
+};
+template <int BS, bool PER_BLOCK>
+__device__ __forceinline__ void load_block(SmemF64 acc, int k, int x, double (&out)[BS * BS])
+{
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+#pragma unroll
+    for (int j = 0; j < BS; ++j)
+      out[i * BS + j] = acc.ld((int)value_index<BS, PER_BLOCK>(0, k, x, i, j));
+}
+template <int BS, bool PER_BLOCK>
+__device__ __forceinline__ void store_block(SmemF64 acc, int k, int x, const double (&v)[BS * BS])
+{
+#pragma unroll
+  for (int i = 0; i < BS; ++i)
+#pragma unroll
+    for (int j = 0; j < BS; ++j)
+      acc.st((int)value_index<BS, PER_BLOCK>(0, k, x, i, j), v[i * BS + j]);
+}
+
 template <int BS, bool PER_BLOCK>
 __device__ __forceinline__ void load_block(const double* __restrict__ acc, int k, int x, double (&out)[BS * BS])
 {
@@ -588,11 +646,14 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
       acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] = v[i * BS + j];
 }
 
+#ifndef B2F_FAN_UNIFORM_PIVOT
+#define B2F_FAN_UNIFORM_PIVOT 1
+#endif
 // One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
-template <class Op, bool PER_BLOCK, bool SKIP_DIAG>
-__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], double* __restrict__ acc, const int32_t* __restrict__ cols,
+template <class Op, bool PER_BLOCK, bool SKIP_DIAG, class AccT, class ColsT>
+__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
                                          int k, uint32_t wc, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
@@ -673,17 +734,30 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     for (int e = 0; e < BS2; ++e)
       leave[e] = dropN ? accN[e] : accO[e];
     store_block<BS, PER_BLOCK>(acc, k, dropN ? sN : sO, leave);
-    if (!dropN) {
-      sO = sN;
+#if B2F_FAN_UNIFORM_PIVOT
+    // Rows of a warp mostly change their pivot O at the same steps (identical link structure on structured meshes), so
+    // the pivot change sits behind a warp-uniform branch: when no lane changes, only the renaming m = h remains.
+    if (__any_sync(__activemask(), !dropN)) {
+#endif
+      if (!dropN) {
+        sO = sN;
 #pragma unroll
-      for (int e = 0; e < BS2; ++e)
-        accO[e] = accN[e];
-    }
+        for (int e = 0; e < BS2; ++e)
+          accO[e] = accN[e];
+      }
 #pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      eO[d] = dropN ? eO[d] : eN[d];
-      m[d] = dropN ? h[d] : T.g[2][d]; // new window (C, O'): eC x eO = h if O stays, eC x eN = g2 if N stays
+      for (int d = 0; d < 3; ++d) {
+        eO[d] = dropN ? eO[d] : eN[d];
+        m[d] = dropN ? h[d] : T.g[2][d]; // new window (C, O'): eC x eO = h if O stays, eC x eN = g2 if N stays
+      }
+#if B2F_FAN_UNIFORM_PIVOT
     }
+    else {
+#pragma unroll
+      for (int d = 0; d < 3; ++d)
+        m[d] = h[d];
+    }
+#endif
   }
   else {
     const auto G = tri_prepare(op, X0, eN, eC, cell, odd);
@@ -800,9 +874,18 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   __syncthreads();
 
   if (nstep > 0) {
+#if B2F_FAN_ASM_SMEM
+    SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) };
+    SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) };
+    SmemU32 st{ (uint32_t)__cvta_generic_to_shared(steps_s + (qb - abeg_al)) };
+    // the addresses become opaque here, after the barrier: the asm loads below depend on them and cannot be hoisted above
+    // the wait, and the compiler keeps them in registers instead of re-deriving them
+    asm volatile("" : "+r"(acc.a), "+r"(cols.a), "+r"(st.a)::"memory");
+#else
     double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
     const int32_t* cols = cols_s + (rb - vbeg_al);
     const uint32_t* st = steps_s + (qb - abeg_al);
+#endif
     const uint32_t* cl = A.fan_cell + qb;
     // bring the coordinates of every neighbour of the row towards the SM now, in one round trip, instead of meeting
     // the misses one by one along the walk
