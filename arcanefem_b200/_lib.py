@@ -58,6 +58,11 @@ class PlanView(C.Structure):
                 ("fan_ptr", C.c_void_p), ("fan_steps", C.c_void_p), ("fan_cell", C.c_void_p)]
 
 
+class IjView(C.Structure):
+    _fields_ = [("nb_row", C.c_int64), ("nb_value", C.c_int64), ("ncols", C.c_void_p), ("rows", C.c_void_p), ("row_local", C.c_void_p),
+                ("cols", C.c_void_p), ("values", C.c_void_p), ("rhs", C.c_void_p)]
+
+
 class Stats(C.Structure):
     _fields_ = [("nb_edge", C.c_int64), ("nb_col", C.c_int64), ("nb_nz", C.c_int64), ("columns_not_found", C.c_int64),
                 ("workspace_bytes", C.c_int64), ("resident_bytes", C.c_int64), ("gather_fallback_tiles", C.c_int64), ("fan_steps", C.c_int64)]
@@ -78,9 +83,11 @@ PROTOTYPES = {
     "b2f_compute_sparsity": (C.c_int, [_H, _S]),
     "b2f_release_workspace": (C.c_int, [_H]),
     "b2f_assemble": (C.c_int, [_H, _P(OperatorDesc), _S]),
+    "b2f_assemble_with_source": (C.c_int, [_H, _P(OperatorDesc), C.c_double, _S]),
     "b2f_reset_values": (C.c_int, [_H, _S]),
     "b2f_get_bsr": (C.c_int, [_H, _P(BsrView)]),
     "b2f_to_csr": (C.c_int, [_H, _P(CsrView), _S]),
+    "b2f_to_hypre_ij": (C.c_int, [_H, C.c_void_p, _P(IjView), _S]),
     "b2f_csr_global_numbering": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, _S]),
     "b2f_get_system": (C.c_int, [_H, _P(SystemView)]),
     "b2f_get_stats": (C.c_int, [_H, _P(Stats)]),

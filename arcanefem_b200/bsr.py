@@ -313,6 +313,11 @@ class BSRFormat:
         d = op.desc(accumulate)
         check(self._lib.b2f_assemble(self._h, C.byref(d), _stream()))
 
+    def assembleBilinearWithSource(self, op, qdot, accumulate=False):
+        """assembleBilinear + applyConstantSourceToRhs(qdot) in one pass over the mesh (b2f_assemble_with_source)."""
+        d = op.desc(accumulate)
+        check(self._lib.b2f_assemble_with_source(self._h, C.byref(d), float(qdot), _stream()))
+
     def assembleBilinearHost(self, op, coords_host, values_host=None):
         """Host-buffer entry point b2f_assemble_host (pinned tensors recommended)."""
         d = op.desc(False)
@@ -352,6 +357,19 @@ class BSRFormat:
         cols = torch.empty(int(v.nb_value), dtype=torch.int32, device="cuda")
         check(self._lib.b2f_csr_global_numbering(self._h, C.c_void_p(dof_number.data_ptr()), C.c_void_p(rows.data_ptr()), C.c_void_p(cols.data_ptr()), _stream()))
         return rows, cols
+
+    def toHypreIJ(self, dof_number=None):
+        """Own rows of the system as the device arrays HYPRE_IJMatrixSetValues / HYPRE_IJVectorSetValues take
+        (b2f_to_hypre_ij): dict(ncols, rows, row_local, cols, values, rhs) of tensor views."""
+        v = _lib.IjView()
+        num = C.c_void_p(dof_number.data_ptr()) if dof_number is not None else None
+        check(self._lib.b2f_to_hypre_ij(self._h, num, C.byref(v), _stream()))
+        nr, nv = int(v.nb_row), int(v.nb_value)
+        out = {"ncols": _as_tensor(v.ncols, nr, "<i4", self), "rows": _as_tensor(v.rows, nr, "<i4", self), "row_local": _as_tensor(v.row_local, nr, "<i4", self),
+               "cols": _as_tensor(v.cols, nv, "<i4", self), "values": _as_tensor(v.values, nv, "<f8", self)}
+        if v.rhs:
+            out["rhs"] = _as_tensor(v.rhs, nr, "<f8", self)
+        return out
 
     def plan(self):
         """Gather plan arrays as tensors (views; "<u4" words are exposed as int32 bit patterns)."""

@@ -150,6 +150,17 @@ int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream)
   return assemble(h, op, (cudaStream_t)stream);
 }
 
+int b2f_assemble_with_source(b2f_handle h, const b2f_operator* op, double qdot, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!op)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_with_source: null operator");
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_with_source: mesh coordinates are null");
+  return assemble(h, op, (cudaStream_t)stream, &qdot);
+}
+
 int b2f_reset_values(b2f_handle h, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
@@ -211,6 +222,15 @@ int b2f_csr_global_numbering(b2f_handle h, const int32_t* dof_number, int32_t* r
   if (!dof_number)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_csr_global_numbering: null numbering");
   return csr_global_numbering(h, dof_number, rows_global_out, cols_global_out, (cudaStream_t)stream);
+}
+
+int b2f_to_hypre_ij(b2f_handle h, const int32_t* dof_number, b2f_ij_view* out, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_to_hypre_ij: null output");
+  return to_hypre_ij(h, dof_number, out, (cudaStream_t)stream);
 }
 
 int b2f_get_system(b2f_handle h, b2f_system_view* out)

@@ -9,7 +9,7 @@ namespace b2f {
 
 namespace {
   template <class Op>
-  int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stream)
+  int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stream, const double* qdot)
   {
     AssembleArgs A;
     A.cell_node = h->mesh.cell_node;
@@ -36,12 +36,21 @@ namespace {
     int variant = h->variant;
     if (variant == B2F_ASM_DEFAULT)
       variant = B2F_ASM_NODE_GATHER;
+    // constant source fused into the walk (value per cell and node = qdot * measure / NV, ArcaneFemFunctionsGpu.h:402-429):
+    // the fan kernel sums 6*volume / 2*area, hence the factor 1/(6*4) / 1/(2*3)
+    const bool fused = qdot != nullptr && variant == B2F_ASM_NODE_GATHER && h->fan_ok && h->mesh.cell_is_own == nullptr;
+    if (fused) {
+      A.rhs = h->rhs.as<double>();
+      A.rhs_factor = *qdot / (Op::NV == 4 ? 24.0 : 6.0);
+    }
     B2F_CUDA(launch_assemble<Op>(A, op, variant, h->per_block, h->nb_nz, stream));
+    if (qdot != nullptr && !fused)
+      return rhs_constant_source(h, *qdot, stream);
     return B2F_OK;
   }
 } // namespace
 
-int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream)
+int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot)
 {
   const int nv = h->nv, bs = h->bs;
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, stream));
@@ -49,18 +58,18 @@ int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream)
   case B2F_OP_LAPLACE:
     if (bs != 1)
       return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_LAPLACE needs block_size 1 (got %d)", bs);
-    return nv == 3 ? run(h, LaplaceTri{}, op->accumulate, stream) : run(h, LaplaceTet{}, op->accumulate, stream);
+    return nv == 3 ? run(h, LaplaceTri{}, op->accumulate, stream, qdot) : run(h, LaplaceTet{}, op->accumulate, stream, qdot);
   case B2F_OP_ELASTICITY:
     if (nv == 3 && bs == 2)
-      return run(h, ElasticityTri{ op->lambda, op->mu2 }, op->accumulate, stream);
+      return run(h, ElasticityTri{ op->lambda, op->mu2 }, op->accumulate, stream, qdot);
     if (nv == 4 && bs == 3)
-      return run(h, ElasticityTet{ op->lambda, op->mu2 }, op->accumulate, stream);
+      return run(h, ElasticityTet{ op->lambda, op->mu2 }, op->accumulate, stream, qdot);
     return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_ELASTICITY needs block_size == dim (dim=%d, block_size=%d)", h->mesh.dim, bs);
   case B2F_OP_HEAT:
     if (bs != 1)
       return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_HEAT needs block_size 1 (got %d)", bs);
-    return nv == 3 ? run(h, HeatTri{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream)
-                   : run(h, HeatTet{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream);
+    return nv == 3 ? run(h, HeatTri{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream, qdot)
+                   : run(h, HeatTet{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream, qdot);
   default:
     return fail(B2F_ERR_NOT_IMPLEMENTED, "unknown operator kind %d", op->kind);
   }

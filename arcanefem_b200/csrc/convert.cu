@@ -5,6 +5,7 @@
 //   spmv   : y = A x on the BSR storage, both layouts (north-star's device check; no reference counterpart).
 #include "internal.h"
 #include "b2f/assemble.cuh"
+#include <cub/device/device_scan.cuh>
 
 namespace b2f {
 
@@ -122,6 +123,123 @@ int csr_global_numbering(b2f_context_s* h, const int32_t* dof_number, int32_t* r
   if (cols_global && nnz > 0)
     k_renumber<<<grid_for(nnz, 256), 256, 0, s>>>(cols, nnz, dof_number, nd, cols_global, err);
   B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
+// Own-row extraction for the solver hand-off.  HypreDoFLinearSystemImpl::solve() walks the own dofs on the host
+// (femutils/HypreDoFLinearSystem.cc:474-519): for each own row it records the global row id, the row length and the
+// global ids of its columns, then copies the four arrays to the device and calls
+// HYPRE_IJMatrixSetValues(ij_A, nb_local_row, ncols, rows, cols, values) (:587-609) and HYPRE_IJVectorSetValues for the
+// right-hand side (:617-640).  Here the same arrays are produced on the device: flag own rows, two exclusive scans (row
+// slot, value offset), one pass that copies rows in order (8 lanes per row).  Rows of ghost nodes are dropped.
+namespace {
+  __global__ void __launch_bounds__(256) k_ij_count(const uint8_t* __restrict__ node_is_own, const int32_t* __restrict__ nbcol, long long nb_row, int bs,
+                                                    int32_t* __restrict__ flag, int32_t* __restrict__ count)
+  {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nb_row)
+      return;
+    const bool own = node_is_own == nullptr || node_is_own[r / bs] != 0;
+    flag[r] = own ? 1 : 0;
+    count[r] = own ? nbcol[r] : 0;
+  }
+
+  __global__ void __launch_bounds__(256) k_ij_fill(const uint8_t* __restrict__ node_is_own, const int32_t* __restrict__ rows_ptr, const int32_t* __restrict__ nbcol,
+                                                   const int32_t* __restrict__ cols_local, const double* __restrict__ values, const double* __restrict__ rhs,
+                                                   const int32_t* __restrict__ numbering, long long nb_row, int bs, const int32_t* __restrict__ row_slot,
+                                                   const int32_t* __restrict__ value_off, int32_t* __restrict__ out_ncols, int32_t* __restrict__ out_rows,
+                                                   int32_t* __restrict__ out_row_local, int32_t* __restrict__ out_cols, double* __restrict__ out_values,
+                                                   double* __restrict__ out_rhs)
+  {
+    const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int l = threadIdx.x & 7;
+    if (r >= nb_row)
+      return;
+    if (node_is_own != nullptr && node_is_own[r / bs] == 0)
+      return;
+    const int k = nbcol[r];
+    const int32_t src = rows_ptr[r], dst = value_off[r];
+    if (l == 0) {
+      const int32_t i = row_slot[r];
+      out_ncols[i] = k;
+      out_rows[i] = numbering ? numbering[r] : (int32_t)r;
+      out_row_local[i] = (int32_t)r;
+      if (out_rhs)
+        out_rhs[i] = rhs[r];
+    }
+    for (int q = l; q < k; q += 8) {
+      const int32_t c = cols_local[src + q];
+      out_cols[dst + q] = numbering ? numbering[c] : c;
+      out_values[dst + q] = values[src + q];
+    }
+  }
+} // namespace
+
+namespace {
+  // in-place exclusive sum of n int32 values (cub; scratch from the handle's workspace)
+  int exclusive_scan_i32(b2f_context_s* h, int32_t* data, long long n, cudaStream_t s)
+  {
+    size_t tb = 0;
+    B2F_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, data, data, n, s));
+    B2F_CUDA(h->ws_tmp.alloc(tb));
+    B2F_CUDA(cub::DeviceScan::ExclusiveSum(h->ws_tmp.p, tb, data, data, n, s));
+    return B2F_OK;
+  }
+} // namespace
+
+int to_hypre_ij(b2f_context_s* h, const int32_t* dof_number, b2f_ij_view* out, cudaStream_t s)
+{
+  if (!h->has_csr) {
+    int rc = to_csr(h, s);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  const long long nd = h->nb_dof, nnz = h->nb_nz;
+  const int32_t* rows_ptr = h->bs == 1 ? h->row_index.as<int32_t>() : h->csr_rows.as<int32_t>();
+  const int32_t* nbcol = h->bs == 1 ? h->nb_nz_per_row.as<int32_t>() : h->csr_nbcol.as<int32_t>();
+  const int32_t* cols = h->bs == 1 ? h->columns.as<int32_t>() : h->csr_cols.as<int32_t>();
+  *out = b2f_ij_view{};
+  if (nd == 0)
+    return B2F_OK;
+  B2F_CUDA(h->ij_flag.alloc(sizeof(int32_t) * (size_t)(nd + 1)));
+  B2F_CUDA(h->ij_off.alloc(sizeof(int32_t) * (size_t)(nd + 1)));
+  int32_t* flag = h->ij_flag.as<int32_t>();
+  int32_t* off = h->ij_off.as<int32_t>();
+  // one extra zero entry so that the exclusive scans also deliver the totals
+  B2F_CUDA(cudaMemsetAsync(flag + nd, 0, sizeof(int32_t), s));
+  B2F_CUDA(cudaMemsetAsync(off + nd, 0, sizeof(int32_t), s));
+  k_ij_count<<<grid_for(nd, 256), 256, 0, s>>>(h->mesh.node_is_own, nbcol, nd, h->bs, flag, off);
+  B2F_CUDA(cudaGetLastError());
+  int rc = exclusive_scan_i32(h, flag, nd + 1, s);
+  if (rc != B2F_OK)
+    return rc;
+  rc = exclusive_scan_i32(h, off, nd + 1, s);
+  if (rc != B2F_OK)
+    return rc;
+  int32_t totals[2] = { 0, 0 };
+  B2F_CUDA(cudaMemcpyAsync(&totals[0], flag + nd, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  B2F_CUDA(cudaMemcpyAsync(&totals[1], off + nd, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  B2F_CUDA(cudaStreamSynchronize(s));
+  const long long nrow = totals[0], nval = totals[1];
+  B2F_CUDA(h->ij_ncols.alloc(sizeof(int32_t) * (size_t)nrow));
+  B2F_CUDA(h->ij_rows.alloc(sizeof(int32_t) * (size_t)nrow));
+  B2F_CUDA(h->ij_row_local.alloc(sizeof(int32_t) * (size_t)nrow));
+  B2F_CUDA(h->ij_cols.alloc(sizeof(int32_t) * (size_t)nval));
+  B2F_CUDA(h->ij_values.alloc(sizeof(double) * (size_t)nval));
+  B2F_CUDA(h->ij_rhs.alloc(sizeof(double) * (size_t)nrow));
+  k_ij_fill<<<grid_for(nd * 8, 256), 256, 0, s>>>(h->mesh.node_is_own, rows_ptr, nbcol, cols, h->values.as<double>(), h->rhs.as<double>(), dof_number, nd, h->bs, flag, off,
+                                                  h->ij_ncols.as<int32_t>(), h->ij_rows.as<int32_t>(), h->ij_row_local.as<int32_t>(), h->ij_cols.as<int32_t>(),
+                                                  h->ij_values.as<double>(), h->rhs.p ? h->ij_rhs.as<double>() : nullptr);
+  B2F_CUDA(cudaGetLastError());
+  (void)nnz;
+  out->nb_row = nrow;
+  out->nb_value = nval;
+  out->ncols = h->ij_ncols.as<int32_t>();
+  out->rows = h->ij_rows.as<int32_t>();
+  out->row_local = h->ij_row_local.as<int32_t>();
+  out->cols = h->ij_cols.as<int32_t>();
+  out->values = h->ij_values.as<double>();
+  out->rhs = h->rhs.p ? h->ij_rhs.as<double>() : nullptr;
   return B2F_OK;
 }
 

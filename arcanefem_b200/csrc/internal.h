@@ -85,6 +85,7 @@ struct b2f_context_s
   int64_t nb_pair = 0; // node/cell incidences of the assembled cells
   int tile_extents[6] = { 0, 0, 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then 64-row, then 32-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
+  b2f::DevBuf ij_flag, ij_off, ij_ncols, ij_rows, ij_row_local, ij_cols, ij_values, ij_rhs; // own-row arrays of b2f_to_hypre_ij
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
   b2f::DevBuf counters; // 8 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..6] tile extents)
   b2f::DevBuf ws_keys_a, ws_keys_b, ws_tmp, ws_i32a, ws_i64; // workspace
@@ -98,7 +99,7 @@ namespace b2f {
 // sparsity.cu
 int build_pattern(b2f_context_s* h, cudaStream_t stream);
 // assemble.cu
-int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream);
+int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot = nullptr); // qdot: fused constant source
 // boundary.cu
 int rhs_fill(b2f_context_s* h, double v, cudaStream_t s);
 int clear_values(b2f_context_s* h, cudaStream_t s);
@@ -110,6 +111,7 @@ int dirichlet_apply(b2f_context_s* h, cudaStream_t s);
 // convert.cu
 int to_csr(b2f_context_s* h, cudaStream_t s);
 int csr_global_numbering(b2f_context_s* h, const int32_t* dof_number, int32_t* rows_global, int32_t* cols_global, cudaStream_t s);
+int to_hypre_ij(b2f_context_s* h, const int32_t* dof_number, b2f_ij_view* out, cudaStream_t s);
 int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
 // ghost.cu
 int ghost_plan(b2f_context_s* h, void* comm, int rank, int world, const int32_t* node_owner, const int64_t* node_gid, cudaStream_t s);

@@ -143,6 +143,14 @@ class DoFLinearSystem
   void clearValues(b2f_stream stream = nullptr) { check(b2f_clear_values(handle(), stream)); } // HypreDoFLinearSystem.cc:184-191
   // prelude of HypreDoFLinearSystemImpl::solve(): _applyRowElimination() + _applyForcedValuesToLhs(), :319-382,:387-391
   void applyDirichlet(b2f_stream stream = nullptr) { check(b2f_dirichlet_apply(handle(), stream)); }
+  // Device-resident replacement of the host loops + copies in front of HYPRE_IJMatrixSetValues / HYPRE_IJVectorSetValues
+  // (HypreDoFLinearSystem.cc:474-519,587-640): own rows only, global ids from `dof_matrix_numbering` (device, may be null).
+  b2f_ij_view toHypreIJ(const Int32* dof_matrix_numbering = nullptr, b2f_stream stream = nullptr) const
+  {
+    b2f_ij_view v{};
+    check(b2f_to_hypre_ij(handle(), dof_matrix_numbering, &v, stream));
+    return v;
+  }
   b2f_handle handle() const
   {
     if (!m_h || !*m_h)
@@ -182,6 +190,9 @@ class BSRFormat
   }
   void computeSparsity() { check(b2f_compute_sparsity(m_h, m_stream)); } // BSRFormat.h:775-781
   void assembleBilinear(const Operator& op) { check(b2f_assemble(m_h, &op.desc, m_stream)); } // BSRFormat.h:1105-1111
+  // assembleBilinear + BoundaryConditions{2D,3D}::applyConstantSourceToRhs(qdot, ...) (ArcaneFemFunctionsGpu.h:605,695) fused:
+  // the source term is summed along the walk that forms the matrix rows.  Needs toLinearSystem() first (the rhs lives there).
+  void assembleBilinearWithSource(const Operator& op, Real qdot) { check(b2f_assemble_with_source(m_h, &op.desc, qdot, m_stream)); }
   // BSRFormat.h:414-430: hands the CSR view to the linear system (views stay valid until the next computeSparsity)
   void toLinearSystem(DoFLinearSystem& linear_system)
   {

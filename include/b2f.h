@@ -194,6 +194,12 @@ int b2f_release_workspace(b2f_handle h);
 
 /* assembleBilinear (BSRFormat.h:1105-1111). */
 int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream);
+/* assembleBilinear and BoundaryConditions{2D,3D}::applyConstantSourceToRhs (ArcaneFemFunctionsGpu.h:402-429,605,695) in
+ * one pass: rhs[dof(n,0)] += qdot * |cell| / Nv over the cells around every own node.  With the node-gather variant the
+ * cell measures are summed along the same walk that forms the matrix row (the determinant is already there): no atomics,
+ * no second sweep over the cells, bitwise reproducible.  Other variants (and the cell_is_own exchange mode, where a
+ * rank only walks its own cells) run b2f_assemble followed by b2f_rhs_constant_source. */
+int b2f_assemble_with_source(b2f_handle h, const b2f_operator* op, double qdot, b2f_stream stream);
 /* resetMatrixValues (BSRFormat.h:1120-1123). */
 int b2f_reset_values(b2f_handle h, b2f_stream stream);
 
@@ -207,6 +213,24 @@ int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream);
  * dof_number is the device array of the global matrix numbering of the local dofs (own: first_own_row + own index,
  * ghosts: the owner's number, :264-303).  Either output may be NULL. */
 int b2f_csr_global_numbering(b2f_handle h, const int32_t* dof_number, int32_t* rows_global_out, int32_t* cols_global_out, b2f_stream stream);
+/* The argument arrays of HYPRE_IJMatrixSetValues(ij_A, nb_row, ncols, rows, cols, values) and of
+ * HYPRE_IJVectorSetValues(ij_b, nb_row, rows, rhs) (femutils/HypreDoFLinearSystem.cc:587-640), device resident:
+ * only the rows of own nodes, in local order, with global row / column ids.  Borrowed; valid until the next
+ * b2f_to_hypre_ij / b2f_compute_sparsity / b2f_destroy. */
+typedef struct b2f_ij_view {
+  int64_t nb_row; /* own scalar rows */
+  int64_t nb_value; /* entries of those rows */
+  const int32_t* ncols; /* [nb_row] row lengths */
+  const int32_t* rows; /* [nb_row] global row ids (dof_number[row_local]) */
+  const int32_t* row_local; /* [nb_row] local dof of each row (to scatter the solution back) */
+  const int32_t* cols; /* [nb_value] global column ids */
+  const double* values; /* [nb_value] */
+  const double* rhs; /* [nb_row] right-hand side of the own rows */
+} b2f_ij_view;
+/* Own-row extraction + global numbering on the device (the reference loops over own dofs and entries on the host,
+ * HypreDoFLinearSystem.cc:474-519, then copies four arrays to the device, :587-599).  dof_number may be NULL (local ids
+ * are kept: single-rank runs).  Call after the Dirichlet treatment; synchronises `stream` once (two totals). */
+int b2f_to_hypre_ij(b2f_handle h, const int32_t* dof_number, b2f_ij_view* out, b2f_stream stream);
 int b2f_get_system(b2f_handle h, b2f_system_view* out);
 /* Device pointers of the gather plan built by b2f_compute_sparsity (read-only; for inspection and tests). */
 int b2f_get_plan(b2f_handle h, b2f_plan_view* out);

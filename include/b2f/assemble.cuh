@@ -45,6 +45,8 @@ struct AssembleArgs
   int tile_extents[6]; // largest tile of the plan: {blocks, steps or pairs} for 128-, 64- and 32-row tiles
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
+  double* rhs = nullptr; // fused constant source (fan kernel): rhs[row * BS] += rhs_factor * (sum of 6*volume / 2*area of the incident cells)
+  double rhs_factor = 0.0;
 };
 
 enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };
@@ -225,6 +227,33 @@ struct GatherCfg
   static constexpr int ADJ_CAP = ROWS * 40; // staged node->cell entries
   static constexpr size_t SMEM_BYTES = (size_t)ACC_BLOCKS * BS2 * sizeof(double) + (size_t)ACC_BLOCKS * sizeof(int32_t) + (size_t)ADJ_CAP * sizeof(uint32_t);
 };
+
+// Sum over the cells incident to `row` of 6*volume (tets) / 2*area (triangles, 3D cross product as computeAreaTria3):
+// the constant-source term of the rows that take the global fallback path of the fan kernel.
+template <int NV>
+__device__ __forceinline__ double row_measure(const AssembleArgs& A, long long row)
+{
+  double sum = 0.0;
+  for (int32_t q = __ldg(A.nc_ptr + row), qe = __ldg(A.nc_ptr + row + 1); q < qe; ++q) {
+    const long long cell = __ldg(A.nc_list + q) >> 2;
+    int32_t n[NV];
+    load_cell_nodes<NV>(A.cell_node, cell, n);
+    double X[NV][3];
+#pragma unroll
+    for (int b = 0; b < NV; ++b)
+      load_xyz(A.coords, n[b], X[b]);
+    const double ax = X[1][0] - X[0][0], ay = X[1][1] - X[0][1], az = X[1][2] - X[0][2];
+    const double bx = X[2][0] - X[0][0], by = X[2][1] - X[0][1], bz = X[2][2] - X[0][2];
+    const double cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+    if constexpr (NV == 3)
+      sum += sqrt(cx * cx + cy * cy + cz * cz);
+    else {
+      const double dx = X[NV - 1][0] - X[0][0], dy = X[NV - 1][1] - X[0][1], dz = X[NV - 1][2] - X[0][2];
+      sum += fabs(cx * dx + cy * dy + cz * dz);
+    }
+  }
+  return sum;
+}
 
 template <class Op, bool PER_BLOCK, bool SMEM>
 __device__ __forceinline__ void gather_rows(const AssembleArgs& A, const Op& op, long long row0, int nrows, int32_t vbeg, int32_t vend, int32_t abeg, int32_t aend,
@@ -652,11 +681,11 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 // One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
-template <class Op, bool PER_BLOCK, bool SKIP_DIAG, class AccT, class ColsT>
+template <class Op, bool PER_BLOCK, bool SKIP_DIAG, bool SRC, class AccT, class ColsT>
 __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
                                          int k, uint32_t wc, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
-                                         double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS])
+                                         double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure)
 {
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   sC = (int)(wc & 1023u);
@@ -708,6 +737,8 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     const double det = eC[0] * m[0] + eC[1] * m[1] + eC[2] * m[2];
     T.vol6 = fabs(det);
     T.s = fast_rcp(6.0 * T.vol6);
+    if constexpr (SRC)
+      measure += T.vol6; // 6 * volume of the incident cell (computeVolumeTetra4, ArcaneFemFunctionsGpu.h:110-122)
     const auto G = tet_finish(op, T, cell, odd);
     op.block(G, 0, 1, out);
 #pragma unroll
@@ -761,6 +792,13 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
   }
   else {
     const auto G = tri_prepare(op, X0, eN, eC, cell, odd);
+    if constexpr (SRC) {
+      // 2 * area with the 3D cross product of computeAreaTria3 (ArcaneFemFunctionsGpu.h:75-83; z takes part)
+      const double ax = eN[0] - X0[0], ay = eN[1] - X0[1], az = eN[2] - X0[2];
+      const double bx = eC[0] - X0[0], by = eC[1] - X0[1], bz = eC[2] - X0[2];
+      const double cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+      measure += sqrt(cx * cx + cy * cy + cz * cz);
+    }
     op.block(G, 0, 1, out);
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
@@ -796,7 +834,10 @@ struct FanCfg : SlotsCfg<Op>
 #endif
 // DIAG_BY_ROW_SUM (operators whose element matrices have zero row sums, BS = 1, overwrite mode): the diagonal entry is
 // not accumulated along the walk but formed at the end as minus the sum of the row's off-diagonal entries.
-template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM>
+// SRC: the constant-source right-hand side (applyConstantSourceToRhsBase, ArcaneFemFunctionsGpu.h:402-429) rides along:
+// the walk sums the measures of the incident cells and the row adds qdot * sum / (NV * NV!) to rhs[dof(row, 0)] with a
+// plain store, no atomics and no second pass over the cells.
+template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC>
 __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
 {
   using C = FanCfg<Op>;
@@ -820,6 +861,10 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     if (t == 0)
       atomicAdd(A.counters + 1, 1ull);
     gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, __ldg(A.nc_ptr + row0), __ldg(A.nc_ptr + row0 + nrows), nullptr, nullptr, nullptr);
+    if constexpr (SRC) {
+      if (t < nrows && (A.node_is_own == nullptr || A.node_is_own[row0 + t] != 0))
+        A.rhs[(row0 + t) * BS] += A.rhs_factor * row_measure<NV>(A, row0 + t);
+    }
     return;
   }
 
@@ -893,6 +938,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       prefetch_l2(A.coords + 3ll * cols[x]);
     double diag[BS2];
     load_block<BS, PER_BLOCK>(acc, k, 0, diag);
+    double measure = 0.0;
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
@@ -935,7 +981,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
@@ -947,7 +993,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
@@ -972,6 +1018,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       diag[0] = -sum;
     }
     store_block<BS, PER_BLOCK>(acc, k, 0, diag);
+    if constexpr (SRC)
+      A.rhs[row * BS] += A.rhs_factor * measure;
   }
 
   __syncthreads();
@@ -997,7 +1045,9 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
     using C = FanCfg<Op>;
     constexpr bool CAN_ROW_SUM = Op::ROW_SUM_ZERO && Op::BS == 1;
-    auto kern = (CAN_ROW_SUM && !A.accumulate) ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM> : k_node_fan<Op, PER_BLOCK, false>;
+    const bool row_sum = CAN_ROW_SUM && !A.accumulate;
+    auto kern = A.rhs ? (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, true> : k_node_fan<Op, PER_BLOCK, false, true>)
+                      : (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false> : k_node_fan<Op, PER_BLOCK, false, false>);
     if (B2F_FAN_CARVEOUT >= 0) {
       cudaError_t ec = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, B2F_FAN_CARVEOUT);
       if (ec != cudaSuccess)

@@ -198,6 +198,40 @@ def test_rhs_source_and_neumann(mesh_name):
     assert_vec_close(_np(ls.rhsVariable()), ref, what="rhs")
 
 
+@pytest.mark.parametrize("variant", [3, 1])
+@pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("cube7_shuffled", 1, "laplace"), ("cube7_shuffled", 1, "heat_cell"), ("cube4_mixed_orientation", 3, "elasticity"),
+                                                ("square9_shuffled", 1, "laplace"), ("square20", 2, "elasticity"), ("square7_mixed_orientation", 1, "heat_cell")])
+def test_fused_source_rhs(mesh_name, bs, kind, variant):
+    """b2f_assemble_with_source = assembleBilinear + applyConstantSourceToRhs: same matrix, same rhs as the two separate calls
+    (variant 3 sums the cell measures along the fan walk; variant 1 takes the two-kernel fallback)."""
+    from oracle import oracle as orc
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, variant)
+    nn = coords.shape[0]
+    params = op_params(kind, nb_cell=cells.shape[0])
+    cl = params.get("cell_lambda")
+    lam = torch.as_tensor(cl).cuda() if cl is not None else None
+    ref = np.zeros(nn * bs)
+    orc.rhs_constant_source(cells, coords, bs, 5.5, ref)
+    ls = _fem().DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    ls.clearValues()
+    bsr.assembleBilinear(_operator(kind, params, lam))
+    torch.cuda.synchronize()
+    v_plain = _np(bsr.matrix().values()).copy()
+    bsr.assembleBilinearWithSource(_operator(kind, params, lam), 5.5)
+    torch.cuda.synchronize()
+    if variant == 3:
+        assert np.array_equal(_np(bsr.matrix().values()), v_plain)
+    else:
+        assert_vec_close(_np(bsr.matrix().values()), v_plain, what="values")
+    assert_vec_close(_np(ls.rhsVariable()), ref, what="fused rhs")
+    # a second call adds the source again (rhs is +=, like the reference) and accumulate mode works too
+    bsr.assembleBilinearWithSource(_operator(kind, params, lam), 5.5, accumulate=True)
+    torch.cuda.synchronize()
+    assert_vec_close(_np(ls.rhsVariable()), 2 * ref, what="fused rhs twice")
+    assert_vec_close(_np(bsr.matrix().values()), 2 * v_plain, what="accumulated values")
+
+
 def _dirichlet_case(mesh_name, bs, kind, mode):
     """mode: 'penalty' | 'row' | 'rowcol' — returns (got values, got rhs, masks...) vs oracle."""
     from oracle import oracle as orc
@@ -371,6 +405,16 @@ def test_long_rows_take_the_global_fallback_path(K):
         assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant}")
         if variant == 3 and K >= 3000:
             assert bsr.stats()["gather_fallback_tiles"] >= 1
+        # fused constant source on the same paths (oversized tile: the source term comes from the node's cell list)
+        ls = fem.DoFLinearSystem()
+        bsr.toLinearSystem(ls)
+        ls.clearValues()
+        bsr.assembleBilinearWithSource(fem.Operator.laplace(), 5.5)
+        torch.cuda.synchronize()
+        rhs_ref = np.zeros(K + 1)
+        orc.rhs_constant_source(cells, coords, 1, 5.5, rhs_ref)
+        assert_vec_close(_np(ls.rhsVariable()), rhs_ref, what=f"fused rhs v{variant}")
+        assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant} with source")
 
 
 def emulate_fan_plan(cells, ri, co, plan):
@@ -436,3 +480,47 @@ def test_csr_global_numbering_on_device(mesh_name, bs):
     torch.cuda.synchronize()
     np.testing.assert_array_equal(_np(rows), numbering)
     np.testing.assert_array_equal(_np(cols), numbering[_np(csr.columns())])
+
+
+@pytest.mark.parametrize("with_ghosts", [False, True])
+@pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("cube7_shuffled", 1, "laplace"), ("square20", 2, "elasticity"), ("cube4_mixed_orientation", 3, "elasticity")])
+def test_hypre_ij_hand_off_on_device(mesh_name, bs, kind, with_ghosts):
+    """b2f_to_hypre_ij: the own rows of the CSR view with global ids, as HypreDoFLinearSystemImpl::solve() builds them on
+    the host (femutils/HypreDoFLinearSystem.cc:474-519, :587-640) — checked against a numpy walk over the own dofs."""
+    dim, cells, coords = MESHES[mesh_name]()
+    nn = coords.shape[0]
+    rng = np.random.default_rng(13)
+    own = (rng.uniform(size=nn) > 0.3).astype(np.uint8) if with_ghosts else None
+    bsr, m, dim, cells, coords = _setup(mesh_name, bs, True, 3, node_is_own=own)
+    params = op_params(kind, nb_cell=cells.shape[0])
+    ls = _fem().DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    ls.clearValues()
+    bsr.assembleBilinearWithSource(_operator(kind, params, None), 5.5)
+    torch.cuda.synchronize()
+    csr = bsr.matrix().toCsr()
+    rp, nbc, cl, va = _np(csr.rows()), _np(csr.rowsNbColumn()), _np(csr.columns()), _np(csr.values())
+    rhs = _np(ls.rhsVariable())
+    ndof = nn * bs
+    numbering = (rng.permutation(ndof) + 77).astype(np.int32)
+    for num in (None, numbering):
+        ij = bsr.toHypreIJ(torch.as_tensor(num).cuda() if num is not None else None)
+        torch.cuda.synchronize()
+        ident = num if num is not None else np.arange(ndof, dtype=np.int32)
+        e_ncols, e_rows, e_local, e_cols, e_vals, e_rhs = [], [], [], [], [], []
+        for r in range(ndof):
+            if own is not None and not own[r // bs]:
+                continue
+            e_ncols.append(nbc[r])
+            e_rows.append(ident[r])
+            e_local.append(r)
+            seg = slice(rp[r], rp[r] + nbc[r])
+            e_cols.extend(ident[cl[seg]])
+            e_vals.extend(va[seg])
+            e_rhs.append(rhs[r])
+        np.testing.assert_array_equal(_np(ij["ncols"]), np.array(e_ncols, dtype=np.int32))
+        np.testing.assert_array_equal(_np(ij["rows"]), np.array(e_rows, dtype=np.int32))
+        np.testing.assert_array_equal(_np(ij["row_local"]), np.array(e_local, dtype=np.int32))
+        np.testing.assert_array_equal(_np(ij["cols"]), np.array(e_cols, dtype=np.int32))
+        np.testing.assert_array_equal(_np(ij["values"]), np.array(e_vals))
+        np.testing.assert_array_equal(_np(ij["rhs"]), np.array(e_rhs))
