@@ -2,6 +2,7 @@
 #include <cstring>
 #include <fstream>
 #include "internal.h"
+#include <algorithm>
 
 namespace b2f {
 
@@ -40,6 +41,10 @@ using namespace b2f;
 #define B2F_NEED_PATTERN(h)                                        \
   if (!(h)->has_pattern)                                           \
   return fail(B2F_ERR_STATE, "%s: b2f_compute_sparsity has not been called", __func__)
+
+#ifndef B2F_HOST_PIPELINE_CHUNKS
+#define B2F_HOST_PIPELINE_CHUNKS 8
+#endif
 
 extern "C" {
 
@@ -86,6 +91,8 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node is null");
   if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
+  if (options->fan_mode < B2F_FAN_AUTO || options->fan_mode > B2F_FAN_LOCKSTEP)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown fan_mode %d", options->fan_mode);
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -108,9 +115,16 @@ int b2f_destroy(b2f_handle h)
     return B2F_OK;
   DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
-                     &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals };
+                     &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals,
+                     &h->ij_flag, &h->ij_off, &h->ij_ncols, &h->ij_rows, &h->ij_row_local, &h->ij_cols, &h->ij_values, &h->ij_rhs };
   for (DevBuf* b : bufs)
     b->release();
+  for (cudaEvent_t e : h->pipe_events)
+    cudaEventDestroy(e);
+  if (h->pipe_h2d)
+    cudaStreamDestroy(h->pipe_h2d);
+  if (h->pipe_d2h)
+    cudaStreamDestroy(h->pipe_d2h);
   delete h;
   return B2F_OK;
 }
@@ -275,6 +289,8 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   out->nb_col = h->nb_col;
   out->nb_nz = h->nb_nz;
   out->fan_steps = h->nb_fan_step;
+  out->fan_lockstep = h->fan_lockstep ? 1 : 0;
+  out->fan_lockstep_bodies_milli = (int64_t)(h->fan_lockstep_bodies * 1000.0 + 0.5);
   if (h->counters.p) {
     unsigned long long c[4] = { 0, 0, 0, 0 };
     B2F_CUDA(cudaMemcpy(c, h->counters.p, sizeof(c), cudaMemcpyDeviceToHost));
@@ -454,18 +470,85 @@ int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords
   if (!op || !coords_host)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_host: null argument");
   cudaStream_t s = (cudaStream_t)stream;
-  const size_t cbytes = sizeof(double) * 3 * (size_t)h->mesh.nb_node;
+  const long long nn = h->mesh.nb_node;
+  const size_t cbytes = sizeof(double) * 3 * (size_t)nn;
   B2F_CUDA(h->coords_stage.alloc(cbytes));
-  B2F_CUDA(cudaMemcpyAsync(h->coords_stage.p, coords_host, cbytes, cudaMemcpyHostToDevice, s));
+  const int variant = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
+  const bool pipelined = variant == B2F_ASM_NODE_GATHER && h->fan_ok && nn >= (1ll << 16);
+  if (!pipelined) {
+    B2F_CUDA(cudaMemcpyAsync(h->coords_stage.p, coords_host, cbytes, cudaMemcpyHostToDevice, s));
+    const double* saved = h->mesh.coords;
+    h->mesh.coords = h->coords_stage.as<double>();
+    int rc = assemble(h, op, s);
+    h->mesh.coords = saved;
+    if (rc != B2F_OK)
+      return rc;
+    if (values_host)
+      B2F_CUDA(cudaMemcpyAsync(values_host, h->values.p, sizeof(double) * (size_t)h->nb_nz, cudaMemcpyDeviceToHost, s));
+    B2F_CUDA(cudaStreamSynchronize(s));
+    return B2F_OK;
+  }
+  // Pipeline over row chunks: coordinates go up as a growing prefix on one copy stream, each chunk of rows is assembled
+  // as soon as the coordinates it reads have landed, and its values go back on a second copy stream while the next
+  // chunk is assembled and the next coordinates arrive (the link is full duplex).
+  if (h->chunk_row.empty()) {
+    int rc = pipeline_plan(h, B2F_HOST_PIPELINE_CHUNKS, s);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  const int nc = (int)h->chunk_row.size() - 1;
+  if (!h->pipe_h2d)
+    B2F_CUDA(cudaStreamCreateWithFlags(&h->pipe_h2d, cudaStreamNonBlocking));
+  if (!h->pipe_d2h)
+    B2F_CUDA(cudaStreamCreateWithFlags(&h->pipe_d2h, cudaStreamNonBlocking));
+  while ((int)h->pipe_events.size() < 2 * nc + 1) {
+    cudaEvent_t e;
+    B2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->pipe_events.push_back(e);
+  }
+  // work queued earlier on the caller's stream comes first
+  B2F_CUDA(cudaEventRecord(h->pipe_events[2 * nc], s));
+  B2F_CUDA(cudaStreamWaitEvent(h->pipe_h2d, h->pipe_events[2 * nc], 0));
+  B2F_CUDA(cudaStreamWaitEvent(h->pipe_d2h, h->pipe_events[2 * nc], 0));
   const double* saved = h->mesh.coords;
   h->mesh.coords = h->coords_stage.as<double>();
-  int rc = assemble(h, op, s);
+  long long pos = 0;
+  int rc = B2F_OK;
+  cudaError_t ce = cudaSuccess;
+  for (int c = 0; c < nc && rc == B2F_OK && ce == cudaSuccess; ++c) {
+    const long long need = (c == nc - 1) ? nn : std::min<long long>(nn, h->chunk_node_hi[c] + 1);
+    if (need > pos) {
+      ce = cudaMemcpyAsync(h->coords_stage.as<double>() + 3 * pos, coords_host + 3 * pos, sizeof(double) * 3 * (size_t)(need - pos), cudaMemcpyHostToDevice, h->pipe_h2d);
+      if (ce == cudaSuccess)
+        ce = cudaEventRecord(h->pipe_events[2 * c], h->pipe_h2d);
+      if (ce == cudaSuccess)
+        ce = cudaStreamWaitEvent(s, h->pipe_events[2 * c], 0);
+      pos = need;
+      if (ce != cudaSuccess)
+        break;
+    }
+    h->range_first_row = h->chunk_row[c];
+    h->range_rows = h->chunk_row[c + 1] - h->chunk_row[c];
+    rc = assemble(h, op, s);
+    if (rc == B2F_OK && values_host) {
+      const int64_t v0 = h->chunk_value_off[c], v1 = h->chunk_value_off[c + 1];
+      ce = cudaEventRecord(h->pipe_events[2 * c + 1], s);
+      if (ce == cudaSuccess)
+        ce = cudaStreamWaitEvent(h->pipe_d2h, h->pipe_events[2 * c + 1], 0);
+      if (ce == cudaSuccess && v1 > v0)
+        ce = cudaMemcpyAsync(values_host + v0, h->values.as<double>() + v0, sizeof(double) * (size_t)(v1 - v0), cudaMemcpyDeviceToHost, h->pipe_d2h);
+    }
+  }
+  h->range_rows = -1;
+  h->range_first_row = 0;
   h->mesh.coords = saved;
+  cudaError_t e1 = cudaStreamSynchronize(h->pipe_h2d), e2 = cudaStreamSynchronize(s), e3 = cudaStreamSynchronize(h->pipe_d2h);
   if (rc != B2F_OK)
     return rc;
-  if (values_host)
-    B2F_CUDA(cudaMemcpyAsync(values_host, h->values.p, sizeof(double) * (size_t)h->nb_nz, cudaMemcpyDeviceToHost, s));
-  B2F_CUDA(cudaStreamSynchronize(s));
+  B2F_CUDA(ce);
+  B2F_CUDA(e1);
+  B2F_CUDA(e2);
+  B2F_CUDA(e3);
   return B2F_OK;
 }
 

@@ -29,6 +29,7 @@ namespace {
     A.fan_steps = h->fan_steps.as<uint32_t>();
     A.fan_cell = h->fan_cell.as<uint32_t>();
     A.fan_ok = h->fan_ok ? 1 : 0;
+    A.fan_lockstep = h->fan_lockstep ? 1 : 0;
     for (int i = 0; i < 6; ++i)
       A.tile_extents[i] = h->tile_extents[i];
     A.counters = h->counters.as<unsigned long long>();
@@ -38,6 +39,10 @@ namespace {
       variant = B2F_ASM_NODE_GATHER;
     // constant source fused into the walk (value per cell and node = qdot * measure / NV, ArcaneFemFunctionsGpu.h:402-429):
     // the fan kernel sums 6*volume / 2*area, hence the factor 1/(6*4) / 1/(2*3)
+    if (h->range_rows >= 0) { // host pipeline: rows [range_first_row, range_first_row + range_rows), multiples of the tile height
+      A.first_tile = h->range_first_row / FanCfg<Op>::ROWS;
+      A.nb_tile = (h->range_rows + FanCfg<Op>::ROWS - 1) / FanCfg<Op>::ROWS;
+    }
     const bool fused = qdot != nullptr && variant == B2F_ASM_NODE_GATHER && h->fan_ok && h->mesh.cell_is_own == nullptr;
     if (fused) {
       A.rhs = h->rhs.as<double>();
@@ -53,7 +58,8 @@ namespace {
 int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot)
 {
   const int nv = h->nv, bs = h->bs;
-  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, stream));
+  if (h->range_rows < 0 || h->range_first_row == 0)
+    B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, stream));
   switch (op->kind) {
   case B2F_OP_LAPLACE:
     if (bs != 1)

@@ -6,6 +6,7 @@
 #include "internal.h"
 #include "b2f/assemble.cuh"
 #include <cub/device/device_scan.cuh>
+#include <algorithm>
 
 namespace b2f {
 
@@ -240,6 +241,60 @@ int to_hypre_ij(b2f_context_s* h, const int32_t* dof_number, b2f_ij_view* out, c
   out->cols = h->ij_cols.as<int32_t>();
   out->values = h->ij_values.as<double>();
   out->rhs = h->rhs.p ? h->ij_rhs.as<double>() : nullptr;
+  return B2F_OK;
+}
+
+// Row chunks of the host pipeline (b2f_assemble_host): chunk boundaries on multiples of 128 rows, the offset of each
+// boundary in the value array and, per chunk, the highest node id its rows read (= highest column; the diagonal makes the
+// row itself a column), made monotone so that "coordinates [0, hi]" is a growing prefix.
+namespace {
+  __global__ void __launch_bounds__(256) k_max_i32(const int32_t* __restrict__ v, long long n, int32_t* __restrict__ out)
+  {
+    int32_t m = -1;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+      m = max(m, v[i]);
+    for (int d = 16; d > 0; d >>= 1)
+      m = max(m, __shfl_xor_sync(0xffffffffu, m, d));
+    if ((threadIdx.x & 31) == 0 && m >= 0)
+      atomicMax(out, m);
+  }
+} // namespace
+
+int pipeline_plan(b2f_context_s* h, int nchunk, cudaStream_t s)
+{
+  const long long nn = h->mesh.nb_node;
+  const long long tiles = (nn + 127) / 128;
+  const long long per = (tiles + nchunk - 1) / nchunk;
+  h->chunk_row.clear();
+  for (long long c = 0; c * per < tiles; ++c)
+    h->chunk_row.push_back(c * per * 128);
+  h->chunk_row.push_back(nn);
+  const int nc = (int)h->chunk_row.size() - 1;
+  std::vector<int32_t> off(nc + 1);
+  for (int c = 0; c <= nc; ++c)
+    B2F_CUDA(cudaMemcpyAsync(&off[c], h->row_index.as<int32_t>() + h->chunk_row[c], sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  B2F_CUDA(cudaStreamSynchronize(s));
+  B2F_CUDA(h->ij_flag.alloc(sizeof(int32_t) * (size_t)(nc + 1)));
+  int32_t* hi_d = h->ij_flag.as<int32_t>();
+  B2F_CUDA(cudaMemsetAsync(hi_d, 0xff, sizeof(int32_t) * (size_t)nc, s));
+  for (int c = 0; c < nc; ++c) {
+    const long long n = (long long)off[c + 1] - off[c];
+    if (n > 0)
+      k_max_i32<<<(unsigned)std::min<long long>(1184, (n + 255) / 256), 256, 0, s>>>(h->columns.as<int32_t>() + off[c], n, hi_d + c);
+  }
+  B2F_CUDA(cudaGetLastError());
+  std::vector<int32_t> hi(nc);
+  B2F_CUDA(cudaMemcpyAsync(hi.data(), hi_d, sizeof(int32_t) * (size_t)nc, cudaMemcpyDeviceToHost, s));
+  B2F_CUDA(cudaStreamSynchronize(s));
+  h->chunk_value_off.assign(nc + 1, 0);
+  h->chunk_node_hi.assign(nc, 0);
+  int64_t run = -1;
+  for (int c = 0; c < nc; ++c) {
+    h->chunk_value_off[c] = (int64_t)off[c] * h->bs * h->bs;
+    run = std::max<int64_t>(run, hi[c]);
+    h->chunk_node_hi[c] = run;
+  }
+  h->chunk_value_off[nc] = (int64_t)off[nc] * h->bs * h->bs;
   return B2F_OK;
 }
 

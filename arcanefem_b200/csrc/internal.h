@@ -81,15 +81,22 @@ struct b2f_context_s
   bool slots_ok = false;
   b2f::DevBuf fan_ptr, fan_steps, fan_cell; // fan-walk plan of the default gather kernel (one word per step, cell id per step)
   bool fan_ok = false;
+  bool fan_lockstep = false; // step words converted to the lockstep form (sparsity.cu k_fan_lockstep)
+  double fan_lockstep_bodies = 0.0; // step bodies a warp would execute per warp step in the lockstep form (1 = rows in step)
   int64_t nb_fan_step = 0;
   int64_t nb_pair = 0; // node/cell incidences of the assembled cells
   int tile_extents[6] = { 0, 0, 0, 0, 0, 0 }; // largest gather tile: {blocks, adj} for 128-row tiles, then 64-row, then 32-row tiles
   b2f::DevBuf csr_rows, csr_nbcol, csr_cols; // BS > 1 CSR expansion
   b2f::DevBuf ij_flag, ij_off, ij_ncols, ij_rows, ij_row_local, ij_cols, ij_values, ij_rhs; // own-row arrays of b2f_to_hypre_ij
   b2f::DevBuf rhs, forced_info, forced_value, elim_info, elim_value; // linear-system state
-  b2f::DevBuf counters; // 8 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..6] tile extents)
+  b2f::DevBuf counters; // 12 x u64 ([0] not found, [1] fallback tiles, [2] bad cells, [3] flags, [4..6] tile extents, [8..9] lockstep cost)
   b2f::DevBuf ws_keys_a, ws_keys_b, ws_tmp, ws_i32a, ws_i64; // workspace
   b2f::DevBuf coords_stage; // b2f_assemble_host
+  // b2f_assemble_host pipeline: row chunks, the highest node id each chunk reads, value offsets at the chunk boundaries
+  int64_t range_first_row = 0, range_rows = -1; // >= 0 while a chunk of the pipeline is being launched
+  std::vector<int64_t> chunk_row, chunk_value_off, chunk_node_hi;
+  cudaStream_t pipe_h2d = nullptr, pipe_d2h = nullptr;
+  std::vector<cudaEvent_t> pipe_events;
   b2f::GhostPlan ghost;
   int64_t last_not_found = 0;
   int64_t last_fallback_tiles = 0;
@@ -112,6 +119,7 @@ int dirichlet_apply(b2f_context_s* h, cudaStream_t s);
 int to_csr(b2f_context_s* h, cudaStream_t s);
 int csr_global_numbering(b2f_context_s* h, const int32_t* dof_number, int32_t* rows_global, int32_t* cols_global, cudaStream_t s);
 int to_hypre_ij(b2f_context_s* h, const int32_t* dof_number, b2f_ij_view* out, cudaStream_t s);
+int pipeline_plan(b2f_context_s* h, int nchunk, cudaStream_t s);
 int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
 // ghost.cu
 int ghost_plan(b2f_context_s* h, void* comm, int rank, int world, const int32_t* node_owner, const int64_t* node_gid, cudaStream_t s);

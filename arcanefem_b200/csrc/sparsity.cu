@@ -542,6 +542,76 @@ namespace {
 
 } // namespace
 
+// ---------------------------------------------------------------------------------------------------
+// Lockstep form of the fan plan (tets).  k_build_fan writes step words for the select walk: window (N, O), bit 10 = N
+// leaves, bit 11 = parity of (row, N, O, C).  The lockstep walk of k_node_fan keeps the window in two of three fixed
+// register sets; its step word names the variant of the step body: bits 10-12 = 2 * f + ly, f = free set (receives C),
+// ly = set f+2 leaves (else f+1), bit 13 = parity of (row, set f+1, set f+2, C); START words gain bits 20-21 = free
+// set of the window they end (3 = none) and always load N into set 1, O into set 2 (free set 0).
+// One thread per row replays its words.  COUNT: nothing is written; per warp and step the number of distinct variants
+// among the rows still walking is added up (= step bodies the warp would execute), next to the number of warp steps.
+// ---------------------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_fan_lockstep(const int32_t* __restrict__ fan_ptr, long long nb_node, uint32_t* __restrict__ steps, unsigned long long* __restrict__ cost)
+{
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int32_t qb = 0, n = 0;
+  if (row < nb_node) {
+    qb = fan_ptr[row];
+    n = fan_ptr[row + 1] - qb;
+  }
+  int nmax = n;
+  if (COUNT) {
+    for (int d = 16; d > 0; d >>= 1)
+      nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, d));
+  }
+  int f = 3, setN = 1, setO = 2; // f = 3: no window yet
+  unsigned long long bodies = 0, wsteps = 0;
+  for (int p = 0; p < nmax; ++p) {
+    int code = 7; // not walking
+    if (p < n) {
+      const uint32_t w = steps[qb + p];
+      uint32_t out;
+      if (w & 0x80000000u) {
+        out = (w & 0x800fffffu) | ((uint32_t)f << 20);
+        f = 0;
+        setN = 1;
+        setO = 2;
+        code = 6;
+      }
+      else {
+        const int X = (f + 1) % 3, Y = (f + 2) % 3;
+        const bool dropN = (w >> 10) & 1u;
+        bool odd = (w >> 11) & 1u;
+        if (setN != X)
+          odd = !odd; // (row, X, Y, C) lists N and O the other way round
+        const int leaving = dropN ? setN : setO;
+        const int ly = (leaving == Y) ? 1 : 0;
+        code = 2 * f + ly;
+        out = (w & 1023u) | ((uint32_t)code << 10) | ((odd ? 1u : 0u) << 13);
+        const int stay = dropN ? setO : setN;
+        setN = f; // C
+        setO = stay;
+        f = leaving;
+      }
+      if (!COUNT)
+        steps[qb + p] = out;
+    }
+    if (COUNT) {
+      int distinct = 0;
+#pragma unroll
+      for (int c = 0; c < 7; ++c)
+        distinct += __any_sync(0xffffffffu, code == c) ? 1 : 0;
+      bodies += distinct;
+      wsteps += 1;
+    }
+  }
+  if (COUNT && (threadIdx.x & 31) == 0 && nmax > 0) {
+    atomicAdd(cost, bodies);
+    atomicAdd(cost + 1, wsteps);
+  }
+}
+
 int build_pattern(b2f_context_s* h, cudaStream_t stream)
 {
   const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
@@ -556,7 +626,8 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
 
   h->has_pattern = false;
   h->has_csr = false;
-  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 8));
+  h->chunk_row.clear();
+  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 12));
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
   unsigned long long* counters = h->counters.as<unsigned long long>();
 
@@ -693,6 +764,24 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
                                                                   h->fan_cell.as<uint32_t>(), counters);
     B2F_CUDA(cudaGetLastError());
     tile_ptr = h->fan_ptr.as<int32_t>();
+    // lockstep form of the step words, on request only (B2F_FAN_LOCKSTEP): measured slower than the select walk even
+    // where the rows of a warp walk in step (N=203 Kuhn cube: 1.07 bodies per warp step, 1.08 ms against 0.98 ms) -
+    // the six-way indirect branch and the moves of the carried product cost what the selects did
+    h->fan_lockstep = false;
+    h->fan_lockstep_bodies = 0.0;
+    if (nv == 4 && nb_step > 0 && h->opt.fan_mode == B2F_FAN_LOCKSTEP) {
+      unsigned long long* cost = counters + 8;
+      B2F_CUDA(cudaMemsetAsync(cost, 0, sizeof(unsigned long long) * 2, stream));
+      k_fan_lockstep<true><<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>(), cost);
+      B2F_CUDA(cudaGetLastError());
+      unsigned long long hc[2] = { 0, 0 };
+      B2F_CUDA(cudaMemcpyAsync(hc, cost, sizeof(hc), cudaMemcpyDeviceToHost, stream));
+      B2F_CUDA(cudaStreamSynchronize(stream));
+      h->fan_lockstep_bodies = hc[1] ? (double)hc[0] / (double)hc[1] : 0.0;
+      k_fan_lockstep<false><<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>(), nullptr);
+      B2F_CUDA(cudaGetLastError());
+      h->fan_lockstep = true;
+    }
   }
   {
     int* ext = reinterpret_cast<int*>(counters + 4);

@@ -122,7 +122,7 @@ def run_b200(args):
     nc, nn = cells.shape[0], coords.shape[0]
     mesh = Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"] if world > 1 else None)
     bsr = fem.BSRFormat(1)
-    bsr.initialize(mesh, True, assembly_variant=args.variant)
+    bsr.initialize(mesh, True, assembly_variant=args.variant, fan_mode=args.fan_mode)
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -222,6 +222,7 @@ def run_b200(args):
         return
 
     peak, peak_src = measured_peak()
+    stats = bsr.stats()
     b_alg = algorithmic_bytes(4, nc, nn, nnzb, 1)
     achieved = b_alg / (ms_step * 1e-3) / 1e9
     variant_names = {0: "node_gather_fan", 1: "cell_atomic", 2: "cell_atomic_warpagg", 3: "node_gather_fan", 4: "node_gather_slots"}
@@ -240,7 +241,9 @@ def run_b200(args):
                    "variant": variant_names.get(args.variant, str(args.variant)), "n_hex": n, "cells_per_gpu": nc, "nnz_per_gpu": nnz, "nnz_job": own_nnz,
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
                    "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
-                   "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum},
+                   "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
+                   "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
+                   "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": b_alg, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
                      "kernel": kernel_names.get(args.variant, "?"),
@@ -337,6 +340,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=203, help="hexes per side of the per-GPU cube (203 -> 50.2M tets)")
     ap.add_argument("--variant", type=int, default=3, help="1 cell atomic, 2 cell atomic warp-aggregated, 3 node gather")
+    ap.add_argument("--fan-mode", type=int, default=0, help="node gather walk on tets: 0 chosen from the plan, 1 select walk, 2 lockstep walk")
     ap.add_argument("--cpu-cells", type=int, default=50_192_562, help="cells of the bounded CPU sample")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -88,12 +88,18 @@ typedef struct b2f_mesh_view {
   const uint8_t* cell_is_own; /* [nb_cell] or NULL = every cell is assembled; 0 = ghost cell: pattern only (multi-GPU exchange mode) */
 } b2f_mesh_view;
 
+/* Walk of the node-gather kernel over the cells around a node (tets).  SELECT (what AUTO picks): one step body, the
+ * roles of the window vertices are chosen with selects.  LOCKSTEP (kept for A/B measurements): the step word names one
+ * of six select-free step bodies, reached through an indirect branch; rows of a warp in different bodies are serialised
+ * (stats.fan_lockstep_bodies_milli).  Measured slower than SELECT even on structured meshes, see DESIGN.md. */
+typedef enum b2f_fan_mode { B2F_FAN_AUTO = 0, B2F_FAN_SELECT = 1, B2F_FAN_LOCKSTEP = 2 } b2f_fan_mode;
+
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
 typedef struct b2f_options {
   int32_t block_size; /* NB_DOF: 1, 2 or 3 */
   int32_t use_csr; /* does_linear_system_use_csr: 1 -> B2F_LAYOUT_PER_ROW, 0 -> B2F_LAYOUT_PER_BLOCK */
   int32_t assembly_variant; /* b2f_assembly_variant; the reference's use_atomic_free=true maps to NODE_GATHER */
-  int32_t reserved;
+  int32_t fan_mode; /* b2f_fan_mode: walk of the node-gather kernel on tets (0 = chosen from the plan) */
 } b2f_options;
 
 typedef struct b2f_operator {
@@ -173,6 +179,8 @@ typedef struct b2f_stats {
   int64_t resident_bytes; /* device bytes owned by the handle, workspace excluded */
   int64_t gather_fallback_tiles; /* node-gather tiles that overflowed shared memory and ran on the global path */
   int64_t fan_steps; /* words of the fan-walk plan (incident node/cell pairs + chain starts) */
+  int64_t fan_lockstep; /* 1: the plan is in the lockstep form (b2f_fan_mode) */
+  int64_t fan_lockstep_bodies_milli; /* 1000 x step bodies per warp step the lockstep walk executes on this plan (1000 = rows in step) */
 } b2f_stats;
 
 int b2f_version(void);

@@ -17,6 +17,7 @@
 //                   value is written exactly once and no zero-fill pass is needed.
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <utility>
 #include <cuda_runtime.h>
 #include "element_ops.cuh"
@@ -45,6 +46,9 @@ struct AssembleArgs
   int tile_extents[6]; // largest tile of the plan: {blocks, steps or pairs} for 128-, 64- and 32-row tiles
   unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
   int accumulate;
+  int fan_lockstep = 0; // the step words are in the lockstep form (tets)
+  long long first_tile = 0; // fan kernel only: the launch covers the tiles [first_tile, first_tile + nb_tile) (host pipeline)
+  long long nb_tile = -1; // -1: every tile
   double* rhs = nullptr; // fused constant source (fan kernel): rhs[row * BS] += rhs_factor * (sum of 6*volume / 2*area of the incident cells)
   double rhs_factor = 0.0;
 };
@@ -837,7 +841,11 @@ struct FanCfg : SlotsCfg<Op>
 // SRC: the constant-source right-hand side (applyConstantSourceToRhsBase, ArcaneFemFunctionsGpu.h:402-429) rides along:
 // the walk sums the measures of the incident cells and the row adds qdot * sum / (NV * NV!) to rhs[dof(row, 0)] with a
 // plain store, no atomics and no second pass over the cells.
-template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC>
+// LOCKSTEP (tets): the walk runs on three fixed register sets and the step word names the variant of the step body to
+// run (which set receives the entering vertex, which of the other two leaves): no selects and no register moves, at the
+// price of one multi-way branch per step.  Rows of a warp that sit in different variants are serialised.  Opt-in
+// (B2F_FAN_LOCKSTEP, plan converted by k_fan_lockstep in sparsity.cu): on B200 it measured slower than the select walk.
+template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC, bool LOCKSTEP>
 __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
 {
   using C = FanCfg<Op>;
@@ -849,7 +857,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   uint32_t* steps_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
 
   const int t = threadIdx.x;
-  const long long row0 = (long long)blockIdx.x * C::ROWS;
+  const long long row0 = ((long long)blockIdx.x + A.first_tile) * C::ROWS;
   const long long left = A.nb_node - row0;
   const int nrows = left < C::ROWS ? (int)left : C::ROWS;
   const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
@@ -939,6 +947,155 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     double diag[BS2];
     load_block<BS, PER_BLOCK>(acc, k, 0, diag);
     double measure = 0.0;
+    if constexpr (LOCKSTEP) {
+      static_assert(!LOCKSTEP || NV == 4, "the lockstep walk is for tetrahedra");
+      // sets 0, 1, 2: edge vector from the row node, accumulator block, column slot.  m = e[f+1] x e[f+2] for the free set f.
+      double e[3][3], av[3][BS2], m[3] = { 0.0, 0.0, 0.0 };
+      int sl[3] = { 0, 0, 0 };
+      double Xn[3];
+      uint32_t w = st[0], wc = 0;
+      load_xyz(A.coords, cols[w & 1023u], Xn);
+      double cv = 0.0, cvn = 0.0;
+      uint32_t cidn = 0;
+      if constexpr (Op::NEEDS_CELL) {
+        cv = op.cell_value((long long)__ldg(cl));
+        if (nstep > 1)
+          cvn = op.cell_value((long long)__ldg(cl + 1));
+        if (nstep > 2)
+          cidn = __ldg(cl + 2);
+      }
+      bool more = false;
+      // F: set that receives the entering vertex C; X = F+1, Y = F+2 hold the window; LY: Y leaves (else X).
+      // Local vertices (0, 1, 2, 3) = (row, X, Y, C): g1 = eY x eC, g2 = eC x eX, g3 = eX x eY = m.
+      auto step = [&](auto Fc, auto LYc) {
+        constexpr int F = decltype(Fc)::value, X = (F + 1) % 3, Y = (F + 2) % 3;
+        constexpr bool LY = decltype(LYc)::value;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+          e[F][d] = Xn[d] - X0[d];
+        if (more)
+          load_xyz(A.coords, cols[w & 1023u], Xn);
+        sl[F] = (int)(wc & 1023u);
+        load_block<BS, PER_BLOCK>(acc, k, sl[F], av[F]);
+        const bool odd = (wc >> 13) & 1u;
+        TetGeom T;
+        T.g[1][0] = e[Y][1] * e[F][2] - e[Y][2] * e[F][1];
+        T.g[1][1] = e[Y][2] * e[F][0] - e[Y][0] * e[F][2];
+        T.g[1][2] = e[Y][0] * e[F][1] - e[Y][1] * e[F][0];
+        T.g[2][0] = e[F][1] * e[X][2] - e[F][2] * e[X][1];
+        T.g[2][1] = e[F][2] * e[X][0] - e[F][0] * e[X][2];
+        T.g[2][2] = e[F][0] * e[X][1] - e[F][1] * e[X][0];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          T.g[3][d] = m[d];
+          T.g[0][d] = -T.g[1][d] - T.g[2][d] - m[d];
+        }
+        const double det = e[F][0] * m[0] + e[F][1] * m[1] + e[F][2] * m[2];
+        T.vol6 = fabs(det);
+        T.s = fast_rcp(6.0 * T.vol6);
+        if constexpr (SRC)
+          measure += T.vol6;
+        const auto G = tet_finish(op, T, cv, odd);
+        double out[BS2];
+        op.block(G, 0, 1, out);
+#pragma unroll
+        for (int q = 0; q < BS2; ++q)
+          av[X][q] += out[q];
+        op.block(G, 0, 2, out);
+#pragma unroll
+        for (int q = 0; q < BS2; ++q)
+          av[Y][q] += out[q];
+        op.block(G, 0, 3, out);
+#pragma unroll
+        for (int q = 0; q < BS2; ++q)
+          av[F][q] += out[q];
+        if constexpr (!DIAG_BY_ROW_SUM) {
+          op.block(G, 0, 0, out);
+#pragma unroll
+          for (int q = 0; q < BS2; ++q)
+            diag[q] += out[q];
+        }
+        if constexpr (LY) {
+          store_block<BS, PER_BLOCK>(acc, k, sl[Y], av[Y]);
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            m[d] = T.g[2][d]; // next free set Y: e[Y+1] x e[Y+2] = eC x eX
+        }
+        else {
+          store_block<BS, PER_BLOCK>(acc, k, sl[X], av[X]);
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            m[d] = T.g[1][d]; // next free set X: e[X+1] x e[X+2] = eY x eC
+        }
+      };
+      using I0 = std::integral_constant<int, 0>;
+      using I1 = std::integral_constant<int, 1>;
+      using I2 = std::integral_constant<int, 2>;
+      for (int p = 0; p < nstep; ++p) {
+        wc = w;
+        more = p + 1 < nstep;
+        if (more)
+          w = st[p + 1];
+        if (wc & FAN_START) {
+          // bits 20-21: free set of the window that ends here (3: there is none); its two sets are flushed, then the new
+          // window goes to the sets 1 (the vertex that came through the prefetch) and 2, free set 0
+          const int fp = (int)((wc >> 20) & 3u);
+          if (fp != 3) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+              if (q != fp)
+                store_block<BS, PER_BLOCK>(acc, k, sl[q], av[q]);
+          }
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            e[1][d] = Xn[d] - X0[d];
+          sl[1] = (int)(wc & 1023u);
+          sl[2] = (int)((wc >> 10) & 1023u);
+          double XB[3];
+          load_xyz(A.coords, cols[sl[2]], XB);
+          if (more)
+            load_xyz(A.coords, cols[w & 1023u], Xn);
+          load_block<BS, PER_BLOCK>(acc, k, sl[1], av[1]);
+          load_block<BS, PER_BLOCK>(acc, k, sl[2], av[2]);
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            e[2][d] = XB[d] - X0[d];
+          m[0] = e[1][1] * e[2][2] - e[1][2] * e[2][1];
+          m[1] = e[1][2] * e[2][0] - e[1][0] * e[2][2];
+          m[2] = e[1][0] * e[2][1] - e[1][1] * e[2][0];
+        }
+        else {
+          switch ((wc >> 10) & 7u) {
+          case 0: step(I0{}, std::false_type{}); break;
+          case 1: step(I0{}, std::true_type{}); break;
+          case 2: step(I1{}, std::false_type{}); break;
+          case 3: step(I1{}, std::true_type{}); break;
+          case 4: step(I2{}, std::false_type{}); break;
+          default: step(I2{}, std::true_type{}); break;
+          }
+        }
+        if constexpr (Op::NEEDS_CELL) {
+          cv = cvn;
+          if (p + 2 < nstep)
+            cvn = op.cell_value((long long)cidn);
+          if (p + 3 < nstep)
+            cidn = __ldg(cl + p + 3);
+        }
+      }
+      // final window: every set but the free one of the last step
+      int fl;
+      if (wc & FAN_START)
+        fl = 0;
+      else {
+        const int code = (int)((wc >> 10) & 7u);
+        fl = ((code >> 1) + 1 + (code & 1)) % 3;
+      }
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        if (q != fl)
+          store_block<BS, PER_BLOCK>(acc, k, sl[q], av[q]);
+    }
+    else {
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
@@ -1011,6 +1168,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       if (sO)
         store_block<BS, PER_BLOCK>(acc, k, sO, accO);
     }
+    } // select walk
     if constexpr (DIAG_BY_ROW_SUM) {
       double sum = 0.0;
       for (int x = 1; x < k; ++x)
@@ -1046,8 +1204,12 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     using C = FanCfg<Op>;
     constexpr bool CAN_ROW_SUM = Op::ROW_SUM_ZERO && Op::BS == 1;
     const bool row_sum = CAN_ROW_SUM && !A.accumulate;
-    auto kern = A.rhs ? (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, true> : k_node_fan<Op, PER_BLOCK, false, true>)
-                      : (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false> : k_node_fan<Op, PER_BLOCK, false, false>);
+    constexpr bool LS = Op::NV == 4; // the lockstep walk exists for tets
+    const bool ls = LS && A.fan_lockstep;
+    auto kern = A.rhs ? (row_sum ? (ls ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, true, LS> : k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, true, false>)
+                                 : (ls ? k_node_fan<Op, PER_BLOCK, false, true, LS> : k_node_fan<Op, PER_BLOCK, false, true, false>))
+                      : (row_sum ? (ls ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false, LS> : k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false, false>)
+                                 : (ls ? k_node_fan<Op, PER_BLOCK, false, false, LS> : k_node_fan<Op, PER_BLOCK, false, false, false>));
     if (B2F_FAN_CARVEOUT >= 0) {
       cudaError_t ec = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, B2F_FAN_CARVEOUT);
       if (ec != cudaSuccess)
@@ -1063,11 +1225,16 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
       return e;
-    const long long grid = (A.nb_node + C::ROWS - 1) / C::ROWS;
+    const long long all = (A.nb_node + C::ROWS - 1) / C::ROWS;
+    long long grid = all - A.first_tile;
+    if (A.nb_tile >= 0 && A.nb_tile < grid)
+      grid = A.nb_tile;
     if (grid > 0)
       kern<<<(unsigned)grid, C::ROWS, smem, stream>>>(A, op, acc_blocks, step_cap);
     return cudaGetLastError();
   }
+  if (A.first_tile != 0 || A.nb_tile >= 0)
+    return cudaErrorInvalidValue; // only the fan kernel takes tile ranges
   if (variant == VARIANT_NODE_GATHER_SLOTS && A.slots_ok) {
     using C = SlotsCfg<Op>;
     auto kern = k_node_gather_slots<Op, PER_BLOCK>;

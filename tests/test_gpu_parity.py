@@ -19,13 +19,16 @@ def _fem():
     return fem
 
 
-def _setup(mesh_name, bs, use_csr, variant, node_is_own=None):
+def _setup(mesh_name, bs, use_csr, variant, node_is_own=None, fan_mode=0):
+    """variant: b2f_assembly_variant; 31 / 32 = node gather (3) with the select / lockstep walk forced (b2f_fan_mode)."""
     fem = _fem()
     from arcanefem_b200.bsr import Mesh
     dim, cells, coords = MESHES[mesh_name]()
     m = Mesh.from_numpy(dim, cells, coords, node_is_own)
     bsr = fem.BSRFormat(bs)
-    bsr.initialize(m, use_csr, assembly_variant=variant)
+    if variant in (31, 32):
+        variant, fan_mode = 3, variant - 30
+    bsr.initialize(m, use_csr, assembly_variant=variant, fan_mode=fan_mode)
     bsr.computeSparsity()
     return bsr, m, dim, cells, coords
 
@@ -34,7 +37,14 @@ def _np(t):
     return t.detach().cpu().numpy()
 
 
-VARIANTS = [1, 2, 3, 4]  # cell atomic, cell atomic warp-aggregated, node gather (fan walk), node gather (slot words)
+def _va(variant):
+    """initialize() keywords of a test variant id (31 / 32: node gather with the select / lockstep walk forced)."""
+    if variant in (31, 32):
+        return dict(assembly_variant=3, fan_mode=variant - 30)
+    return dict(assembly_variant=variant)
+
+
+VARIANTS = [1, 2, 3, 4, 31, 32]  # 31 / 32: node gather with the select / lockstep walk forced  # cell atomic, cell atomic warp-aggregated, node gather (fan walk), node gather (slot words)
 
 
 @pytest.mark.parametrize("mesh_name", sorted(MESHES))
@@ -198,7 +208,7 @@ def test_rhs_source_and_neumann(mesh_name):
     assert_vec_close(_np(ls.rhsVariable()), ref, what="rhs")
 
 
-@pytest.mark.parametrize("variant", [3, 1])
+@pytest.mark.parametrize("variant", [3, 31, 32, 1])
 @pytest.mark.parametrize("mesh_name,bs,kind", [("cube5", 1, "laplace"), ("cube7_shuffled", 1, "laplace"), ("cube7_shuffled", 1, "heat_cell"), ("cube4_mixed_orientation", 3, "elasticity"),
                                                 ("square9_shuffled", 1, "laplace"), ("square20", 2, "elasticity"), ("square7_mixed_orientation", 1, "heat_cell")])
 def test_fused_source_rhs(mesh_name, bs, kind, variant):
@@ -220,7 +230,7 @@ def test_fused_source_rhs(mesh_name, bs, kind, variant):
     v_plain = _np(bsr.matrix().values()).copy()
     bsr.assembleBilinearWithSource(_operator(kind, params, lam), 5.5)
     torch.cuda.synchronize()
-    if variant == 3:
+    if variant in (3, 31, 32):
         assert np.array_equal(_np(bsr.matrix().values()), v_plain)
     else:
         assert_vec_close(_np(bsr.matrix().values()), v_plain, what="values")
@@ -362,7 +372,7 @@ def test_medium_cube_parity(variant):
     cells, coords = gen.cube_kuhn(40)
     m = Mesh.from_numpy(3, cells, coords)
     bsr = fem.BSRFormat(1)
-    bsr.initialize(m, True, assembly_variant=variant)
+    bsr.initialize(m, True, **_va(variant))
     bsr.computeSparsity()
     ri, co = orc.build_pattern(cells, coords.shape[0])
     np.testing.assert_array_equal(_np(bsr.matrix().rowIndexWithEnd()), ri)
@@ -375,7 +385,11 @@ def test_medium_cube_parity(variant):
     assert_values_close(_np(bsr.matrix().values()), ref, ri, 1)
     st = bsr.stats()
     assert st["gather_fallback_tiles"] == 0
-    if variant == 3:
+    assert st["fan_lockstep"] == (1 if variant == 32 else 0)
+    if variant == 32:
+        # the rows of a structured mesh mostly walk in step: few step bodies per warp step
+        assert 1000 <= st["fan_lockstep_bodies_milli"] < 2000, st
+    if variant in (3, 31, 32):
         # fan plan: one chain start per row on this mesh (every node link is a disc or a sphere), so
         # steps = node/cell pairs + rows
         assert st["fan_steps"] == 4 * nc + nn
@@ -397,13 +411,13 @@ def test_long_rows_take_the_global_fallback_path(K):
     ref, _ = orc.assemble(cells, coords, ri, co)
     for variant in VARIANTS:
         bsr = fem.BSRFormat(1)
-        bsr.initialize(Mesh.from_numpy(2, cells, coords), True, assembly_variant=variant)
+        bsr.initialize(Mesh.from_numpy(2, cells, coords), True, **_va(variant))
         bsr.computeSparsity()
         np.testing.assert_array_equal(_np(bsr.matrix().columns()), co)
         bsr.assembleBilinear(fem.Operator.laplace())
         torch.cuda.synchronize()
         assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant}")
-        if variant == 3 and K >= 3000:
+        if variant in (3, 31, 32) and K >= 3000:
             assert bsr.stats()["gather_fallback_tiles"] >= 1
         # fused constant source on the same paths (oversized tile: the source term comes from the node's cell list)
         ls = fem.DoFLinearSystem()
@@ -417,8 +431,9 @@ def test_long_rows_take_the_global_fallback_path(K):
         assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant} with source")
 
 
-def emulate_fan_plan(cells, ri, co, plan):
-    """Replay the fan-walk plan on the host: returns, per row, the list of (cell, (row, N, O, C) node ids, odd) it emits."""
+def emulate_fan_plan(cells, ri, co, plan, lockstep=False):
+    """Replay the fan-walk plan on the host: returns, per row, the list of (cell, (row, N, O, C) node ids, odd) it emits
+    (lockstep form: (row, set f+1, set f+2, C))."""
     nv = cells.shape[1]
     fan_ptr = plan["fan_ptr"]
     steps = plan["fan_steps"].view(np.uint32)
@@ -428,8 +443,24 @@ def emulate_fan_plan(cells, ri, co, plan):
         cols = co[ri[row]:ri[row + 1]]
         n = o = None
         emitted = []
+        sets, free = [None, None, None], 3
         for q in range(fan_ptr[row], fan_ptr[row + 1]):
             w = int(steps[q])
+            if lockstep:
+                # three fixed sets; START: bits 20-21 = free set of the window that ends; N -> set 1, O -> set 2, free 0
+                if w & 0x80000000:
+                    assert ((w >> 20) & 3) == free, f"row {row}: START names free set {(w >> 20) & 3}, walk has {free}"
+                    sets, free = [None, int(cols[w & 1023]), int(cols[(w >> 10) & 1023])], 0
+                    continue
+                code = (w >> 10) & 7
+                assert code < 6 and code >> 1 == free, f"row {row}: step variant {code} with free set {free}"
+                x, y = (free + 1) % 3, (free + 2) % 3
+                c = int(cols[w & 1023])
+                emitted.append((int(fcell[q]), (row, sets[x], sets[y], c), (w >> 13) & 1))
+                sets[free] = c
+                free = y if code & 1 else x
+                sets[free] = None
+                continue
             if w & 0x80000000:
                 n = int(cols[w & 1023])
                 o = int(cols[(w >> 10) & 1023]) if nv == 4 else None
@@ -446,15 +477,18 @@ def emulate_fan_plan(cells, ri, co, plan):
     return out
 
 
+@pytest.mark.parametrize("fan_mode", [1, 2])
 @pytest.mark.parametrize("mesh_name", sorted(MESHES))
-def test_fan_plan_visits_every_incident_cell_once(mesh_name):
+def test_fan_plan_visits_every_incident_cell_once(mesh_name, fan_mode):
     """The plan is a cover of every node's incident cells by face-adjacent walks; the orientation bit is the parity of
-    the emitted vertex order relative to the cell's own."""
-    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3)
+    the emitted vertex order relative to the cell's own.  Both forms of the step words (select walk, lockstep walk)."""
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3, fan_mode=fan_mode)
     plan = {k: _np(v) for k, v in bsr.plan().items()}
     mat = bsr.matrix()
     ri, co = _np(mat.rowIndexWithEnd()), _np(mat.columns())
-    rows = emulate_fan_plan(cells, ri, co, plan)
+    st = bsr.stats()
+    assert st["fan_lockstep"] == (1 if fan_mode == 2 and cells.shape[1] == 4 else 0)
+    rows = emulate_fan_plan(cells, ri, co, plan, lockstep=bool(st["fan_lockstep"]))
     incident = [[] for _ in range(coords.shape[0])]
     for c, vs in enumerate(cells):
         for v in vs:
@@ -524,3 +558,51 @@ def test_hypre_ij_hand_off_on_device(mesh_name, bs, kind, with_ghosts):
         np.testing.assert_array_equal(_np(ij["cols"]), np.array(e_cols, dtype=np.int32))
         np.testing.assert_array_equal(_np(ij["values"]), np.array(e_vals))
         np.testing.assert_array_equal(_np(ij["rhs"]), np.array(e_rhs))
+
+
+@pytest.mark.parametrize("case", ["small", "structured", "shuffled", "heat_shuffled_cells"])
+def test_host_entry_point_matches_device_path(case):
+    """b2f_assemble_host (host coordinates in, host values out).  Small meshes take the one-shot path; from 65536 rows on
+    the call is pipelined over row chunks (coordinate prefix up, chunk assembled, chunk values down): same values either
+    way, also when the numbering has no locality and every chunk needs all coordinates."""
+    from oracle import oracle as orc
+    from arcanefem_b200 import mesh as gen
+    from arcanefem_b200.bsr import Mesh
+    fem = _fem()
+    if case == "small":
+        cells, coords = gen.cube_kuhn(6)
+    elif case == "structured":
+        cells, coords = gen.cube_kuhn(41)
+    elif case == "shuffled":
+        cells, coords = gen.cube_kuhn(41, shuffle_cells=42, shuffle_nodes=7)
+    else:
+        cells, coords = gen.cube_kuhn(41, shuffle_cells=5)
+    nn = coords.shape[0]
+    assert (nn >= 65536) == (case != "small")
+    if case == "heat_shuffled_cells":
+        lam = np.random.default_rng(3).uniform(0.5, 2.0, size=cells.shape[0])
+        params = dict(op=orc.OP_HEAT, lambda_=0.0, inv_dt=10.0, cell_lambda=lam)
+        dlam = torch.as_tensor(lam).cuda()
+        op = fem.Operator.heat(0.0, 0.1, cell_lambda=dlam)
+    else:
+        params, op = dict(op=orc.OP_LAPLACE), fem.Operator.laplace()
+    # the handle is created on a mesh whose device coordinates are garbage: the host entry point must use the host array
+    bsr = fem.BSRFormat(1)
+    bsr.initialize(Mesh.from_numpy(3, cells, np.full_like(coords, 1.0e9)), True, assembly_variant=3)
+    bsr.computeSparsity()
+    ri, co = orc.build_pattern(cells, nn)
+    ref, nf = orc.assemble(cells, coords, ri, co, bs=1, per_block=False, **params)
+    assert nf == 0
+    coords_host = torch.as_tensor(coords).pin_memory()
+    values_host = torch.full((ri[-1],), np.nan, dtype=torch.float64).pin_memory()
+    for rep in range(2):
+        values_host.fill_(float("nan"))
+        bsr.assembleBilinearHost(op, coords_host, values_host)
+        assert_values_close(values_host.numpy(), ref, ri, 1, what=f"{case} host values (call {rep})")
+        np.testing.assert_array_equal(_np(bsr.matrix().values()), values_host.numpy())
+    assert bsr.stats()["columns_not_found"] == 0
+    # no read-back requested: device values only
+    bsr.resetMatrixValues()
+    bsr.assembleBilinearHost(op, coords_host, None)
+    torch.cuda.synchronize()
+    assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, what=f"{case} device values")
