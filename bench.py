@@ -48,17 +48,38 @@ def measured_peak():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """Samples SM clocks / clock-event reasons while the timed region runs: NVML in-process, one poll per millisecond
+    (the timed region is about 10 ms), nvidia-smi at 100 ms as the fallback.  start() returns once sampling runs, so it
+    is called BEFORE the barrier that opens the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index=0):
         self.index = index
         self.rows = []
+        self.samples = []  # (sm_mhz, reason bit mask)
         self.proc = None
         self.thread = None
+        self.nvml = None
+        self.handle = None
+        self.sm_max = None
+        self.running = False
+        self.active = False  # only samples taken while `active` count
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.running = True
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -68,11 +89,32 @@ class ClockSampler:
         self.thread = threading.Thread(target=self._read, daemon=True)
         self.thread.start()
 
+    def _poll(self):
+        n = self.nvml
+        while self.running:
+            if self.active:
+                try:
+                    self.samples.append((float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)), int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))))
+                except Exception:
+                    pass
+            time.sleep(0.001)
+
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            if self.active:
+                self.rows.append(line.strip())
 
     def stop(self):
+        self.active = False
+        if self.nvml is not None:
+            self.running = False
+            self.thread.join(timeout=1)
+            n = self.nvml
+            bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": n.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksEventReasonSwPowerCap}
+            reasons = sorted(k for k, b in bits.items() if any(m & b for _, m in self.samples))
+            sm = [x for x, _ in self.samples]
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.sm_max, "reasons": reasons, "samples": len(sm), "source": "nvml, 1 ms polls inside the timed region"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -82,7 +124,6 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
@@ -92,10 +133,10 @@ class ClockSampler:
                 mx.append(float(f[1]))
             except ValueError:
                 continue
-            for name, val in zip(names, f[3:7]):
+            for name, val in zip(self.NAMES, f[3:7]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 def run_b200(args):
@@ -155,17 +196,21 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step()
     torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
+    # the sampler is started before the barrier: starting it takes milliseconds on rank 0 alone, and a rank that enters
+    # the timed loop late makes its neighbour's first exchange wait inside the neighbour's timed region
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    if dist is not None:
+        dist.barrier()
     torch.cuda.synchronize()
+    sampler.active = True
     ev0.record()
     for _ in range(args.steps):
         step()
     ev1.record()
     torch.cuda.synchronize()
+    sampler.active = False
     ms_total = ev0.elapsed_time(ev1)
     if dist is not None:
         t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
@@ -174,6 +219,23 @@ def run_b200(args):
         dist.barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
+
+    # where a multi-GPU step goes: assembly alone and exchange alone, same protocol (reported, not part of `value`)
+    breakdown = None
+    if exchange is not None:
+        parts = {}
+        for name, fn in (("assemble", lambda: bsr.assembleBilinear(op)), ("exchange", exchange.run)):
+            torch.cuda.synchronize()
+            dist.barrier()
+            ev0.record()
+            for _ in range(args.steps):
+                fn()
+            ev1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([ev0.elapsed_time(ev1) / args.steps], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            parts[name + "_ms"] = round(float(t.item()), 4)
+        breakdown = parts
 
     # nonzeros the whole job produced = rows owned by some rank (ghost copies are not counted twice)
     own_nnz = nnz
@@ -242,6 +304,7 @@ def run_b200(args):
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
                    "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
                    "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
+                   "step_breakdown": breakdown,
                    "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
                    "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,
