@@ -744,6 +744,15 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     if constexpr (SRC)
       measure += T.vol6; // 6 * volume of the incident cell (computeVolumeTetra4, ArcaneFemFunctionsGpu.h:110-122)
     const auto G = tet_finish(op, T, cell, odd);
+    if constexpr (Op::LINEAR_POST) {
+      // plain outer products (s*g0) (x) g_b; the operator's linear map is applied once per stored block at the end
+      double u[BS];
+      op.raw_begin(G, u);
+      op.raw_add(G, u, 1, accN);
+      op.raw_add(G, u, 2, accO);
+      op.raw_add(G, u, NV - 1, accC);
+    }
+    else {
     op.block(G, 0, 1, out);
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
@@ -756,6 +765,7 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
 #pragma unroll
     for (int e = 0; e < BS2; ++e)
       accC[e] += out[e];
+    }
     if constexpr (!SKIP_DIAG) {
       op.block(G, 0, 0, out);
 #pragma unroll
@@ -803,14 +813,22 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       const double cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
       measure += sqrt(cx * cx + cy * cy + cz * cz);
     }
-    op.block(G, 0, 1, out);
+    if constexpr (Op::LINEAR_POST) {
+      double u[BS];
+      op.raw_begin(G, u);
+      op.raw_add(G, u, 1, accN);
+      op.raw_add(G, u, 2, accC);
+    }
+    else {
+      op.block(G, 0, 1, out);
 #pragma unroll
-    for (int e = 0; e < BS2; ++e)
-      accN[e] += out[e];
-    op.block(G, 0, 2, out);
+      for (int e = 0; e < BS2; ++e)
+        accN[e] += out[e];
+      op.block(G, 0, 2, out);
 #pragma unroll
-    for (int e = 0; e < BS2; ++e)
-      accC[e] += out[e];
+      for (int e = 0; e < BS2; ++e)
+        accC[e] += out[e];
+    }
     if constexpr (!SKIP_DIAG) {
       op.block(G, 0, 0, out);
 #pragma unroll
@@ -850,6 +868,10 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
 {
   using C = FanCfg<Op>;
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
+  // POST (operators that are a linear map of plain outer-product sums, element_ops.cuh LINEAR_POST): the walk accumulates
+  // the outer products from zero, the diagonal block is minus the sum of the row's other blocks (gradients of a cell sum
+  // to zero), the map runs once per stored block after the walk, and accumulate mode adds the old values at the store.
+  constexpr bool POST = Op::LINEAR_POST;
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
   double* acc_s = reinterpret_cast<double*>(b2f_smem + 16);
@@ -887,7 +909,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       tma_load_1d(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
   }
   const int nval = (vend - vbeg) * BS2;
-  if (A.accumulate) {
+  if (A.accumulate && !POST) {
     for (int q = t; q < nval; q += C::ROWS)
       acc_s[q] = A.values[(long long)vbeg * BS2 + q];
   }
@@ -996,20 +1018,30 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         if constexpr (SRC)
           measure += T.vol6;
         const auto G = tet_finish(op, T, cv, odd);
-        double out[BS2];
-        op.block(G, 0, 1, out);
+        if constexpr (POST) {
+          double u[BS];
+          op.raw_begin(G, u);
+          op.raw_add(G, u, 1, av[X]);
+          op.raw_add(G, u, 2, av[Y]);
+          op.raw_add(G, u, 3, av[F]);
+        }
+        else {
+          double out[BS2];
+          op.block(G, 0, 1, out);
 #pragma unroll
-        for (int q = 0; q < BS2; ++q)
-          av[X][q] += out[q];
-        op.block(G, 0, 2, out);
+          for (int q = 0; q < BS2; ++q)
+            av[X][q] += out[q];
+          op.block(G, 0, 2, out);
 #pragma unroll
-        for (int q = 0; q < BS2; ++q)
-          av[Y][q] += out[q];
-        op.block(G, 0, 3, out);
+          for (int q = 0; q < BS2; ++q)
+            av[Y][q] += out[q];
+          op.block(G, 0, 3, out);
 #pragma unroll
-        for (int q = 0; q < BS2; ++q)
-          av[F][q] += out[q];
-        if constexpr (!DIAG_BY_ROW_SUM) {
+          for (int q = 0; q < BS2; ++q)
+            av[F][q] += out[q];
+        }
+        if constexpr (!DIAG_BY_ROW_SUM && !POST) {
+          double out[BS2];
           op.block(G, 0, 0, out);
 #pragma unroll
           for (int q = 0; q < BS2; ++q)
@@ -1138,7 +1170,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
@@ -1150,7 +1182,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         w = st[p + 1];
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
@@ -1169,7 +1201,22 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         store_block<BS, PER_BLOCK>(acc, k, sO, accO);
     }
     } // select walk
-    if constexpr (DIAG_BY_ROW_SUM) {
+    if constexpr (POST) {
+#pragma unroll
+      for (int q = 0; q < BS2; ++q)
+        diag[q] = 0.0;
+      for (int x = 1; x < k; ++x) {
+        double a[BS2];
+        load_block<BS, PER_BLOCK>(acc, k, x, a);
+#pragma unroll
+        for (int q = 0; q < BS2; ++q)
+          diag[q] -= a[q];
+        op.post(a);
+        store_block<BS, PER_BLOCK>(acc, k, x, a);
+      }
+      op.post(diag);
+    }
+    else if constexpr (DIAG_BY_ROW_SUM) {
       double sum = 0.0;
       for (int x = 1; x < k; ++x)
         sum += acc[x];
@@ -1183,15 +1230,24 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   __syncthreads();
   const long long base = (long long)vbeg * BS2;
   const int head = (int)(base & 1); // values is 16-byte aligned at element 0
+  const bool add_old = POST && A.accumulate;
   if (t < head && t < nval)
-    A.values[base + t] = acc_s[t];
+    A.values[base + t] = acc_s[t] + (add_old ? A.values[base + t] : 0.0);
   const int nvec = (nval - head) >> 1;
   double2* dst = reinterpret_cast<double2*>(A.values + base + head);
-  for (int q = t; q < nvec; q += C::ROWS)
-    dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+  if (add_old) {
+    for (int q = t; q < nvec; q += C::ROWS) {
+      const double2 o = dst[q];
+      dst[q] = make_double2(o.x + acc_s[head + 2 * q], o.y + acc_s[head + 2 * q + 1]);
+    }
+  }
+  else {
+    for (int q = t; q < nvec; q += C::ROWS)
+      dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+  }
   const int tail = head + 2 * nvec;
   if (t == 0 && tail < nval)
-    A.values[base + tail] = acc_s[tail];
+    A.values[base + tail] = acc_s[tail] + (add_old ? A.values[base + tail] : 0.0);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -38,6 +38,9 @@
 #ifndef B2F_FAN_WARPS
 #define B2F_FAN_WARPS 24
 #endif
+#ifndef B2F_FAN_WARPS_ELTET
+#define B2F_FAN_WARPS_ELTET 4
+#endif
 
 namespace b2f {
 
@@ -110,6 +113,7 @@ struct LaplaceTet
   static constexpr int FAN_WARPS_PER_SM = B2F_FAN_WARPS; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
+  static constexpr bool LINEAR_POST = false;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
   __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
@@ -126,6 +130,7 @@ struct LaplaceTri
   static constexpr int FAN_WARPS_PER_SM = B2F_FAN_WARPS; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = true; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
+  static constexpr bool LINEAR_POST = false;
   struct Geom
   {
     TriGeom t;
@@ -156,6 +161,7 @@ struct ElasticityTri
   static constexpr int FAN_WARPS_PER_SM = 16; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
+  static constexpr bool LINEAR_POST = true; // K = lambda*A + mu*A^T + mu*tr(A)*I with A = sum of s * n_a (x) n_b: see raw_add / post
   double lambda, mu2;
   struct Geom
   {
@@ -171,6 +177,32 @@ struct ElasticityTri
   }
   __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
   __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], double, bool) const { return prepare(X, 0); }
+  // The node-gather kernel accumulates the plain outer products A_(0,b) += (s*n_0) (x) n_b along its walk (4 FMAs per
+  // block instead of the full entries) and applies the material law once per stored block at the end: the law is linear
+  // in A.  mu = mu2 / 2: entry (0,0) = l*xx + mu2*xx + .5*mu2*yy = l*A00 + mu*A00 + mu*(A00 + A11).
+  __device__ __forceinline__ void raw_begin(const Geom& G, double (&u)[2]) const
+  {
+    u[0] = G.s * G.t.n[0][0];
+    u[1] = G.s * G.t.n[0][1];
+  }
+  __device__ __forceinline__ void raw_add(const Geom& G, const double (&u)[2], int b, double (&acc)[4]) const
+  {
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+        acc[i * 2 + j] = fma(u[i], G.t.n[b][j], acc[i * 2 + j]);
+  }
+  __device__ __forceinline__ void post(double (&A)[4]) const
+  {
+    const double mu = 0.5 * mu2, tr = mu * (A[0] + A[3]);
+    const double k00 = lambda * A[0] + mu * A[0] + tr, k01 = lambda * A[1] + mu * A[2];
+    const double k10 = lambda * A[2] + mu * A[1], k11 = lambda * A[3] + mu * A[3] + tr;
+    A[0] = k00;
+    A[1] = k01;
+    A[2] = k10;
+    A[3] = k11;
+  }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[4]) const
   {
     const double pxa = G.t.n[a][0], pya = G.t.n[a][1], pxb = G.t.n[b][0], pyb = G.t.n[b][1];
@@ -187,14 +219,47 @@ struct ElasticityTri
 struct ElasticityTet
 {
   static constexpr int NV = 4, BS = 3;
-  static constexpr int FAN_WARPS_PER_SM = 4; // occupancy the fan kernel is compiled for (register budget)
+  static constexpr int FAN_WARPS_PER_SM = B2F_FAN_WARPS_ELTET; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = false;
+  static constexpr bool LINEAR_POST = true; // K = lambda*A + mu*A^T + mu*tr(A)*I with A = sum of s * g_a (x) g_b: see raw_add / post
   double lambda, mu2;
   using Geom = TetGeom;
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long) const { return tet_geometry(X); }
   __device__ __forceinline__ double cell_value(long long) const { return 0.0; }
   __device__ __forceinline__ Geom finish(const TetGeom& T, double, bool) const { return T; }
+  // node-gather kernel: A_(0,b) += (s*g_0) (x) g_b along the walk (9 FMAs per block), material law once per stored block
+  __device__ __forceinline__ void raw_begin(const Geom& G, double (&u)[3]) const
+  {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+      u[i] = G.s * G.g[0][i];
+  }
+  __device__ __forceinline__ void raw_add(const Geom& G, const double (&u)[3], int b, double (&acc)[9]) const
+  {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        acc[i * 3 + j] = fma(u[i], G.g[b][j], acc[i * 3 + j]);
+  }
+  __device__ __forceinline__ void post(double (&A)[9]) const
+  {
+    const double mu = 0.5 * mu2, tr = mu * (A[0] + A[4] + A[8]);
+    double K[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        double v = lambda * A[i * 3 + j] + mu * A[j * 3 + i];
+        if (i == j)
+          v += tr;
+        K[i * 3 + j] = v;
+      }
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+      A[q] = K[q];
+  }
   __device__ __forceinline__ void block(const Geom& G, int a, int b, double (&out)[9]) const
   {
     const double mu = 0.5 * mu2;
@@ -219,6 +284,7 @@ struct HeatTri
   static constexpr int FAN_WARPS_PER_SM = 24; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true; // per-cell conductivity
+  static constexpr bool LINEAR_POST = false;
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
@@ -253,6 +319,7 @@ struct HeatTet
   static constexpr int FAN_WARPS_PER_SM = 20; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true;
+  static constexpr bool LINEAR_POST = false;
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
