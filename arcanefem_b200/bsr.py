@@ -282,7 +282,7 @@ class BSRFormat:
         except Exception:
             pass
 
-    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0):
+    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0, sparsity_build=0):
         if mesh is None:
             raise ValueError("BSRFormat(initialize): null mesh")  # ARCANE_CHECK_POINTER, BSRFormat.h:391
         if self._h.value:
@@ -304,6 +304,7 @@ class BSRFormat:
             assembly_variant = ASM_NODE_GATHER if use_atomic_free else ASM_DEFAULT
         opt.assembly_variant = int(assembly_variant)
         opt.fan_mode = int(fan_mode)  # b2f_fan_mode: 0 auto, 1 select walk, 2 lockstep walk
+        opt.sparsity_build = int(sparsity_build)  # b2f_sparsity_build: 0 auto, 1 global sort, 2 row-wise from the node->cell lists
         check(self._lib.b2f_create(C.byref(mv), C.byref(opt), C.byref(self._h)))
         self._mesh = mesh
 

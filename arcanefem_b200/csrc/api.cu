@@ -91,6 +91,8 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node is null");
   if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
+  if (options->sparsity_build < B2F_SPARSITY_AUTO || options->sparsity_build > B2F_SPARSITY_LISTS)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown sparsity_build %d", options->sparsity_build);
   if (options->fan_mode < B2F_FAN_AUTO || options->fan_mode > B2F_FAN_LOCKSTEP)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown fan_mode %d", options->fan_mode);
   int ndev = 0;
@@ -289,6 +291,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   out->nb_col = h->nb_col;
   out->nb_nz = h->nb_nz;
   out->fan_steps = h->nb_fan_step;
+  out->sparsity_by_lists = h->pattern_by_lists ? 1 : 0;
   out->fan_lockstep = h->fan_lockstep ? 1 : 0;
   out->fan_lockstep_bodies_milli = (int64_t)(h->fan_lockstep_bodies * 1000.0 + 0.5);
   if (h->counters.p) {

@@ -73,6 +73,7 @@ struct b2f_context_s
   int device = 0;
 
   bool has_pattern = false;
+  bool pattern_by_lists = false; // the pattern came from the row-wise build (no global sort)
   bool has_csr = false;
   int64_t nb_col = 0, nb_nz = 0, nb_edge = 0, nb_dof = 0;
 

@@ -612,25 +612,158 @@ __global__ void __launch_bounds__(128) k_fan_lockstep(const int32_t* __restrict_
   }
 }
 
-int build_pattern(b2f_context_s* h, cudaStream_t stream)
+namespace {
+  // Cells with a node id outside [0, nb_node): counted before anything indexes with them.
+  __global__ void __launch_bounds__(256) k_validate_cells(const int32_t* __restrict__ cell_node, long long n_entries, long long nb_node, unsigned long long* __restrict__ counters)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    bool bad = false;
+    if (i < n_entries) {
+      const int32_t v = cell_node[i];
+      bad = v < 0 || v >= nb_node;
+    }
+    if (__any_sync(0xffffffffu, bad)) {
+      const unsigned m = __ballot_sync(0xffffffffu, bad);
+      if ((threadIdx.x & 31) == 0)
+        atomicAdd(counters + 2, (unsigned long long)__popc(m));
+    }
+  }
+
+  // Row-wise pattern build: one thread per row walks the node's cell list and keeps the sorted set of the other vertices
+  // it meets (shared memory, one column of RU_CAP entries per thread; the cells of a list come in ascending cell order,
+  // so most insertions land at or near the end).  Pass 1 (WRITE = false) counts, pass 2 repeats the walk and writes the
+  // row: diagonal first, then ascending - the canonical order of the sort-based build, with no global sort.
+  // Same result as K1-K5 (femutils/BSRFormat.h:602-744): two nodes are neighbours iff they share a cell (P1 cells).
+  constexpr int RU_ROWS = 128, RU_CAP = 64;
+  template <int NV, bool WRITE>
+  __global__ void __launch_bounds__(RU_ROWS) k_row_unique(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list,
+                                                          long long nb_node, const int32_t* __restrict__ row_index, int32_t* __restrict__ deg,
+                                                          int32_t* __restrict__ columns, unsigned long long* __restrict__ counters)
+  {
+    __shared__ int32_t set[RU_CAP][RU_ROWS];
+    const int t = threadIdx.x;
+    const long long row = (long long)blockIdx.x * RU_ROWS + t;
+    if (row >= nb_node)
+      return;
+    int cnt = 0;
+    bool overflow = false;
+    const int32_t qe = nc_ptr[row + 1];
+    for (int32_t q = nc_ptr[row]; q < qe; ++q) {
+      const long long cell = __ldg(nc_list + q) >> 2;
+      int32_t n[NV];
+      if (NV == 4) {
+        const int4 v = __ldg(reinterpret_cast<const int4*>(cell_node) + cell);
+        n[0] = v.x;
+        n[1] = v.y;
+        n[2] = v.z;
+        n[NV - 1] = v.w;
+      }
+      else {
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          n[k] = __ldg(cell_node + cell * NV + k);
+      }
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int32_t c = n[k];
+        if (c == (int32_t)row)
+          continue;
+        int i = cnt;
+        while (i > 0 && set[i - 1][t] > c)
+          --i;
+        if (i > 0 && set[i - 1][t] == c)
+          continue;
+        if (cnt == RU_CAP) {
+          overflow = true;
+          continue;
+        }
+        for (int j = cnt; j > i; --j)
+          set[j][t] = set[j - 1][t];
+        set[i][t] = c;
+        ++cnt;
+      }
+    }
+    if (!WRITE) {
+      deg[row] = cnt + 1;
+      if (overflow)
+        atomicAdd(counters + 3, 1ull);
+    }
+    else {
+      const int32_t rb = row_index[row];
+      columns[rb] = (int32_t)row;
+      for (int i = 0; i < cnt; ++i)
+        columns[rb + 1 + i] = set[i][t];
+    }
+  }
+} // namespace
+
+// K1-K6 from the node->cell lists (built first): no edge keys, no global sort.  *fallback is set when a row has more than
+// RU_CAP neighbours: the caller then runs the sort-based build.
+static int pattern_from_lists(b2f_context_s* h, cudaStream_t stream, bool* fallback)
+{
+  const long long nn = h->mesh.nb_node;
+  const int nv = h->nv;
+  unsigned long long* counters = h->counters.as<unsigned long long>();
+  *fallback = false;
+  B2F_CUDA(cudaMemsetAsync(counters + 3, 0, sizeof(unsigned long long), stream));
+  B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  int32_t* deg = h->ws_i32a.as<int32_t>();
+  const int32_t* ncp = h->nc_ptr.as<int32_t>();
+  const uint32_t* ncl = h->nc_list.as<uint32_t>();
+  if (nn > 0) {
+    if (nv == 3)
+      k_row_unique<3, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters);
+    else
+      k_row_unique<4, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters);
+    B2F_CUDA(cudaGetLastError());
+  }
+  B2F_CUDA(h->row_index.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  long long nb_col = 0;
+  int rc = scan_counts(h, deg, nn, h->row_index.as<int32_t>(), &nb_col, stream);
+  if (rc != B2F_OK)
+    return rc;
+  unsigned long long long_rows = 0;
+  B2F_CUDA(cudaMemcpyAsync(&long_rows, counters + 3, sizeof(long_rows), cudaMemcpyDeviceToHost, stream));
+  B2F_CUDA(cudaStreamSynchronize(stream));
+  if (long_rows != 0) {
+    *fallback = true;
+    return B2F_OK;
+  }
+  const long long nb_nz = nb_col * h->bs * h->bs;
+  if (nb_nz > 2147483647ll)
+    return fail(B2F_ERR_OVERFLOW, "nb_non_zero_value=%lld does not fit the reference's Int32 (femutils/BSRFormat.h:402)", nb_nz);
+  h->nb_col = nb_col;
+  h->nb_nz = nb_nz;
+  h->nb_edge = (nb_col - nn) / 2;
+  B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
+  B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
+  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)nb_nz, stream)); // BSRMatrix::initialize fills 0, BSRFormat.h:136
+  if (nn > 0) {
+    if (nv == 3)
+      k_row_unique<3, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters);
+    else
+      k_row_unique<4, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters);
+    B2F_CUDA(cudaGetLastError());
+  }
+  B2F_CUDA(h->nb_nz_per_row.alloc(sizeof(int32_t) * (size_t)nn));
+  k_nz_per_row<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->nb_nz_per_row.as<int32_t>());
+  B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
+// K1-K6 by a global sort of the packed edge keys (the reference's algorithm, femutils/BSRFormat.h:583-770).  Used when
+// ghost cells take part in the pattern only (cell_is_own: the node->cell lists then miss them), on request
+// (b2f_options.sparsity_build) and when a row has more neighbours than the row-wise build holds.
+static int pattern_by_sort(b2f_context_s* h, cudaStream_t stream)
 {
   const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
   const int nv = h->nv;
   const int epe = (nv == 3) ? 3 : 6;
   const long long nkeys = nc * epe;
-  if (nc * 4 > 4294967295ll || nc * (long long)nv > 2147483647ll)
-    return fail(B2F_ERR_OVERFLOW, "nb_cell=%lld is too large for one rank (node->cell entries are 32-bit)", nc);
   int shift = 1;
   while ((1ll << shift) < nn)
     ++shift;
-
-  h->has_pattern = false;
-  h->has_csr = false;
-  h->chunk_row.clear();
-  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 12));
-  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
   unsigned long long* counters = h->counters.as<unsigned long long>();
-
   // --- K1: edge keys + radix sort over the 2*shift significant bits
   B2F_CUDA(h->ws_keys_a.alloc(sizeof(unsigned long long) * (size_t)nkeys));
   B2F_CUDA(h->ws_keys_b.alloc(sizeof(unsigned long long) * (size_t)nkeys));
@@ -695,11 +828,21 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   k_nz_per_row<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->nb_nz_per_row.as<int32_t>());
   B2F_CUDA(cudaGetLastError());
 
-  // --- node -> cell lists (the reference takes them from Arcane's nodeCell() connectivity, BSRFormat.h:942)
   B2F_CUDA(cudaStreamSynchronize(stream));
   h->ws_keys_a.release();
   h->ws_keys_b.release();
-  int32_t* cnt = deg;
+  return B2F_OK;
+}
+
+static int node_cell_lists(b2f_context_s* h, cudaStream_t stream)
+{
+  const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
+  const int nv = h->nv;
+  // --- node -> cell lists (the reference takes them from Arcane's nodeCell() connectivity, BSRFormat.h:942)
+  B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
+  int32_t* cnt = h->ws_i32a.as<int32_t>();
+  int32_t* cursor = cnt;
+  int rc = B2F_OK;
   B2F_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
   if (nc > 0)
     k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nv, nc * nv, cnt);
@@ -720,6 +863,66 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   }
   k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
   B2F_CUDA(cudaGetLastError());
+
+  return B2F_OK;
+}
+
+int build_pattern(b2f_context_s* h, cudaStream_t stream)
+{
+  const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
+  const int nv = h->nv;
+  if (nc * 4 > 4294967295ll || nc * (long long)nv > 2147483647ll)
+    return fail(B2F_ERR_OVERFLOW, "nb_cell=%lld is too large for one rank (node->cell entries are 32-bit)", nc);
+
+  h->has_pattern = false;
+  h->has_csr = false;
+  h->chunk_row.clear();
+  B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 12));
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
+  unsigned long long* counters = h->counters.as<unsigned long long>();
+  int rc = B2F_OK;
+
+  // node ids are checked before anything indexes with them
+  if (nc > 0) {
+    k_validate_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, nc * nv, nn, counters);
+    B2F_CUDA(cudaGetLastError());
+    unsigned long long bad = 0;
+    B2F_CUDA(cudaMemcpyAsync(&bad, counters + 2, sizeof(bad), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    if (bad != 0)
+      return fail(B2F_ERR_INVALID_ARGUMENT, "cell_node holds %llu node ids outside [0, nb_node)", bad);
+  }
+
+  // Pattern (K1-K6) and node -> cell lists.  Default: lists first, rows built from them (no global sort).  The sort-based
+  // build runs when ghost cells only take part in the pattern (the lists hold the assembled cells), on request, or when a
+  // row is too long for the row-wise kernel.
+  h->pattern_by_lists = false;
+  bool lists_first = h->mesh.cell_is_own == nullptr && h->opt.sparsity_build != B2F_SPARSITY_SORT;
+  if (lists_first) {
+    rc = node_cell_lists(h, stream);
+    if (rc != B2F_OK)
+      return rc;
+    bool fallback = false;
+    rc = pattern_from_lists(h, stream, &fallback);
+    if (rc != B2F_OK)
+      return rc;
+    if (fallback) {
+      rc = pattern_by_sort(h, stream);
+      if (rc != B2F_OK)
+        return rc;
+    }
+    else
+      h->pattern_by_lists = true;
+  }
+  else {
+    rc = pattern_by_sort(h, stream);
+    if (rc != B2F_OK)
+      return rc;
+    rc = node_cell_lists(h, stream);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  const long long nb_adj = h->nb_pair;
 
   // --- plan of the gather kernel: fan walk (default) or the column-slot words of the first-generation kernel
   const int32_t* tile_ptr = h->nc_ptr.as<int32_t>();

@@ -163,7 +163,7 @@ def run_b200(args):
     nc, nn = cells.shape[0], coords.shape[0]
     mesh = Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"] if world > 1 else None)
     bsr = fem.BSRFormat(1)
-    bsr.initialize(mesh, True, assembly_variant=args.variant, fan_mode=args.fan_mode)
+    bsr.initialize(mesh, True, assembly_variant=args.variant, fan_mode=args.fan_mode, sparsity_build=args.sparsity_build)
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -303,7 +303,7 @@ def run_b200(args):
                    "variant": variant_names.get(args.variant, str(args.variant)), "n_hex": n, "cells_per_gpu": nc, "nnz_per_gpu": nnz, "nnz_job": own_nnz,
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
                    "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
-                   "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
+                   "sparsity_build": "row-wise from node->cell lists" if stats["sparsity_by_lists"] else "global edge sort", "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
                    "step_breakdown": breakdown,
                    "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
                    "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
@@ -404,6 +404,7 @@ def main():
     ap.add_argument("--n", type=int, default=203, help="hexes per side of the per-GPU cube (203 -> 50.2M tets)")
     ap.add_argument("--variant", type=int, default=3, help="1 cell atomic, 2 cell atomic warp-aggregated, 3 node gather")
     ap.add_argument("--fan-mode", type=int, default=0, help="node gather walk on tets: 0 chosen from the plan, 1 select walk, 2 lockstep walk")
+    ap.add_argument("--sparsity-build", type=int, default=0, help="0 default (row-wise from the node->cell lists), 1 global edge sort (the reference's algorithm)")
     ap.add_argument("--cpu-cells", type=int, default=50_192_562, help="cells of the bounded CPU sample")
     args = ap.parse_args()
     if args.impl == "reference":

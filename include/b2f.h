@@ -94,12 +94,20 @@ typedef struct b2f_mesh_view {
  * (stats.fan_lockstep_bodies_milli).  Measured slower than SELECT even on structured meshes, see DESIGN.md. */
 typedef enum b2f_fan_mode { B2F_FAN_AUTO = 0, B2F_FAN_SELECT = 1, B2F_FAN_LOCKSTEP = 2 } b2f_fan_mode;
 
+/* How b2f_compute_sparsity forms the pattern.  SORT: the reference's algorithm (femutils/BSRFormat.h:602-744): cell -> edge
+ * keys, global radix sort, run ends, degree scan, column fill.  LISTS: node -> cell lists first, then every row gathers
+ * the vertices of its cells into a sorted set - no edge keys and no global sort, same pattern bit for bit.  AUTO = LISTS,
+ * except in the cell_is_own exchange mode and for rows with more than 64 neighbours, which take SORT. */
+typedef enum b2f_sparsity_build { B2F_SPARSITY_AUTO = 0, B2F_SPARSITY_SORT = 1, B2F_SPARSITY_LISTS = 2 } b2f_sparsity_build;
+
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
 typedef struct b2f_options {
   int32_t block_size; /* NB_DOF: 1, 2 or 3 */
   int32_t use_csr; /* does_linear_system_use_csr: 1 -> B2F_LAYOUT_PER_ROW, 0 -> B2F_LAYOUT_PER_BLOCK */
   int32_t assembly_variant; /* b2f_assembly_variant; the reference's use_atomic_free=true maps to NODE_GATHER */
   int32_t fan_mode; /* b2f_fan_mode: walk of the node-gather kernel on tets (0 = chosen from the plan) */
+  int32_t sparsity_build; /* b2f_sparsity_build */
+  int32_t reserved;
 } b2f_options;
 
 typedef struct b2f_operator {
@@ -179,6 +187,7 @@ typedef struct b2f_stats {
   int64_t resident_bytes; /* device bytes owned by the handle, workspace excluded */
   int64_t gather_fallback_tiles; /* node-gather tiles that overflowed shared memory and ran on the global path */
   int64_t fan_steps; /* words of the fan-walk plan (incident node/cell pairs + chain starts) */
+  int64_t sparsity_by_lists; /* 1: the pattern came from the row-wise build (b2f_sparsity_build) */
   int64_t fan_lockstep; /* 1: the plan is in the lockstep form (b2f_fan_mode) */
   int64_t fan_lockstep_bodies_milli; /* 1000 x step bodies per warp step the lockstep walk executes on this plan (1000 = rows in step) */
 } b2f_stats;

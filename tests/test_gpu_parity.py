@@ -19,7 +19,7 @@ def _fem():
     return fem
 
 
-def _setup(mesh_name, bs, use_csr, variant, node_is_own=None, fan_mode=0):
+def _setup(mesh_name, bs, use_csr, variant, node_is_own=None, fan_mode=0, sparsity_build=0):
     """variant: b2f_assembly_variant; 31 / 32 = node gather (3) with the select / lockstep walk forced (b2f_fan_mode)."""
     fem = _fem()
     from arcanefem_b200.bsr import Mesh
@@ -28,7 +28,7 @@ def _setup(mesh_name, bs, use_csr, variant, node_is_own=None, fan_mode=0):
     bsr = fem.BSRFormat(bs)
     if variant in (31, 32):
         variant, fan_mode = 3, variant - 30
-    bsr.initialize(m, use_csr, assembly_variant=variant, fan_mode=fan_mode)
+    bsr.initialize(m, use_csr, assembly_variant=variant, fan_mode=fan_mode, sparsity_build=sparsity_build)
     bsr.computeSparsity()
     return bsr, m, dim, cells, coords
 
@@ -47,10 +47,14 @@ def _va(variant):
 VARIANTS = [1, 2, 3, 4, 31, 32]  # 31 / 32: node gather with the select / lockstep walk forced  # cell atomic, cell atomic warp-aggregated, node gather (fan walk), node gather (slot words)
 
 
+@pytest.mark.parametrize("sparsity_build", [0, 1, 2])
 @pytest.mark.parametrize("mesh_name", sorted(MESHES))
-def test_sparsity_pattern_bit_exact(mesh_name):
+def test_sparsity_pattern_bit_exact(mesh_name, sparsity_build):
+    """Both builds (1: the reference's global edge sort; 2: row-wise from the node->cell lists, the default) give the
+    oracle's pattern bit for bit."""
     from oracle import oracle as orc
-    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3)
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3, sparsity_build=sparsity_build)
+    assert bsr.stats()["sparsity_by_lists"] == (0 if sparsity_build == 1 else 1)
     ri, co = orc.build_pattern(cells, coords.shape[0])
     mat = bsr.matrix()
     assert mat.nbRow() == coords.shape[0]
@@ -379,6 +383,7 @@ def test_medium_cube_parity(variant):
     np.testing.assert_array_equal(_np(bsr.matrix().columns()), co)
     nc, nn, e, nnzb = gen.kuhn_counts(40)
     assert bsr.matrix().nbEdge() == e and bsr.matrix().nbCol() == nnzb
+    assert bsr.stats()["sparsity_by_lists"] == 1
     ref, _ = orc.assemble(cells, coords, ri, co)
     bsr.assembleBilinear(fem.Operator.laplace())
     torch.cuda.synchronize()
@@ -414,6 +419,8 @@ def test_long_rows_take_the_global_fallback_path(K):
         bsr.initialize(Mesh.from_numpy(2, cells, coords), True, **_va(variant))
         bsr.computeSparsity()
         np.testing.assert_array_equal(_np(bsr.matrix().columns()), co)
+        # the hub row has K neighbours: more than the row-wise build holds, the sort-based build takes over
+        assert bsr.stats()["sparsity_by_lists"] == 0
         bsr.assembleBilinear(fem.Operator.laplace())
         torch.cuda.synchronize()
         assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, rtol=1e-11, what=f"fan v{variant}")
