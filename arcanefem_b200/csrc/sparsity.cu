@@ -356,6 +356,25 @@ namespace {
         nb[i][f] = -1;
       }
     }
+    if (k <= 64) {
+      // the cell across the face of i that omits vertex f holds all the other vertices of i: intersect, per other vertex,
+      // the set of cells (bit mask) that contain it.  O(m) instead of the pairwise comparison below.
+      unsigned long long with[64];
+      for (int x = 0; x < k; ++x)
+        with[x] = 0ull;
+      for (int i = 0; i < m; ++i)
+        for (int f = 0; f < NO; ++f)
+          with[v[i][f]] |= 1ull << i;
+      for (int i = 0; i < m; ++i)
+        for (int f = 0; f < NO; ++f) {
+          unsigned long long mk = ~(1ull << i);
+          for (int g = 0; g < NO; ++g)
+            if (g != f)
+              mk &= with[v[i][g]];
+          nb[i][f] = mk ? (int8_t)(__ffsll((long long)mk) - 1) : (int8_t)-1;
+        }
+    }
+    else
     for (int i = 0; i < m; ++i)
       for (int j = i + 1; j < m; ++j) {
         int common = 0, fi = -1, fj = -1; // fi: the vertex of i not shared, fj: same for j
