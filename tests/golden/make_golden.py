@@ -45,6 +45,32 @@ CASES = {
     # modules/testlab/inputs/Test.L-shape.3D.arc
     "testlab_Lshape_3D": dict(mesh="L-shape-3D", result="modules/testlab/tests/poisson_test_ref_L-shape_3D.txt", f=5.5,
                               dirichlet=[("bot", 50.0), ("bc", 10.0)], penalty=1.0e30, eps=1.0e-4),
+    # modules/laplace/inputs/L-shape.3D.bsr.arc (Laplace = no source; penalty default of femutils/FemBoundaryConditions.axl:67)
+    "laplace_Lshape_3D": dict(mesh="L-shape-3D", result="modules/laplace/check/test_3D_L-shape.txt", f=0.0,
+                              dirichlet=[("bot", 50.0), ("bc", 10.0)], penalty=1.0e30, eps=1.0e-4),
+    # modules/laplace/inputs/PointDirichlet.bsr.hypreDirect.arc
+    "laplace_point_dirichlet_2D": dict(mesh="plancher", result="modules/laplace/check/test3_results.txt", f=0.0,
+                                       dirichlet=[("topLeftCorner", 50.0), ("topRightCorner", 20.0), ("botLeftCorner", 20.0), ("botRightCorner", 50.0)],
+                                       penalty=1.0e30, eps=1.0e-4),
+}
+
+
+NULL = float("nan")  # a component the .arc leaves "NULL" (not imposed / no load)
+
+# Elasticity cases (modules/elasticity): vector unknown (ux, uy), BS = 2.  Result files hold `uid ux uy uz`; the module
+# validates with epsilon = 1e-3 and min value 1e-16 (modules/elasticity/FemModule.cc:547-553).  Penalty default 1e30
+# (modules/elasticity/Fem.axl:37).
+ELASTICITY_CASES = {
+    # modules/elasticity/inputs/bar.2D.traction.bsr.hypre.arc
+    "elasticity_traction_bar": dict(mesh="bar", result="modules/elasticity/check/elasticity_traction_bar_test_ref.txt", E=21.0e5, nu=0.28, f=(NULL, NULL),
+                                    dirichlet=[("left", (0.0, 0.0))], traction=[("right", (1.0, NULL))], penalty=1.0e30, eps=1.0e-3),
+    # modules/elasticity/inputs/bar.2D.traction.bodyforce.bsr.arc
+    "elasticity_traction_bodyforce_bar": dict(mesh="bar", result="modules/elasticity/check/elasticity_traction_bodyforce_bar_test_ref.txt", E=21.0e5, nu=0.28,
+                                              f=(3.33, -6.66), dirichlet=[("left", (0.0, 0.0))], traction=[("right", (1.33, 2.13))], penalty=1.0e30, eps=1.0e-3),
+    # modules/elasticity/inputs/bar.2D.PointDirichlet.bsr.hypre.arc
+    "elasticity_point_dirichlet_bar": dict(mesh="bar", result="modules/elasticity/check/elasticity_point-dirichlet_bar_test_ref.txt", E=21.0e5, nu=0.28,
+                                           f=(NULL, -1.0), dirichlet=[("left", (0.0, NULL)), ("right", (1.0, NULL)), ("botLeft", (0.0, 0.0)), ("botRight", (NULL, 0.0))],
+                                           traction=[], penalty=1.0e30, eps=1.0e-3),
 }
 
 
@@ -90,5 +116,27 @@ def main():
         print(name, cells.shape, coords.shape, exp.shape, os.path.getsize(path), "bytes")
 
 
+def main_elasticity():
+    for name, case in ELASTICITY_CASES.items():
+        m = read_msh(os.path.join(REF, "meshes", "msh", case["mesh"] + ".msh"))
+        cells, coords = m.cells(), m.coords
+        exp = np.loadtxt(os.path.join(REF, case["result"]))
+        out = dict(kind=np.array("elasticity"), dim=np.int32(m.dim), cells=cells, coords=coords, node_uid=m.node_tags, expected_uid=exp[:, 0].astype(np.int64),
+                   expected_vec=exp[:, 1:3], E=np.float64(case["E"]), nu=np.float64(case["nu"]), f2=np.array(case["f"], dtype=np.float64),
+                   penalty=np.float64(case["penalty"]), eps=np.float64(case["eps"]))
+        for i, (group, value) in enumerate(case["dirichlet"]):
+            out[f"dirichlet{i}_nodes"] = m.group_nodes(group)
+            out[f"dirichlet{i}_value2"] = np.array(value, dtype=np.float64)
+        out["nb_dirichlet"] = np.int32(len(case["dirichlet"]))
+        for i, (group, t) in enumerate(case["traction"]):
+            out[f"traction{i}_faces"] = m.group_elements(group)
+            out[f"traction{i}_t"] = np.array(t, dtype=np.float64)
+        out["nb_traction"] = np.int32(len(case["traction"]))
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, **out)
+        print(name, cells.shape, coords.shape, exp.shape, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     main()
+    main_elasticity()

@@ -26,14 +26,48 @@ def load_case(path):
     return case
 
 
+def is_elasticity(case):
+    return "kind" in case and str(case["kind"]) == "elasticity"
+
+
+def elasticity_rhs(case):
+    """Body force and traction of modules/elasticity/FemModule.cc:220-272 (host loops in the reference as well; "NULL"
+    components, stored as NaN, carry no load): rhs[dof(n,i)] += f_i * area / 3 per cell node and t_i * length / 2 per
+    face node."""
+    cells, coords = case["cells"], case["coords"]
+    rhs = np.zeros(2 * coords.shape[0])
+    f = np.nan_to_num(case["f2"], nan=0.0)
+    if not np.isnan(case["f2"]).all():
+        p = coords[cells]
+        cr = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
+        area = 0.5 * np.sqrt((cr * cr).sum(axis=1)) if cr.ndim == 2 else 0.5 * np.abs(cr)
+        for i in range(2):
+            np.add.at(rhs, 2 * cells.ravel() + i, np.repeat(f[i] * area / 3.0, 3))
+    for k in range(int(case["nb_traction"])):
+        faces, t = case[f"traction{k}_faces"], np.nan_to_num(case[f"traction{k}_t"], nan=0.0)
+        d = coords[faces[:, 1]] - coords[faces[:, 0]]
+        length = np.sqrt((d * d).sum(axis=1))
+        for i in range(2):
+            np.add.at(rhs, 2 * faces.ravel() + i, np.repeat(t[i] * length / 2.0, 2))
+    return rhs
+
+
+def elasticity_params(case):
+    E, nu = float(case["E"]), float(case["nu"])
+    return dict(op=orc.OP_ELASTICITY, lambda_=E * nu / ((1 + nu) * (1 - 2 * nu)), mu2=(E / (2 * (1 + nu))) * 2)  # FemModule.cc:133-134
+
+
 def check_against_reference(case, u):
     """femutils/FemUtils.cc:84-90,146-163: |ref - v| / (|ref| + |v|) compared with epsilon (Arcane isNearlyEqualWithEpsilon),
     values below min_value on both sides are skipped."""
     uid_to_lid = {int(t): i for i, t in enumerate(case["node_uid"])}
     eps, min_value = float(case["eps"]), 1.0e-16
     bad = []
-    for uid, ref in zip(case["expected_uid"], case["expected_value"]):
-        v = u[uid_to_lid[int(uid)]]
+    if is_elasticity(case):  # Real3 rule: every component with the scalar rule (femutils/FemUtils.cc:92-99)
+        pairs = [(uid, ref[i], u[2 * uid_to_lid[int(uid)] + i]) for uid, ref in zip(case["expected_uid"], case["expected_vec"]) for i in range(2)]
+    else:
+        pairs = [(uid, ref, u[uid_to_lid[int(uid)]]) for uid, ref in zip(case["expected_uid"], case["expected_value"])]
+    for uid, ref, v in pairs:
         if abs(ref) < min_value and abs(v) < min_value:
             continue
         if abs(ref - v) / (abs(ref) + abs(v)) > eps:
@@ -47,6 +81,21 @@ def oracle_system(case):
     cells, coords = case["cells"], case["coords"]
     nn = coords.shape[0]
     ri, co = orc.build_pattern(cells, nn)
+    if is_elasticity(case):
+        # modules/elasticity/FemModule.cc:102-116: bilinear operator (BS = 2), toLinearSystem, body force + traction,
+        # per-component penalty Dirichlet (ArcaneFemFunctionsGpu.h:514-523), then the solve() prelude
+        vals, nf = orc.assemble(cells, coords, ri, co, bs=2, per_block=False, **elasticity_params(case))
+        assert nf == 0
+        rows, nbcol, cols = orc.to_csr(2, ri, co)
+        rhs = elasticity_rhs(case)
+        finfo, fval = np.zeros(2 * nn, np.uint8), np.zeros(2 * nn)
+        einfo, ev = np.zeros(2 * nn, np.uint8), np.zeros(2 * nn)
+        for i in range(int(case["nb_dirichlet"])):
+            for comp, value in enumerate(case[f"dirichlet{i}_value2"]):
+                if not np.isnan(value):
+                    orc.dirichlet_flag_penalty(2, comp, float(value), float(case["penalty"]), case[f"dirichlet{i}_nodes"], finfo, fval, rhs)
+        orc.dirichlet_apply(rows, cols, vals, einfo, ev, finfo, fval, rhs)
+        return ri, co, vals, rhs, (rows, cols)
     vals, nf = orc.assemble(cells, coords, ri, co, per_block=False)
     assert nf == 0
     rows, nbcol, cols = orc.to_csr(1, ri, co)
@@ -72,4 +121,4 @@ def test_oracle_reproduces_reference_solution(path):
 
 
 def test_golden_fixtures_present():
-    assert len(GOLDEN) >= 7
+    assert len(GOLDEN) >= 12
