@@ -3,57 +3,13 @@
 // shipped element callbacks (modules/poisson/FemModule.h:139-186, modules/elasticity/FemModule.h:112-152,
 // modules/heat/FemModule.cc:678-770).
 #include "internal.h"
-#include "b2f/assemble.cuh"
 
 namespace b2f {
 
-namespace {
-  template <class Op>
-  int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stream, const double* qdot)
-  {
-    AssembleArgs A;
-    A.cell_node = h->mesh.cell_node;
-    A.coords = h->mesh.coords;
-    A.node_is_own = h->mesh.node_is_own;
-    A.cell_is_own = h->mesh.cell_is_own;
-    A.nb_cell = h->mesh.nb_cell;
-    A.nb_node = h->mesh.nb_node;
-    A.row_index = h->row_index.as<int32_t>();
-    A.columns = h->columns.as<int32_t>();
-    A.values = h->values.as<double>();
-    A.nc_ptr = h->nc_ptr.as<int32_t>();
-    A.nc_list = h->nc_list.as<uint32_t>();
-    A.nc_slots = h->nc_slots.as<uint32_t>();
-    A.slots_ok = h->slots_ok ? 1 : 0;
-    A.fan_ptr = h->fan_ptr.as<int32_t>();
-    A.fan_steps = h->fan_steps.as<uint32_t>();
-    A.fan_cell = h->fan_cell.as<uint32_t>();
-    A.fan_ok = h->fan_ok ? 1 : 0;
-    A.fan_lockstep = h->fan_lockstep ? 1 : 0;
-    for (int i = 0; i < 6; ++i)
-      A.tile_extents[i] = h->tile_extents[i];
-    A.counters = h->counters.as<unsigned long long>();
-    A.accumulate = accumulate;
-    int variant = h->variant;
-    if (variant == B2F_ASM_DEFAULT)
-      variant = B2F_ASM_NODE_GATHER;
-    // constant source fused into the walk (value per cell and node = qdot * measure / NV, ArcaneFemFunctionsGpu.h:402-429):
-    // the fan kernel sums 6*volume / 2*area, hence the factor 1/(6*4) / 1/(2*3)
-    if (h->range_rows >= 0) { // host pipeline: rows [range_first_row, range_first_row + range_rows), multiples of the tile height
-      A.first_tile = h->range_first_row / FanCfg<Op>::ROWS;
-      A.nb_tile = (h->range_rows + FanCfg<Op>::ROWS - 1) / FanCfg<Op>::ROWS;
-    }
-    const bool fused = qdot != nullptr && variant == B2F_ASM_NODE_GATHER && h->fan_ok && h->mesh.cell_is_own == nullptr;
-    if (fused) {
-      A.rhs = h->rhs.as<double>();
-      A.rhs_factor = *qdot / (Op::NV == 4 ? 24.0 : 6.0);
-    }
-    B2F_CUDA(launch_assemble<Op>(A, op, variant, h->per_block, h->nb_nz, stream));
-    if (qdot != nullptr && !fused)
-      return rhs_constant_source(h, *qdot, stream);
-    return B2F_OK;
-  }
-} // namespace
+// one translation unit per operator family (parallel compilation of the kernel instantiations)
+int run_laplace(b2f_context_s* h, int accumulate, cudaStream_t stream, const double* qdot);
+int run_elasticity(b2f_context_s* h, double lambda, double mu2, int accumulate, cudaStream_t stream, const double* qdot);
+int run_heat(b2f_context_s* h, double lambda, double inv_dt, const double* cell_lambda, int accumulate, cudaStream_t stream, const double* qdot);
 
 int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot)
 {
@@ -64,18 +20,15 @@ int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, cons
   case B2F_OP_LAPLACE:
     if (bs != 1)
       return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_LAPLACE needs block_size 1 (got %d)", bs);
-    return nv == 3 ? run(h, LaplaceTri{}, op->accumulate, stream, qdot) : run(h, LaplaceTet{}, op->accumulate, stream, qdot);
+    return run_laplace(h, op->accumulate, stream, qdot);
   case B2F_OP_ELASTICITY:
-    if (nv == 3 && bs == 2)
-      return run(h, ElasticityTri{ op->lambda, op->mu2 }, op->accumulate, stream, qdot);
-    if (nv == 4 && bs == 3)
-      return run(h, ElasticityTet{ op->lambda, op->mu2 }, op->accumulate, stream, qdot);
+    if ((nv == 3 && bs == 2) || (nv == 4 && bs == 3))
+      return run_elasticity(h, op->lambda, op->mu2, op->accumulate, stream, qdot);
     return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_ELASTICITY needs block_size == dim (dim=%d, block_size=%d)", h->mesh.dim, bs);
   case B2F_OP_HEAT:
     if (bs != 1)
       return fail(B2F_ERR_INVALID_ARGUMENT, "B2F_OP_HEAT needs block_size 1 (got %d)", bs);
-    return nv == 3 ? run(h, HeatTri{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream, qdot)
-                   : run(h, HeatTet{ op->lambda, op->inv_dt, op->cell_lambda }, op->accumulate, stream, qdot);
+    return run_heat(h, op->lambda, op->inv_dt, op->cell_lambda, op->accumulate, stream, qdot);
   default:
     return fail(B2F_ERR_NOT_IMPLEMENTED, "unknown operator kind %d", op->kind);
   }

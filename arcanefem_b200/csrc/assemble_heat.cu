@@ -1,0 +1,10 @@
+// Heat P1, mass + stiffness (modules/heat/FemModule.cc:678-770) and its tetrahedral twin: kernel instantiations of
+// include/b2f/assemble.cuh.
+#include "assemble_run.cuh"
+
+namespace b2f {
+int run_heat(b2f_context_s* h, double lambda, double inv_dt, const double* cell_lambda, int accumulate, cudaStream_t stream, const double* qdot)
+{
+  return h->nv == 3 ? run(h, HeatTri{ lambda, inv_dt, cell_lambda }, accumulate, stream, qdot) : run(h, HeatTet{ lambda, inv_dt, cell_lambda }, accumulate, stream, qdot);
+}
+} // namespace b2f

@@ -7,7 +7,7 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 mkdir -p build/var_$NAME arcanefem_b200/lib
 for f in arcanefem_b200/csrc/*.cu; do
   b=$(basename $f .cu)
-  if [ "$b" = "assemble" ]; then
+  if [[ "$b" == assemble_* ]]; then
     $NVCC $ARCH -O3 -std=c++17 -lineinfo -ccbin /usr/bin/g++ -Xcompiler -fPIC -Iinclude -Iarcanefem_b200/csrc "$@" -c $f -o build/var_$NAME/$b.o &
   else
     [ -f build/$b.o ] || { echo "run make first"; exit 1; }
