@@ -842,10 +842,15 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
 #ifndef B2F_FAN_ROWS
 #define B2F_FAN_ROWS 128
 #endif
+#ifndef B2F_FAN_ROWS_BS3
+#define B2F_FAN_ROWS_BS3 32
+#endif
 template <class Op>
 struct FanCfg : SlotsCfg<Op>
 {
-  static constexpr int ROWS = (Op::BS == 1) ? B2F_FAN_ROWS : 64; // block rows (= threads) per CTA
+  // BS = 3: 9 doubles per block make shared memory the occupancy limit (1.2 KB per row); 32-row CTAs pack 6 CTAs = 6 warps
+  // per SM where 64-row CTAs fit 2 CTAs = 4 warps (elasticity3d 2.51 -> 2.07 ms)
+  static constexpr int ROWS = (Op::BS == 1) ? B2F_FAN_ROWS : (Op::BS == 3 ? B2F_FAN_ROWS_BS3 : 64); // block rows (= threads) per CTA
   static_assert(ROWS == 128 || ROWS == 64 || ROWS == 32, "tile extents exist for 128, 64 and 32 rows");
 };
 #ifndef B2F_FAN_TILE_AHEAD
