@@ -5,6 +5,8 @@
                 row elimination on the plane z=0 (flag + apply)
   heat3d/heat2d config #4: heat, mass + stiffness re-assembled every time step on a fixed pattern (repeated-assembly throughput)
   poisson2d     2D twin of the headline (square, 2 triangles per quad)
+  poisson3d_shuffled_cells / poisson3d_shuffled   the headline mesh with a random cell order / random cell order and node
+                numbering (the unstructured-access cost); not in the default list
 Prints one JSON line per workload: GNNZ/s, ms/step, algorithmic GB/s and the fraction of the measured HBM peak.
 """
 import argparse
@@ -38,6 +40,10 @@ def run(workload, n, steps, warmup, variant):
         dim, bs, (cells, coords), op = 2, 1, gen.square(n), None
     elif workload == "poisson2d":
         dim, bs, (cells, coords), op = 2, 1, gen.square(n), fem.Operator.laplace()
+    elif workload == "poisson3d_shuffled_cells":  # random cell permutation (seed 42), node numbering kept
+        dim, bs, (cells, coords), op = 3, 1, gen.cube_kuhn(n, shuffle_cells=42), fem.Operator.laplace()
+    elif workload == "poisson3d_shuffled":  # random cell permutation and random node renumbering (seed 7): no locality at all
+        dim, bs, (cells, coords), op = 3, 1, gen.cube_kuhn(n, shuffle_cells=42, shuffle_nodes=7), fem.Operator.laplace()
     else:
         raise SystemExit(f"unknown workload {workload}")
     nc, nn, nv = cells.shape[0], coords.shape[0], cells.shape[1]
@@ -91,7 +97,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--variant", type=int, default=3)
     args = ap.parse_args()
-    sizes = {"elasticity3d": 149, "heat3d": 203, "heat2d": 5000, "poisson2d": 5000}
+    sizes = {"elasticity3d": 149, "heat3d": 203, "heat2d": 5000, "poisson2d": 5000, "poisson3d_shuffled_cells": 203, "poisson3d_shuffled": 203}
     for w in args.workloads.split(","):
         print(json.dumps(run(w, sizes[w], args.steps, args.warmup, args.variant)), flush=True)
 
