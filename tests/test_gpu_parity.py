@@ -613,3 +613,51 @@ def test_host_entry_point_matches_device_path(case):
     bsr.assembleBilinearHost(op, coords_host, None)
     torch.cuda.synchronize()
     assert_values_close(_np(bsr.matrix().values()), ref, ri, 1, what=f"{case} device values")
+
+
+@pytest.mark.parametrize("sparsity_build", [1, 2])
+@pytest.mark.parametrize("variant", [1, 3, 4])
+def test_empty_ragged_and_repeated_inputs(variant, sparsity_build):
+    """Edge inputs: no cells at all (every row is its diagonal), nodes that no cell references, a single cell, the same
+    cell listed twice (contributions add, the pattern does not change), a mesh with no nodes (refused)."""
+    from oracle import oracle as orc
+    from arcanefem_b200.bsr import Mesh
+    fem = _fem()
+    rng = np.random.default_rng(21)
+
+    def run(dim, cells, coords, bs=1, op=None, params=None):
+        nn = coords.shape[0]
+        bsr = fem.BSRFormat(bs)
+        bsr.initialize(Mesh.from_numpy(dim, cells, coords), True, assembly_variant=variant, sparsity_build=sparsity_build)
+        bsr.computeSparsity()
+        ri, co = orc.build_pattern(cells, nn)
+        mat = bsr.matrix()
+        assert mat.nbRow() == nn and mat.nbCol() == co.shape[0]
+        np.testing.assert_array_equal(_np(mat.rowIndexWithEnd()), ri)
+        np.testing.assert_array_equal(_np(mat.columns()), co)
+        bsr.assembleBilinear(op or fem.Operator.laplace())
+        torch.cuda.synchronize()
+        ref, nf = orc.assemble(cells, coords, ri, co, bs=bs, per_block=False, **(params or {}))
+        assert nf == 0 and bsr.stats()["columns_not_found"] == 0
+        assert_values_close(_np(mat.values()), ref, ri, bs)
+        return bsr
+
+    # no cells: nnzb = Nn, all values zero
+    run(3, np.zeros((0, 4), np.int32), rng.uniform(size=(7, 3)))
+    run(2, np.zeros((0, 3), np.int32), rng.uniform(size=(5, 3)))
+    # one cell, and nodes nobody references (rows 4..9 hold their diagonal only)
+    b = run(3, np.array([[2, 0, 3, 1]], np.int32), rng.uniform(size=(10, 3)))
+    assert _np(b.matrix().nbNzPerRow()).tolist() == [4, 4, 4, 4, 1, 1, 1, 1, 1, 1]
+    # the same cell twice, next to another one
+    c2 = np.array([[0, 1, 2], [0, 1, 2], [1, 3, 2]], np.int32)
+    x2 = np.array([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [1.1, 0.9, 0.0], [5.0, 5.0, 0.0]])
+    run(2, c2, x2)
+    run(2, c2, x2, bs=2, op=fem.Operator.elasticity(21.0e5, 0.28), params=op_params("elasticity"))
+    c3 = np.array([[0, 1, 2, 3], [0, 1, 2, 3], [1, 2, 3, 4]], np.int32)
+    x3 = rng.uniform(size=(6, 3))
+    run(3, c3, x3)
+    run(3, c3, x3, bs=3, op=fem.Operator.elasticity(21.0e5, 0.28), params=op_params("elasticity"))
+    # a mesh with no nodes is refused like the reference does (ArgumentException, femutils/BSRFormat.h:121-125)
+    with pytest.raises(fem.B2FError) as err:
+        fem.BSRFormat(1).initialize(Mesh.from_numpy(3, np.zeros((0, 4), np.int32), np.zeros((0, 3))), True, assembly_variant=variant, sparsity_build=sparsity_build)
+    assert err.value.status == -1 and "should be positive and not null" in err.value.message
