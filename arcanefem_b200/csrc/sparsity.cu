@@ -276,11 +276,18 @@ namespace {
   constexpr int FAN_MAXC = 64;
   constexpr unsigned FAN_START = 0x80000000u;
 
-  template <int NV, bool WRITE>
+  //
+  // Built in one walk per row.  k_build_fan walks and leaves ONE staged word per cell at stage[nc_ptr[row] + visit rank]
+  // (an exact bound, so no counting pass): bits 0-7 slot of C, bit 8 N leaves, bit 9 parity, bits 10-17 / 18-25 slots of
+  // the window (N, O) a START word has to load before this cell (0 = none; slots of other vertices are >= 1), bits 26-31
+  // position of the cell in the node's list.  Walked rows have at most FAN_MAXC cells, hence at most 3 FAN_MAXC + 1 = 193
+  // blocks, so 8-bit slots do.  The row's word count (cells + STARTs) goes to fan_count; after the scan k_pack_fan expands
+  // the staged words into the step words and cell ids at fan_ptr[row].  Rows that are not walked stage nothing (count =
+  // 2 per cell) and get their words from k_pack_fan directly.
+  template <int NV>
   __global__ void __launch_bounds__(128) k_build_fan(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
                                                      const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, long long nb_node,
-                                                     const int32_t* __restrict__ fan_ptr, int32_t* __restrict__ fan_count, uint32_t* __restrict__ fan_steps,
-                                                     uint32_t* __restrict__ fan_cell, unsigned long long* __restrict__ counters)
+                                                     int32_t* __restrict__ fan_count, uint32_t* __restrict__ stage, unsigned long long* __restrict__ counters)
   {
     constexpr int NO = NV - 1; // other vertices of a cell
     const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -291,15 +298,16 @@ namespace {
     const int32_t qb = nc_ptr[row];
     const int m = nc_ptr[row + 1] - qb;
     if (k > 1023) {
-      if (!WRITE) {
-        atomicAdd(counters + 3, 1ull);
-        fan_count[row] = 0;
-      }
+      atomicAdd(counters + 3, 1ull);
+      fan_count[row] = 0;
       return;
     }
-    uint32_t* out = WRITE ? fan_steps + fan_ptr[row] : nullptr;
-    uint32_t* outc = WRITE ? fan_cell + fan_ptr[row] : nullptr;
-    int nout = 0;
+    if (m > FAN_MAXC) { // very high valence: no walk, every cell is its own chain (k_pack_fan writes the words)
+      fan_count[row] = 2 * m;
+      return;
+    }
+    uint32_t* out = stage + qb;
+    int nout = 0, nstart = 0;
     auto slot_of = [&](int32_t c) {
       int lo = 1, hi = k;
       while (lo < hi) {
@@ -319,30 +327,6 @@ namespace {
           inv += pos[i] > pos[j];
       return inv & 1;
     };
-    if (m > FAN_MAXC) { // very high valence: no walk, every cell is its own chain
-      for (int q = 0; q < m; ++q) {
-        const uint32_t e = nc_list[qb + q];
-        const long long cell = e >> 2;
-        const int a = (int)(e & 3u);
-        int pos[NV];
-        uint32_t sl[NO];
-        pos[0] = a;
-        for (int f = 0; f < NO; ++f) {
-          pos[f + 1] = f < a ? f : f + 1;
-          sl[f] = (uint32_t)slot_of(cell_node[cell * NV + pos[f + 1]]);
-        }
-        if (WRITE) {
-          out[nout] = FAN_START | sl[0] | (NV == 4 ? (sl[1] << 10) : 0u);
-          outc[nout] = (uint32_t)cell;
-          out[nout + 1] = sl[NO - 1] | ((uint32_t)is_odd(pos) << 11);
-          outc[nout + 1] = (uint32_t)cell;
-        }
-        nout += 2;
-      }
-      if (!WRITE)
-        fan_count[row] = nout;
-      return;
-    }
     // The walk is made canonical in the row's own terms: the other vertices of a cell are held in ascending slot order and
     // every choice (start cell, ties between equally good next cells) goes to the smallest slot triple, never to a cell
     // id or a position in the list.  Rows with the same local topology then walk alike whatever the cell numbering is, so
@@ -501,12 +485,9 @@ namespace {
         for (int f = 0; f < NO; ++f)
           if (f != fc && f != fnext)
             win[w++] = v[cur][f];
-        if (WRITE) {
-          out[nout] = FAN_START | win[0] | (NV == 4 ? (win[1] << 10) : 0u);
-          outc[nout] = nc_list[qb + cur] >> 2;
-        }
-        ++nout;
+        ++nstart;
       }
+      const uint32_t staged_window = start ? ((win[0] << 10) | (NV == 4 ? (win[1] << 18) : 0u)) : 0u;
       const uint32_t sc = v[cur][fc];
       // positions in the cell of (row node, A, [B,] C)
       int pos[NV];
@@ -519,18 +500,95 @@ namespace {
       uint32_t drop_n = 0;
       if (fnext >= 0 && NV == 4)
         drop_n = (v[cur][fnext] == win[0]) ? 1u : 0u;
-      if (WRITE) {
-        out[nout] = sc | (drop_n << 10) | ((uint32_t)is_odd(pos) << 11);
-        outc[nout] = nc_list[qb + cur] >> 2;
-      }
+      out[nout] = sc | (drop_n << 8) | ((uint32_t)is_odd(pos) << 9) | staged_window | ((uint32_t)cur << 26);
       ++nout;
       if (NV == 4 && !drop_n)
         win[1] = win[0];
       win[0] = sc;
       cur = fnext >= 0 ? nb[cur][fnext] : -1;
     }
-    if (!WRITE)
-      fan_count[row] = nout;
+    fan_count[row] = nout + nstart;
+  }
+
+  // Expands the staged words of k_build_fan into the plan: one warp per 32 rows, the lanes take the cells of a row together.
+  template <int NV>
+  __global__ void __launch_bounds__(256) k_pack_fan(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
+                                                    const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, const int32_t* __restrict__ fan_ptr,
+                                                    long long nb_node, const uint32_t* __restrict__ stage, uint32_t* __restrict__ fan_steps, uint32_t* __restrict__ fan_cell)
+  {
+    constexpr int NO = NV - 1;
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const long long r0 = w * 32;
+    if (r0 >= nb_node)
+      return;
+    const long long mine = r0 + lane < nb_node ? r0 + lane : nb_node - 1;
+    const int32_t my_dst = fan_ptr[mine];
+    const int32_t my_cnt = fan_ptr[mine + 1] - my_dst;
+    const int32_t my_qb = nc_ptr[mine];
+    const int32_t my_m = nc_ptr[mine + 1] - my_qb;
+    const int rows = nb_node - r0 < 32 ? (int)(nb_node - r0) : 32;
+    for (int r = 0; r < rows; ++r) {
+      const int32_t dst = __shfl_sync(0xffffffffu, my_dst, r);
+      const int32_t cnt = __shfl_sync(0xffffffffu, my_cnt, r);
+      const int32_t qb = __shfl_sync(0xffffffffu, my_qb, r);
+      const int32_t m = __shfl_sync(0xffffffffu, my_m, r);
+      if (cnt == 0)
+        continue;
+      if (m > FAN_MAXC) { // not walked: START + EMIT per cell, vertices in cell order
+        const int32_t rb = row_index[r0 + r];
+        const int k = row_index[r0 + r + 1] - rb;
+        for (int q = lane; q < m; q += 32) {
+          const uint32_t e = nc_list[qb + q];
+          const long long cell = e >> 2;
+          const int a = (int)(e & 3u);
+          int pos[NV];
+          uint32_t sl[NO];
+          pos[0] = a;
+          for (int f = 0; f < NO; ++f) {
+            pos[f + 1] = f < a ? f : f + 1;
+            const int32_t c = cell_node[cell * NV + pos[f + 1]];
+            int lo = 1, hi = k;
+            while (lo < hi) {
+              const int mid = (lo + hi) >> 1;
+              if (columns[rb + mid] < c)
+                lo = mid + 1;
+              else
+                hi = mid;
+            }
+            sl[f] = (uint32_t)lo;
+          }
+          int inv = 0;
+          for (int i = 0; i < NV; ++i)
+            for (int j = i + 1; j < NV; ++j)
+              inv += pos[i] > pos[j];
+          fan_steps[dst + 2 * q] = FAN_START | sl[0] | (NV == 4 ? (sl[1] << 10) : 0u);
+          fan_cell[dst + 2 * q] = (uint32_t)cell;
+          fan_steps[dst + 2 * q + 1] = sl[NO - 1] | ((uint32_t)(inv & 1) << 11);
+          fan_cell[dst + 2 * q + 1] = (uint32_t)cell;
+        }
+        continue;
+      }
+      int before = 0; // START words of the row so far
+      for (int base = 0; base < m; base += 32) {
+        const int j = base + lane;
+        const uint32_t sw = j < m ? stage[qb + j] : 0u;
+        const uint32_t wn = (sw >> 10) & 255u, wo = (sw >> 18) & 255u;
+        const unsigned has = __ballot_sync(0xffffffffu, wn != 0u);
+        if (j < m) {
+          int p = dst + j + before + __popc(has & ((1u << lane) - 1u));
+          const uint32_t cell = nc_list[qb + (sw >> 26)] >> 2;
+          if (wn != 0u) {
+            fan_steps[p] = FAN_START | wn | (wo << 10);
+            fan_cell[p] = cell;
+            ++p;
+          }
+          fan_steps[p] = (sw & 255u) | (((sw >> 8) & 1u) << 10) | (((sw >> 9) & 1u) << 11);
+          fan_cell[p] = cell;
+        }
+        before += __popc(has);
+      }
+    }
   }
 
   // Largest gather tile of the plan for tiles of 128, 64 and 32 consecutive rows: out = {blocks128, adj128, blocks64, adj64, blocks32, adj32}.
@@ -787,7 +845,6 @@ static int pattern_from_lists(b2f_context_s* h, cudaStream_t stream, bool* fallb
   h->nb_edge = (nb_col - nn) / 2;
   B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
   B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
-  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)nb_nz, stream)); // BSRMatrix::initialize fills 0, BSRFormat.h:136
   if (nn > 0) {
     if (nv == 3)
       k_row_unique<3, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters);
@@ -864,7 +921,6 @@ static int pattern_by_sort(b2f_context_s* h, cudaStream_t stream)
   // --- K5: columns, then canonical order inside every row
   B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
   B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
-  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)nb_nz, stream)); // BSRMatrix::initialize fills 0, BSRFormat.h:136
   int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724
   k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(cursor, nn, 1);
   k_fill_diagonal<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->columns.as<int32_t>());
@@ -996,10 +1052,20 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     const int32_t* co = h->columns.as<int32_t>();
     const int32_t* ncp = h->nc_ptr.as<int32_t>();
     const uint32_t* ncl = h->nc_list.as<uint32_t>();
+    // staging of the walk (one word per adjacency): the value array is idle until the first assembly and large enough on
+    // any ordinary mesh, so it lends its memory (and is zero-filled afterwards, BSRFormat.h:136)
+    uint32_t* stage = nullptr;
+    const size_t stage_bytes = sizeof(uint32_t) * (size_t)(nb_adj + 8);
+    if (h->values.bytes >= stage_bytes)
+      stage = h->values.as<uint32_t>();
+    else {
+      B2F_CUDA(h->ws_keys_a.alloc(stage_bytes));
+      stage = h->ws_keys_a.as<uint32_t>();
+    }
     if (nv == 3)
-      k_build_fan<3, false><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, nullptr, fan_count, nullptr, nullptr, counters);
+      k_build_fan<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters);
     else
-      k_build_fan<4, false><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, nullptr, fan_count, nullptr, nullptr, counters);
+      k_build_fan<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters);
     B2F_CUDA(cudaGetLastError());
     B2F_CUDA(h->fan_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
     long long nb_step = 0;
@@ -1010,11 +1076,11 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     B2F_CUDA(h->fan_steps.alloc(sizeof(uint32_t) * (size_t)(nb_step + 8)));
     B2F_CUDA(h->fan_cell.alloc(sizeof(uint32_t) * (size_t)(nb_step + 8)));
     if (nv == 3)
-      k_build_fan<3, true><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, h->fan_ptr.as<int32_t>(), nullptr, h->fan_steps.as<uint32_t>(),
-                                                                  h->fan_cell.as<uint32_t>(), counters);
+      k_pack_fan<3><<<grid_for(((nn + 31) / 32) * 32, 256), 256, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, h->fan_ptr.as<int32_t>(), nn, stage,
+                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>());
     else
-      k_build_fan<4, true><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, h->fan_ptr.as<int32_t>(), nullptr, h->fan_steps.as<uint32_t>(),
-                                                                  h->fan_cell.as<uint32_t>(), counters);
+      k_pack_fan<4><<<grid_for(((nn + 31) / 32) * 32, 256), 256, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, h->fan_ptr.as<int32_t>(), nn, stage,
+                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>());
     B2F_CUDA(cudaGetLastError());
     tile_ptr = h->fan_ptr.as<int32_t>();
     // lockstep form of the step words, on request only (B2F_FAN_LOCKSTEP): measured slower than the select walk even
@@ -1049,6 +1115,9 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0);
   }
 
+  // BSRMatrix::initialize fills the values with 0 (femutils/BSRFormat.h:136); done last because the plan build borrows the array
+  B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)h->nb_nz, stream));
+
   // --- linear-system state (HypreDoFLinearSystem.cc:224-242)
   h->nb_dof = nn * h->bs;
   B2F_CUDA(h->rhs.alloc(sizeof(double) * (size_t)h->nb_dof));
@@ -1065,6 +1134,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   h->ws_i64.release();
   h->ws_tmp.release();
   h->ws_i32a.release();
+  h->ws_keys_a.release();
   h->has_pattern = true;
   return B2F_OK;
 }
