@@ -127,6 +127,11 @@ int b2f_destroy(b2f_handle h)
     cudaStreamDestroy(h->pipe_h2d);
   if (h->pipe_d2h)
     cudaStreamDestroy(h->pipe_d2h);
+  for (cudaEvent_t e : h->comm_events)
+    if (e)
+      cudaEventDestroy(e);
+  if (h->comm_stream)
+    cudaStreamDestroy(h->comm_stream);
   delete h;
   return B2F_OK;
 }
@@ -570,6 +575,72 @@ int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream)
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
   return ghost_exchange(h, nccl_comm, (cudaStream_t)stream);
+}
+
+int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!op)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_exchange: null operator");
+  cudaStream_t s = (cudaStream_t)stream;
+  const GhostPlan& P = h->ghost;
+  if (!P.ready)
+    return fail(B2F_ERR_STATE, "b2f_assemble_exchange: b2f_ghost_plan has not been called");
+  const long long nn = h->mesh.nb_node;
+  const int variant = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
+  // rows the exchange reads, widened to whole tiles of the gather kernel (128 rows is a multiple of every tile height)
+  const long long lo = (P.send_row_lo / 128) * 128;
+  const long long hi = std::min<long long>(nn, ((P.send_row_hi + 127) / 128) * 128);
+  const bool overlap = variant == B2F_ASM_NODE_GATHER && h->fan_ok && !op->accumulate && (P.total_send > 0 ? (hi - lo) * 4 <= nn : P.total_recv > 0);
+  if (!overlap) { // nothing to hide the exchange behind (or the sent rows are spread over the whole numbering)
+    int rc = assemble(h, op, s);
+    return rc != B2F_OK ? rc : ghost_exchange(h, nccl_comm, s);
+  }
+  if (!h->comm_stream) {
+    int least = 0, greatest = 0;
+    B2F_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B2F_CUDA(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, greatest));
+    for (cudaEvent_t& e : h->comm_events)
+      B2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  // 1. the rows that travel; 2. their pack + send/recv on the communication stream; 3. every other row meanwhile;
+  // 4. the received partial sums are added once both are done
+  auto assemble_rows = [&](long long first, long long count, bool keep_counters) -> int {
+    if (count <= 0)
+      return B2F_OK;
+    h->range_first_row = first;
+    h->range_rows = count;
+    h->range_keep_counters = keep_counters;
+    const int rc = assemble(h, op, s);
+    h->range_rows = -1;
+    h->range_first_row = 0;
+    h->range_keep_counters = false;
+    return rc;
+  };
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, s));
+  int rc = P.total_send > 0 ? assemble_rows(lo, hi - lo, true) : B2F_OK; // a rank that only receives posts its receives at once
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(cudaEventRecord(h->comm_events[0], s));
+  B2F_CUDA(cudaStreamWaitEvent(h->comm_stream, h->comm_events[0], 0));
+  rc = ghost_send_recv(h, nccl_comm, h->comm_stream);
+  if (P.total_send > 0) {
+    if (rc == B2F_OK)
+      rc = assemble_rows(0, lo, true);
+    if (rc == B2F_OK)
+      rc = assemble_rows(hi, nn - hi, true);
+  }
+  else if (rc == B2F_OK)
+    rc = assemble_rows(0, nn, true);
+  // the caller's stream always rejoins the communication stream, also on an error path
+  cudaError_t e1 = cudaEventRecord(h->comm_events[1], h->comm_stream);
+  cudaError_t e2 = e1 == cudaSuccess ? cudaStreamWaitEvent(s, h->comm_events[1], 0) : e1;
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(e1);
+  B2F_CUDA(e2);
+  return ghost_add(h, s);
 }
 
 } // extern "C"

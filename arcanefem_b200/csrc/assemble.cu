@@ -14,7 +14,7 @@ int run_heat(b2f_context_s* h, double lambda, double inv_dt, const double* cell_
 int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot)
 {
   const int nv = h->nv, bs = h->bs;
-  if (h->range_rows < 0 || h->range_first_row == 0)
+  if (h->range_rows < 0 ? true : (h->range_first_row == 0 && !h->range_keep_counters))
     B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, stream));
   switch (op->kind) {
   case B2F_OP_LAPLACE:

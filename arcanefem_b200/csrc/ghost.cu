@@ -266,6 +266,12 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
       send_rows.push_back(e.second);
   }
   const long long nsend_rows = (long long)send_rows.size();
+  P.send_row_lo = P.send_row_hi = 0;
+  if (nsend_rows > 0) {
+    const auto mm = std::minmax_element(send_rows.begin(), send_rows.end());
+    P.send_row_lo = *mm.first;
+    P.send_row_hi = (int64_t)*mm.second + 1;
+  }
 
   // 2. block offsets of the sent rows
   std::vector<int32_t> ri((size_t)nn + 1);
@@ -423,7 +429,8 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
   return B2F_OK;
 }
 
-int ghost_exchange(b2f_context_s* h, void* comm_v, cudaStream_t stream)
+// First half of the exchange: pack the ghost rows (zeroing them) and run the grouped send/recv of every neighbour.
+int ghost_send_recv(b2f_context_s* h, void* comm_v, cudaStream_t stream)
 {
   NcclApi* api = nccl_api();
   if (!api)
@@ -448,10 +455,23 @@ int ghost_exchange(b2f_context_s* h, void* comm_v, cudaStream_t stream)
       B2F_NCCL(api->Recv(P.recv_vals.as<double>() + P.recv_off[(size_t)p] * bs2, (size_t)(P.recv_blocks[(size_t)p] * bs2), ncclDouble, p, comm, stream));
   }
   B2F_NCCL(api->GroupEnd());
+  return B2F_OK;
+}
+
+// Second half: the received partial sums are added into the owner rows.
+int ghost_add(b2f_context_s* h, cudaStream_t stream)
+{
+  GhostPlan& P = h->ghost;
   if (P.total_recv > 0)
     k_ghost_add<<<grid_for(P.total_recv, 256), 256, 0, stream>>>(P.recv_index.as<long long>(), P.total_recv, P.recv_vals.as<double>(), h->values.as<double>());
   B2F_CUDA(cudaGetLastError());
   return B2F_OK;
+}
+
+int ghost_exchange(b2f_context_s* h, void* comm_v, cudaStream_t stream)
+{
+  const int rc = ghost_send_recv(h, comm_v, stream);
+  return rc != B2F_OK ? rc : ghost_add(h, stream);
 }
 
 } // namespace b2f

@@ -60,6 +60,7 @@ struct GhostPlan
   std::vector<int64_t> send_off, recv_off; // offsets (in blocks) of every peer's part of the packed buffers
   DevBuf send_index, recv_index, send_vals, recv_vals; // value index per exchanged scalar; packed values
   int64_t total_send = 0, total_recv = 0; // scalars
+  int64_t send_row_lo = 0, send_row_hi = 0; // span of the local rows that are sent (ghost rows an assembled cell touches)
 };
 
 } // namespace b2f
@@ -95,6 +96,9 @@ struct b2f_context_s
   b2f::DevBuf coords_stage; // b2f_assemble_host
   // b2f_assemble_host pipeline: row chunks, the highest node id each chunk reads, value offsets at the chunk boundaries
   int64_t range_first_row = 0, range_rows = -1; // >= 0 while a chunk of the pipeline is being launched
+  bool range_keep_counters = false; // a later range of the same assembly: the counters are not cleared again
+  cudaStream_t comm_stream = nullptr; // b2f_assemble_exchange: ghost rows travel here while the other rows are assembled
+  cudaEvent_t comm_events[2] = { nullptr, nullptr };
   std::vector<int64_t> chunk_row, chunk_value_off, chunk_node_hi;
   cudaStream_t pipe_h2d = nullptr, pipe_d2h = nullptr;
   std::vector<cudaEvent_t> pipe_events;
@@ -125,4 +129,6 @@ int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s);
 // ghost.cu
 int ghost_plan(b2f_context_s* h, void* comm, int rank, int world, const int32_t* node_owner, const int64_t* node_gid, cudaStream_t s);
 int ghost_exchange(b2f_context_s* h, void* comm, cudaStream_t s);
+int ghost_send_recv(b2f_context_s* h, void* comm, cudaStream_t s);
+int ghost_add(b2f_context_s* h, cudaStream_t s);
 } // namespace b2f

@@ -152,6 +152,13 @@ class GhostExchange:
         import torch
         check(self._lib.b2f_ghost_exchange(self._bsr._h, self._comm, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
+    def assemble_and_run(self, op):
+        """One multi-GPU assembly step with the exchange hidden behind the assembly of the rows that do not travel
+        (b2f_assemble_exchange): same values as bsr.assembleBilinear(op) followed by run()."""
+        import torch
+        d = op.desc(False)
+        check(self._lib.b2f_assemble_exchange(self._bsr._h, C.byref(d), self._comm, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
     def close(self):
         if self._comm:
             self._lib.b2f_nccl_comm_destroy(self._comm)

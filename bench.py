@@ -186,9 +186,13 @@ def run_b200(args):
         exchange = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"])
 
     def step():
-        bsr.assembleBilinear(op)
-        if exchange is not None:
+        if exchange is None:
+            bsr.assembleBilinear(op)
+        elif args.no_overlap:
+            bsr.assembleBilinear(op)
             exchange.run()
+        else:
+            exchange.assemble_and_run(op)  # C ABI b2f_assemble_exchange: ghost rows first, exchange behind the other rows
 
     if exchange is not None:
         for _ in range(10):  # untimed: NCCL channel / proxy set-up for the neighbour pattern
@@ -257,8 +261,7 @@ def run_b200(args):
             bsr.assembleBilinearHost(op, coords_host, values_host)  # C ABI b2f_assemble_host; synchronises before returning
         else:
             coords_dev.copy_(coords_host, non_blocking=True)
-            bsr.assembleBilinear(op)
-            exchange.run()
+            step()
             values_host.copy_(mat.values(), non_blocking=True)
             torch.cuda.synchronize()
 
@@ -291,7 +294,9 @@ def run_b200(args):
     kernel_names = {0: "k_node_fan<LaplaceTet>", 1: "memset + k_cell_atomic<LaplaceTet>", 2: "memset + k_cell_atomic<LaplaceTet,warpagg>", 3: "k_node_fan<LaplaceTet>",
                     4: "k_node_gather_slots<LaplaceTet>"}
     # our kernels per step: the assembly kernel (+ pack and add kernels of the ghost exchange; NCCL's own kernels not counted)
-    launches_per_step = 1 + (2 if exchange is not None else 0)
+    # (overlapped step: the ghost-row tiles and the remaining rows are two launches of the assembly kernel)
+    overlapped = exchange is not None and not args.no_overlap
+    launches_per_step = (2 if overlapped else 1) + (2 if exchange is not None else 0)
 
     # --- CPU baseline: oracle port of the reference's legacy loop on this box's host cores (bounded sample)
     cpu = cpu_baseline(cells, coords, mat, args.cpu_cells)
@@ -304,7 +309,7 @@ def run_b200(args):
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
                    "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
                    "sparsity_build": "row-wise from node->cell lists" if stats["sparsity_by_lists"] else "global edge sort", "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
-                   "step_breakdown": breakdown,
+                   "step_breakdown": breakdown, "exchange_overlapped": overlapped,
                    "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
                    "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,
@@ -315,7 +320,7 @@ def run_b200(args):
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(coords_host.numel() * 8), "d2h_bytes_per_step": int(values_host.numel() * 8),
                 "ms_per_step": round(e2e_s * 1e3, 3),
                 "api": "b2f_assemble_host (pinned host coordinates in, values out)" if exchange is None else
-                       "pinned coordinates H2D + BSRFormat.assembleBilinear + b2f_ghost_exchange + values D2H, per rank, max over ranks"},
+                       "pinned coordinates H2D + b2f_assemble_exchange + values D2H, per rank, max over ranks"},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
     }
@@ -404,6 +409,7 @@ def main():
     ap.add_argument("--n", type=int, default=203, help="hexes per side of the per-GPU cube (203 -> 50.2M tets)")
     ap.add_argument("--variant", type=int, default=3, help="1 cell atomic, 2 cell atomic warp-aggregated, 3 node gather")
     ap.add_argument("--fan-mode", type=int, default=0, help="node gather walk on tets: 0 chosen from the plan, 1 select walk, 2 lockstep walk")
+    ap.add_argument("--no-overlap", action="store_true", help="N > 1: b2f_assemble then b2f_ghost_exchange in sequence instead of b2f_assemble_exchange")
     ap.add_argument("--sparsity-build", type=int, default=0, help="0 default (row-wise from the node->cell lists), 1 global edge sort (the reference's algorithm)")
     ap.add_argument("--cpu-cells", type=int, default=50_192_562, help="cells of the bounded CPU sample")
     args = ap.parse_args()

@@ -299,6 +299,12 @@ int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords
 int b2f_ghost_plan(b2f_handle h, void* nccl_comm, int32_t rank, int32_t world, const int32_t* node_owner_rank_host, const int64_t* node_global_id_host,
                    b2f_stream stream);
 int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream);
+/* One multi-GPU assembly step, b2f_assemble followed by b2f_ghost_exchange with the exchange hidden: the ghost rows are
+ * assembled first and travel on a high-priority stream of the handle while the remaining rows are assembled on `stream`;
+ * the received sums are added at the end, on `stream`.  Same values as the two calls in sequence (every row is written by
+ * one launch, the additions happen in the same order).  Falls back to the sequence when the operator accumulates, the
+ * default gather kernel is not in use, or the sent rows span more than a quarter of the local numbering. */
+int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm, b2f_stream stream);
 /* NCCL bootstrap helpers so a host without its own NCCL binding can create the communicator. */
 int b2f_nccl_unique_id(void* id128_out_host);
 int b2f_nccl_comm_init(const void* id128_host, int32_t rank, int32_t world, void** comm_out);
