@@ -604,38 +604,35 @@ int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm,
     for (cudaEvent_t& e : h->comm_events)
       B2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
-  // communication stream: the rows that travel, their pack, the grouped send/recv; caller's stream: every other row
-  // meanwhile, then (after joining) the addition of the received partial sums
-  auto assemble_rows = [&](long long first, long long count, cudaStream_t on) -> int {
+  // 1. the rows that travel; 2. their pack + send/recv on the communication stream; 3. every other row meanwhile;
+  // 4. the received partial sums are added once both are done
+  auto assemble_rows = [&](long long first, long long count, bool keep_counters) -> int {
     if (count <= 0)
       return B2F_OK;
     h->range_first_row = first;
     h->range_rows = count;
-    h->range_keep_counters = true;
-    const int rc = assemble(h, op, on);
+    h->range_keep_counters = keep_counters;
+    const int rc = assemble(h, op, s);
     h->range_rows = -1;
     h->range_first_row = 0;
     h->range_keep_counters = false;
     return rc;
   };
-  // The travelling rows are a small launch (less than a wave of CTAs): it runs on the communication stream, whose
-  // priority puts its CTAs first, next to the launch of the other rows instead of in front of it.
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, s));
-  B2F_CUDA(cudaEventRecord(h->comm_events[0], s)); // work queued earlier on the caller's stream comes first
+  int rc = P.total_send > 0 ? assemble_rows(lo, hi - lo, true) : B2F_OK; // a rank that only receives posts its receives at once
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(cudaEventRecord(h->comm_events[0], s));
   B2F_CUDA(cudaStreamWaitEvent(h->comm_stream, h->comm_events[0], 0));
-  int rc = B2F_OK;
-  if (P.total_send > 0)
-    rc = assemble_rows(lo, hi - lo, h->comm_stream);
-  if (rc == B2F_OK)
-    rc = ghost_send_recv(h, nccl_comm, h->comm_stream);
+  rc = ghost_send_recv(h, nccl_comm, h->comm_stream);
   if (P.total_send > 0) {
     if (rc == B2F_OK)
-      rc = assemble_rows(0, lo, s);
+      rc = assemble_rows(0, lo, true);
     if (rc == B2F_OK)
-      rc = assemble_rows(hi, nn - hi, s);
+      rc = assemble_rows(hi, nn - hi, true);
   }
   else if (rc == B2F_OK)
-    rc = assemble_rows(0, nn, s);
+    rc = assemble_rows(0, nn, true);
   // the caller's stream always rejoins the communication stream, also on an error path
   cudaError_t e1 = cudaEventRecord(h->comm_events[1], h->comm_stream);
   cudaError_t e2 = e1 == cudaSuccess ? cudaStreamWaitEvent(s, h->comm_events[1], 0) : e1;
