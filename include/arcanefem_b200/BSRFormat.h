@@ -193,6 +193,14 @@ class BSRFormat
   // assembleBilinear + BoundaryConditions{2D,3D}::applyConstantSourceToRhs(qdot, ...) (ArcaneFemFunctionsGpu.h:605,695) fused:
   // the source term is summed along the walk that forms the matrix rows.  Needs toLinearSystem() first (the rhs lives there).
   void assembleBilinearWithSource(const Operator& op, Real qdot) { check(b2f_assemble_with_source(m_h, &op.desc, qdot, m_stream)); }
+  // Multi-GPU (one rank per GPU, own cells + ghost-cell layer, b2f.h "Multi-GPU"): the plan once after computeSparsity(), then one
+  // call per assembly; the NCCL exchange of the ghost rows runs behind the assembly of the rows that do not travel.
+  void setGhostExchange(void* nccl_comm, int32_t rank, int32_t world, const int32_t* node_owner_rank, const int64_t* node_unique_id)
+  {
+    check(b2f_ghost_plan(m_h, nccl_comm, rank, world, node_owner_rank, node_unique_id, m_stream));
+    m_comm = nccl_comm;
+  }
+  void assembleBilinearAndExchange(const Operator& op) { check(b2f_assemble_exchange(m_h, &op.desc, m_comm, m_stream)); }
   // BSRFormat.h:414-430: hands the CSR view to the linear system (views stay valid until the next computeSparsity)
   void toLinearSystem(DoFLinearSystem& linear_system)
   {
@@ -210,6 +218,7 @@ class BSRFormat
  private:
   b2f_handle m_h = nullptr;
   b2f_stream m_stream;
+  void* m_comm = nullptr; // ncclComm_t of setGhostExchange
   BSRMatrix<NB_DOF> m_matrix;
 };
 
