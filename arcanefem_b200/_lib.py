@@ -86,6 +86,7 @@ PROTOTYPES = {
     "b2f_release_workspace": (C.c_int, [_H]),
     "b2f_assemble": (C.c_int, [_H, _P(OperatorDesc), _S]),
     "b2f_assemble_with_source": (C.c_int, [_H, _P(OperatorDesc), C.c_double, _S]),
+    "b2f_user_assemble_begin": (C.c_int, [_H, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t, _P(C.c_int32), _P(C.c_int32), _P(C.c_int64), _S]),
     "b2f_reset_values": (C.c_int, [_H, _S]),
     "b2f_get_bsr": (C.c_int, [_H, _P(BsrView)]),
     "b2f_to_csr": (C.c_int, [_H, _P(CsrView), _S]),

@@ -2,6 +2,7 @@
 #include <cstring>
 #include <fstream>
 #include "internal.h"
+#include "b2f/assemble_args.h"
 #include <algorithm>
 
 namespace b2f {
@@ -180,6 +181,30 @@ int b2f_assemble_with_source(b2f_handle h, const b2f_operator* op, double qdot, 
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_with_source: mesh coordinates are null");
   return assemble(h, op, (cudaStream_t)stream, &qdot);
+}
+
+int b2f_user_assemble_begin(b2f_handle h, int32_t nodes_per_cell, int32_t block_size, void* args_out, size_t args_size, int32_t* variant_out, int32_t* per_block_out,
+                            int64_t* nb_values_out, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!args_out || !variant_out || !per_block_out || !nb_values_out)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: null output");
+  if (args_size != sizeof(AssembleArgs))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: caller was compiled against another b2f::AssembleArgs (%zu bytes, library has %zu)",
+                args_size, sizeof(AssembleArgs));
+  if (nodes_per_cell != h->nv || block_size != h->bs)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: operator is for %d nodes per cell, block size %d; the handle has %d and %d", nodes_per_cell,
+                block_size, h->nv, h->bs);
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: mesh coordinates are null");
+  B2F_CUDA(cudaSetDevice(h->device));
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, (cudaStream_t)stream));
+  fill_assemble_args(h, static_cast<AssembleArgs*>(args_out));
+  *variant_out = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
+  *per_block_out = h->per_block ? 1 : 0;
+  *nb_values_out = h->nb_nz;
+  return B2F_OK;
 }
 
 int b2f_reset_values(b2f_handle h, b2f_stream stream)

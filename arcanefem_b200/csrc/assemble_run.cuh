@@ -10,27 +10,7 @@ template <class Op>
 inline int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stream, const double* qdot)
   {
     AssembleArgs A;
-    A.cell_node = h->mesh.cell_node;
-    A.coords = h->mesh.coords;
-    A.node_is_own = h->mesh.node_is_own;
-    A.cell_is_own = h->mesh.cell_is_own;
-    A.nb_cell = h->mesh.nb_cell;
-    A.nb_node = h->mesh.nb_node;
-    A.row_index = h->row_index.as<int32_t>();
-    A.columns = h->columns.as<int32_t>();
-    A.values = h->values.as<double>();
-    A.nc_ptr = h->nc_ptr.as<int32_t>();
-    A.nc_list = h->nc_list.as<uint32_t>();
-    A.nc_slots = h->nc_slots.as<uint32_t>();
-    A.slots_ok = h->slots_ok ? 1 : 0;
-    A.fan_ptr = h->fan_ptr.as<int32_t>();
-    A.fan_steps = h->fan_steps.as<uint32_t>();
-    A.fan_cell = h->fan_cell.as<uint32_t>();
-    A.fan_ok = h->fan_ok ? 1 : 0;
-    A.fan_lockstep = h->fan_lockstep ? 1 : 0;
-    for (int i = 0; i < 6; ++i)
-      A.tile_extents[i] = h->tile_extents[i];
-    A.counters = h->counters.as<unsigned long long>();
+    fill_assemble_args(h, &A);
     A.accumulate = accumulate;
     int variant = h->variant;
     if (variant == B2F_ASM_DEFAULT)

@@ -111,6 +111,8 @@ namespace b2f {
 // sparsity.cu
 int build_pattern(b2f_context_s* h, cudaStream_t stream);
 // assemble.cu
+struct AssembleArgs;
+void fill_assemble_args(const b2f_context_s* h, AssembleArgs* A); // pointers, plan and counters of the handle (accumulate = 0, whole matrix)
 int assemble(b2f_context_s* h, const b2f_operator* op, cudaStream_t stream, const double* qdot = nullptr); // qdot: fused constant source
 // boundary.cu
 int rhs_fill(b2f_context_s* h, double v, cudaStream_t s);

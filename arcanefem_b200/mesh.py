@@ -113,3 +113,52 @@ def kuhn_counts(N):
     nc = 6 * N ** 3
     e = 3 * N * (N + 1) ** 2 + 3 * N * N * (N + 1) + N ** 3
     return nc, nn, e, 2 * e + nn
+
+
+def kuhn_pattern(N):
+    """Closed-form BSR pattern of cube_kuhn(N) in the canonical order (diagonal first, then ascending neighbour ids):
+    (row_index int32 [Nn+1], columns int32 [nnzb]).  Two lattice nodes share an edge of the Kuhn triangulation iff their
+    index difference is a non-zero monotone 0/1 vector or its negative (7 + 7 offsets; interior rows have 15 entries,
+    SURVEY.md §8).  Independent of the edge-key algorithm (femutils/BSRFormat.h:602-744), so it pins the pattern at sizes
+    where a sequential sort-based restatement takes minutes."""
+    n1 = N + 1
+    nn = n1 ** 3
+    pos = [(dx, dy, dz) for dz in (0, 1) for dy in (0, 1) for dx in (0, 1) if (dx, dy, dz) != (0, 0, 0)]
+    offs = sorted(pos + [(-a, -b, -c) for a, b, c in pos], key=lambda d: d[0] + n1 * (d[1] + n1 * d[2]))
+    idx = np.arange(n1, dtype=np.int32)
+    k, j, i = np.meshgrid(idx, idx, idx, indexing="ij")
+    i, j, k = i.ravel(), j.ravel(), k.ravel()
+    node = np.arange(nn, dtype=np.int32)
+    cand = np.empty((nn, 15), dtype=np.int32)
+    keep = np.empty((nn, 15), dtype=bool)
+    cand[:, 0] = node
+    keep[:, 0] = True
+    for q, (dx, dy, dz) in enumerate(offs, start=1):
+        cand[:, q] = node + np.int32(dx + n1 * (dy + n1 * dz))
+        keep[:, q] = (i + dx >= 0) & (i + dx <= N) & (j + dy >= 0) & (j + dy <= N) & (k + dz >= 0) & (k + dz <= N)
+    row_index = np.zeros(nn + 1, dtype=np.int64)
+    np.cumsum(keep.sum(axis=1), out=row_index[1:])
+    return row_index.astype(np.int32), np.ascontiguousarray(cand[keep])
+
+
+def square_pattern(N):
+    """Closed-form BSR pattern of square(N), canonical order: neighbours at +-1, +-(N+1), +-(N+2) (the quad diagonal),
+    7 entries per interior row."""
+    n1 = N + 1
+    nn = n1 * n1
+    pos = [(1, 0), (0, 1), (1, 1)]
+    offs = sorted(pos + [(-a, -b) for a, b in pos], key=lambda d: d[0] + n1 * d[1])
+    idx = np.arange(n1, dtype=np.int32)
+    j, i = np.meshgrid(idx, idx, indexing="ij")
+    i, j = i.ravel(), j.ravel()
+    node = np.arange(nn, dtype=np.int32)
+    cand = np.empty((nn, 7), dtype=np.int32)
+    keep = np.empty((nn, 7), dtype=bool)
+    cand[:, 0] = node
+    keep[:, 0] = True
+    for q, (dx, dy) in enumerate(offs, start=1):
+        cand[:, q] = node + np.int32(dx + n1 * dy)
+        keep[:, q] = (i + dx >= 0) & (i + dx <= N) & (j + dy >= 0) & (j + dy <= N)
+    row_index = np.zeros(nn + 1, dtype=np.int64)
+    np.cumsum(keep.sum(axis=1), out=row_index[1:])
+    return row_index.astype(np.int32), np.ascontiguousarray(cand[keep])

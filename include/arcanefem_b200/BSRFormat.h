@@ -17,6 +17,9 @@
 #include <stdexcept>
 #include <string>
 #include "../b2f.h"
+#ifdef __CUDACC__
+#include "../b2f/user_operator.cuh" // element callbacks written by the caller (needs nvcc: the callback is device code)
+#endif
 
 namespace ArcaneFemB200 {
 
@@ -190,6 +193,17 @@ class BSRFormat
   }
   void computeSparsity() { check(b2f_compute_sparsity(m_h, m_stream)); } // BSRFormat.h:775-781
   void assembleBilinear(const Operator& op) { check(b2f_assemble(m_h, &op.desc, m_stream)); } // BSRFormat.h:1105-1111
+#ifdef __CUDACC__
+  // BSRFormat.h:1105-1111 with a callback of the caller, in the reference's shape (the full element matrix of one cell):
+  //   __device__ void f(long long cell, const double (&X)[NV][3], double (&Ke)[NB_DOF*NV][NB_DOF*NV])
+  // NV = 3 (Triangle3) or 4 (Tetraedron4) is a template argument here; the reference picks the callback from
+  // mesh->dimension() at run time (modules/poisson/FemModule.cc:255-286).  See include/b2f/user_operator.cuh.
+  template <int NV, class Function>
+  void assembleBilinear(const Function& compute_element_matrix, bool accumulate = false)
+  {
+    check(b2f::assemble_with_element_matrix<NV, NB_DOF>(m_h, compute_element_matrix, accumulate, (cudaStream_t)m_stream));
+  }
+#endif
   // assembleBilinear + BoundaryConditions{2D,3D}::applyConstantSourceToRhs(qdot, ...) (ArcaneFemFunctionsGpu.h:605,695) fused:
   // the source term is summed along the walk that forms the matrix rows.  Needs toLinearSystem() first (the rhs lives there).
   void assembleBilinearWithSource(const Operator& op, Real qdot) { check(b2f_assemble_with_source(m_h, &op.desc, qdot, m_stream)); }

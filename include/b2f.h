@@ -217,6 +217,14 @@ int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream);
  * no second sweep over the cells, bitwise reproducible.  Other variants (and the cell_is_own exchange mode, where a
  * rank only walks its own cells) run b2f_assemble followed by b2f_rhs_constant_source. */
 int b2f_assemble_with_source(b2f_handle h, const b2f_operator* op, double qdot, b2f_stream stream);
+/* User-written element operators: the C ABI cannot carry the reference's `template <class Function> assembleBilinear(Function)`
+ * (BSRFormat.h:1105-1111), so a caller that has its own element callback compiles include/b2f/user_operator.cuh with nvcc
+ * and calls b2f::assemble_with(handle, op, ...) there; that template fetches the kernel argument block of the handle through
+ * this entry (args_out = b2f::AssembleArgs*, args_size = sizeof of the caller's copy; a mismatch of it, of the arity or of the
+ * block size is refused) and launches the
+ * same kernels the built-in operators use.  Clears the handle's error counters on `stream`. */
+int b2f_user_assemble_begin(b2f_handle h, int32_t nodes_per_cell, int32_t block_size, void* args_out, size_t args_size, int32_t* variant_out,
+                            int32_t* per_block_out, int64_t* nb_values_out, b2f_stream stream);
 /* resetMatrixValues (BSRFormat.h:1120-1123). */
 int b2f_reset_values(b2f_handle h, b2f_stream stream);
 

@@ -20,40 +20,11 @@
 #include <type_traits>
 #include <utility>
 #include <cuda_runtime.h>
+#include "assemble_args.h"
 #include "element_ops.cuh"
 
 namespace b2f {
 
-struct AssembleArgs
-{
-  const int32_t* cell_node;
-  const double* coords;
-  const uint8_t* node_is_own; // may be null
-  const uint8_t* cell_is_own; // may be null; 0 = ghost cell (pattern only, not assembled)
-  long long nb_cell;
-  long long nb_node;
-  const int32_t* row_index; // nb_node + 1
-  const int32_t* columns;
-  double* values;
-  const int32_t* nc_ptr; // node -> cell list offsets, nb_node + 1
-  const uint32_t* nc_list; // entries: cell * 4 + local index of the node in the cell
-  const uint32_t* nc_slots; // per node->cell entry: column slots of the cell's other vertices, 10 bits each (see k_node_gather_slots)
-  int slots_ok; // nc_slots is usable (every row has at most 1023 blocks)
-  const int32_t* fan_ptr; // node -> fan-walk step offsets, nb_node + 1
-  const uint32_t* fan_steps; // one word per step (see k_node_fan)
-  const uint32_t* fan_cell; // cell id of every step (read by operators with per-cell data only)
-  int fan_ok; // the fan plan is usable
-  int tile_extents[6]; // largest tile of the plan: {blocks, steps or pairs} for 128-, 64- and 32-row tiles
-  unsigned long long* counters; // [0] columns not found, [1] gather tiles on the global fallback path
-  int accumulate;
-  int fan_lockstep = 0; // the step words are in the lockstep form (tets)
-  long long first_tile = 0; // fan kernel only: the launch covers the tiles [first_tile, first_tile + nb_tile) (host pipeline)
-  long long nb_tile = -1; // -1: every tile
-  double* rhs = nullptr; // fused constant source (fan kernel): rhs[row * BS] += rhs_factor * (sum of 6*volume / 2*area of the incident cells)
-  double rhs_factor = 0.0;
-};
-
-enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };
 
 // Scalar index of entry (i,j) of the x-th block of a block row that starts at block rb and holds k blocks
 // (femutils/BSRFormat.h:145-171).
@@ -1258,9 +1229,19 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
 // ---------------------------------------------------------------------------------------------------
 // Launch
 // ---------------------------------------------------------------------------------------------------
+// Operators that only offer prepare()/block() (no finish()/prepare_oriented() for the fan walk) declare
+// `static constexpr bool NO_FAN = true`: the node gather then runs on the slot-word / search kernels.
+template <class Op, class = void>
+struct uses_fan : std::true_type
+{};
+template <class Op>
+struct uses_fan<Op, std::enable_if_t<Op::NO_FAN>> : std::false_type
+{};
+
 template <class Op, bool PER_BLOCK>
 inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
 {
+  if constexpr (uses_fan<Op>::value)
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
     using C = FanCfg<Op>;
     constexpr bool CAN_ROW_SUM = Op::ROW_SUM_ZERO && Op::BS == 1;

@@ -160,3 +160,21 @@ def test_legacy_cpu_baseline_equals_bsr_assembly():
         v = np.zeros_like(ref)
         orc.legacy_assemble_csr(cells, coords, ri, co, v, threads=threads)
         assert np.abs(v - ref).max() <= 1e-13 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("N", [1, 2, 3, 6, 11])
+def test_closed_form_patterns_equal_the_edge_key_algorithm(N):
+    """gen.kuhn_pattern / gen.square_pattern (index arithmetic on the lattice) = the oracle's K1-K5 restatement
+    (femutils/BSRFormat.h:602-744), bit for bit.  The full-size GPU tests (tests/test_gpu_zz_fullsize.py) use the closed
+    forms, where the sequential edge-key sort would take minutes."""
+    cells, coords = gen.cube_kuhn(N)
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    r2, c2 = gen.kuhn_pattern(N)
+    np.testing.assert_array_equal(ri, r2)
+    np.testing.assert_array_equal(co, c2)
+    assert co.shape[0] == gen.kuhn_counts(N)[3]
+    cells, coords = gen.square(N)
+    ri, co = orc.build_pattern(cells, coords.shape[0])
+    r2, c2 = gen.square_pattern(N)
+    np.testing.assert_array_equal(ri, r2)
+    np.testing.assert_array_equal(co, c2)
