@@ -101,7 +101,9 @@ PROTOTYPES = {
     "b2f_clear_values": (C.c_int, [_H, _S]),
     "b2f_rhs_fill": (C.c_int, [_H, C.c_double, _S]),
     "b2f_rhs_constant_source": (C.c_int, [_H, C.c_double, _S]),
+    "b2f_rhs_nodal_source": (C.c_int, [_H, C.c_void_p, C.c_double, C.c_void_p, _S]),
     "b2f_rhs_neumann": (C.c_int, [_H, _P(Neumann), _S]),
+    "b2f_add_face_mass": (C.c_int, [_H, C.c_int64, C.c_void_p, C.c_double, _S]),
     "b2f_dirichlet_flag_penalty": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double, _S]),
     "b2f_dirichlet_flag_weak_penalty": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double, _S]),
     "b2f_dirichlet_flag_elimination": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_int32, _S]),

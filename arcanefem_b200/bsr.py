@@ -395,6 +395,16 @@ class BSRFormat:
     def applyConstantSourceToRhs(self, qdot):
         check(self._lib.b2f_rhs_constant_source(self._h, float(qdot), _stream()))
 
+    def applyNodalSourceToRhs(self, node_field, scale, node_skip=None):
+        """modules/heat/FemModule.cc:480-495: rhs[n] += (node_field[n] * scale) * |cell| / Nv (T_old / dt of the transient heat module)."""
+        check(self._lib.b2f_rhs_nodal_source(self._h, C.c_void_p(node_field.data_ptr()), float(scale),
+                                             C.c_void_p(node_skip.data_ptr()) if node_skip is not None else None, _stream()))
+
+    def addFaceMass(self, face_node, coefficient):
+        """Convection boundary term of the heat module (modules/heat/FemModule.cc:628-672,813-840): K += h * face mass matrix."""
+        nf = int(face_node.shape[0])
+        check(self._lib.b2f_add_face_mass(self._h, nf, C.c_void_p(face_node.data_ptr()) if nf else None, float(coefficient), _stream()))
+
     def applyNeumannToRhs(self, face_node, value=None, value_xyz=None, face_outside=None):
         bc = _lib.Neumann()
         bc.nb_face = int(face_node.shape[0])

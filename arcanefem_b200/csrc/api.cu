@@ -444,6 +444,18 @@ int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream)
   return rhs_constant_source(h, qdot, (cudaStream_t)stream);
 }
 
+int b2f_rhs_nodal_source(b2f_handle h, const double* node_field, double scale, const uint8_t* node_skip, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (!node_field)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_nodal_source: null node field");
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_nodal_source: mesh coordinates are null");
+  B2F_CUDA(cudaSetDevice(h->device));
+  return rhs_nodal_source(h, node_field, scale, node_skip, (cudaStream_t)stream);
+}
+
 int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
@@ -451,6 +463,20 @@ int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream)
   if (!bc || (bc->nb_face > 0 && !bc->face_node))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_neumann: null boundary condition / face list");
   return rhs_neumann(h, bc, (cudaStream_t)stream);
+}
+
+int b2f_add_face_mass(b2f_handle h, int64_t nb_face, const int32_t* face_node, double coefficient, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  if (h->bs != 1)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass needs block_size 1 (got %d)", h->bs);
+  if (nb_face < 0 || (nb_face > 0 && !face_node))
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass: bad face list");
+  if (!h->mesh.coords)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass: mesh coordinates are null");
+  B2F_CUDA(cudaSetDevice(h->device));
+  return add_face_mass(h, nb_face, face_node, coefficient, (cudaStream_t)stream);
 }
 
 int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream)

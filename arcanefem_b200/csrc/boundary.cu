@@ -1,7 +1,9 @@
 // boundary.cu — RHS and Dirichlet kernels on the device-resident system (sm_100a).
 //
 //   rhs_constant_source         BoundaryCondtionsHelpers::applyConstantSourceToRhsBase, femutils/ArcaneFemFunctionsGpu.h:402-429
+//   rhs_nodal_source            transient heat source (T_old / dt) * |cell| / NV, modules/heat/FemModule.cc:480-495
 //   rhs_neumann                 BoundaryConditions{2D,3D}::applyNeumannToRhs, :621-677 / :711-768 (geometry :88-197)
+//   add_face_mass               convection boundary term of the heat module, modules/heat/FemModule.cc:628-672,813-840
 //   dirichlet_flag_penalty      applyDirichletToNodeGroupViaPenalty, :434-456
 //   dirichlet_flag_elimination  applyDirichletToNodeGroupViaRowElimination<MODE>, :461-482
 //   dirichlet_apply             HypreDoFLinearSystemImpl::_applyRowElimination / _applyForcedValuesToLhs,
@@ -56,6 +58,39 @@ namespace {
         atomicAdd(rhs + (long long)n[k] * bs, value);
   }
 
+  // Nodal-field source of the transient heat module, modules/heat/FemModule.cc:480-495: rhs[n] += (field[n] * scale) * |cell| / NV
+  // for own nodes that are not skipped (m_node_is_temperature_fixed).  Triangles use the module's signed 2D area
+  // (_computeAreaTriangle3, :605-612); tets (3D twin) |det| / 6.
+  template <int NV>
+  __global__ void __launch_bounds__(256) k_rhs_nodal_source(const int32_t* __restrict__ cell_node, const double* __restrict__ coords, const uint8_t* __restrict__ own,
+                                                            const uint8_t* __restrict__ skip, const double* __restrict__ field,
+                                                            long long nb_cell, int bs, double scale, double* __restrict__ rhs)
+  {
+    const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= nb_cell) // every cell, ghost layer included, like the reference's allCells() loop; only own nodes receive
+      return;
+    int32_t n[NV];
+    load_cell_nodes<NV>(cell_node, cell, n);
+    double X[NV][3];
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      load_xyz(coords, n[k], X[k]);
+    double domain;
+    if (NV == 3)
+      domain = 0.5 * ((X[1][0] - X[0][0]) * (X[2][1] - X[0][1]) - (X[2][0] - X[0][0]) * (X[1][1] - X[0][1]));
+    else {
+      const double ax = X[1][0] - X[0][0], ay = X[1][1] - X[0][1], az = X[1][2] - X[0][2];
+      const double bx = X[2][0] - X[0][0], by = X[2][1] - X[0][1], bz = X[2][2] - X[0][2];
+      const double dx = X[NV - 1][0] - X[0][0], dy = X[NV - 1][1] - X[0][1], dz = X[NV - 1][2] - X[0][2];
+      const double c2x = by * dz - bz * dy, c2y = bz * dx - bx * dz, c2z = bx * dy - by * dx;
+      domain = fabs(ax * c2x + ay * c2y + az * c2z) / 6.0;
+    }
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      if ((own == nullptr || own[n[k]]) && (skip == nullptr || !skip[n[k]]))
+        atomicAdd(rhs + (long long)n[k] * bs, (field[n[k]] * scale) * domain / NV);
+  }
+
   template <int NVF>
   __global__ void __launch_bounds__(256) k_rhs_neumann(b2f_neumann bc, const double* __restrict__ coords, const uint8_t* __restrict__ own, int bs, double* __restrict__ rhs)
   {
@@ -108,6 +143,53 @@ namespace {
     for (int k = 0; k < NVF; ++k)
       if (own == nullptr || own[n[k]])
         atomicAdd(rhs + (long long)n[k] * bs, contrib);
+  }
+
+  // Convection (Robin) term of the heat module, modules/heat/FemModule.cc:628-672 + :813-840: per boundary face
+  // K[a,b] += h * |face| / (NVF (NVF + 1)) * (1 + delta_ab) over the face's nodes (edges: h L/6 [[2,1],[1,2]], L from x and y
+  // only like _computeEdgeLength2 :617-623; triangles, the 3D twin: h A/12 (1 + delta)).  Own rows only.  Surface-sized: one
+  // thread per face, NVF^2 fp64 REDs, column slot by search in the sorted row.  BS = 1 (both value layouts coincide).
+  template <int NVF>
+  __global__ void __launch_bounds__(256) k_add_face_mass(long long nb_face, const int32_t* __restrict__ face_node, double h, const double* __restrict__ coords,
+                                                         const uint8_t* __restrict__ own, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
+                                                         double* __restrict__ values, unsigned long long* __restrict__ counters)
+  {
+    const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nb_face)
+      return;
+    int32_t n[NVF];
+    double X[NVF][3];
+#pragma unroll
+    for (int k = 0; k < NVF; ++k) {
+      n[k] = face_node[f * NVF + k];
+      load_xyz(coords, n[k], X[k]);
+    }
+    double off;
+    if (NVF == 2) {
+      const double ex = X[1][0] - X[0][0], ey = X[1][1] - X[0][1];
+      off = (sqrt(ex * ex + ey * ey) / 3.0) * 0.5 * h;
+    }
+    else {
+      const double ax = X[1][0] - X[0][0], ay = X[1][1] - X[0][1], az = X[1][2] - X[0][2];
+      const double bx = X[NVF - 1][0] - X[0][0], by = X[NVF - 1][1] - X[0][1], bz = X[NVF - 1][2] - X[0][2];
+      const double cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+      off = ((sqrt(cx * cx + cy * cy + cz * cz) / 2.0) / 12.0) * h;
+    }
+#pragma unroll
+    for (int a = 0; a < NVF; ++a) {
+      if (own != nullptr && !own[n[a]])
+        continue;
+      const int32_t rb = __ldg(row_index + n[a]);
+      const int k = __ldg(row_index + n[a] + 1) - rb;
+#pragma unroll
+      for (int b = 0; b < NVF; ++b) {
+        const int x = (a == b) ? 0 : find_slot(columns + rb, k, n[b]);
+        if (x < 0)
+          atomicAdd(counters, 1ull);
+        else
+          atomicAdd(values + rb + x, (a == b) ? off * 2.0 : off);
+      }
+    }
   }
 
   __global__ void k_flag_penalty(const int32_t* __restrict__ ids, long long n, const uint8_t* __restrict__ own, int bs, int dof_index, double value, double penalty, int weak,
@@ -283,6 +365,21 @@ int rhs_constant_source(b2f_context_s* h, double qdot, cudaStream_t s)
   return B2F_OK;
 }
 
+int rhs_nodal_source(b2f_context_s* h, const double* node_field, double scale, const uint8_t* node_skip, cudaStream_t s)
+{
+  const long long nc = h->mesh.nb_cell;
+  if (nc == 0)
+    return B2F_OK;
+  if (h->nv == 3)
+    k_rhs_nodal_source<3><<<grid_for(nc, 256), 256, 0, s>>>(h->mesh.cell_node, h->mesh.coords, h->mesh.node_is_own, node_skip, node_field, nc, h->bs,
+                                                           scale, h->rhs.as<double>());
+  else
+    k_rhs_nodal_source<4><<<grid_for(nc, 256), 256, 0, s>>>(h->mesh.cell_node, h->mesh.coords, h->mesh.node_is_own, node_skip, node_field, nc, h->bs,
+                                                           scale, h->rhs.as<double>());
+  B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
 int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s)
 {
   if (bc->nb_face == 0)
@@ -291,6 +388,21 @@ int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s)
     k_rhs_neumann<2><<<grid_for(bc->nb_face, 256), 256, 0, s>>>(*bc, h->mesh.coords, h->mesh.node_is_own, h->bs, h->rhs.as<double>());
   else
     k_rhs_neumann<3><<<grid_for(bc->nb_face, 256), 256, 0, s>>>(*bc, h->mesh.coords, h->mesh.node_is_own, h->bs, h->rhs.as<double>());
+  B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
+int add_face_mass(b2f_context_s* h, int64_t nb_face, const int32_t* face_node, double coefficient, cudaStream_t s)
+{
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long), s));
+  if (nb_face == 0)
+    return B2F_OK;
+  if (h->mesh.dim == 2)
+    k_add_face_mass<2><<<grid_for(nb_face, 256), 256, 0, s>>>(nb_face, face_node, coefficient, h->mesh.coords, h->mesh.node_is_own, h->row_index.as<int32_t>(),
+                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>());
+  else
+    k_add_face_mass<3><<<grid_for(nb_face, 256), 256, 0, s>>>(nb_face, face_node, coefficient, h->mesh.coords, h->mesh.node_is_own, h->row_index.as<int32_t>(),
+                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>());
   B2F_CUDA(cudaGetLastError());
   return B2F_OK;
 }

@@ -119,6 +119,8 @@ int rhs_fill(b2f_context_s* h, double v, cudaStream_t s);
 int clear_values(b2f_context_s* h, cudaStream_t s);
 int rhs_constant_source(b2f_context_s* h, double qdot, cudaStream_t s);
 int rhs_neumann(b2f_context_s* h, const b2f_neumann* bc, cudaStream_t s);
+int rhs_nodal_source(b2f_context_s* h, const double* node_field, double scale, const uint8_t* node_skip, cudaStream_t s);
+int add_face_mass(b2f_context_s* h, int64_t nb_face, const int32_t* face_node, double coefficient, cudaStream_t s);
 int dirichlet_flag_penalty(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, double penalty, int weak, cudaStream_t s);
 int dirichlet_flag_elimination(b2f_context_s* h, const int32_t* ids, int64_t n, int dof_index, double value, int mode, cudaStream_t s);
 int dirichlet_apply(b2f_context_s* h, cudaStream_t s);

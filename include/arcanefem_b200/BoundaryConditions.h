@@ -68,6 +68,20 @@ namespace BoundaryConditionsND {
     bc.value_x = vx; bc.value_y = vy; bc.value_z = vz;
     check(b2f_rhs_neumann(ls.handle(), &bc, stream));
   }
+  // Transient heat module (modules/heat/FemModule.cc; CPU-only in the reference).  Source (T_old / dt) * |cell| / Nv, :480-495:
+  inline void applyNodalSourceToRhs(DoFLinearSystem& ls, const Real* node_field, Real scale, const uint8_t* node_skip = nullptr, b2f_stream stream = nullptr)
+  {
+    check(b2f_rhs_nodal_source(ls.handle(), node_field, scale, node_skip, stream));
+  }
+  // Convection boundary: matrix term h * face mass (_assembleBilinearOperatorEDGE2, :628-672,813-840) and rhs h * Text * |face| / Nvf (:517-537)
+  inline void applyConvectionToMatrix(DoFLinearSystem& ls, const FaceGroup& g, Real h, b2f_stream stream = nullptr)
+  {
+    check(b2f_add_face_mass(ls.handle(), g.n, g.face_node, h, stream));
+  }
+  inline void applyConvectionToRhs(DoFLinearSystem& ls, const FaceGroup& g, Real h, Real Text, b2f_stream stream = nullptr)
+  {
+    applyNeumannToRhs(ls, g, h * Text, stream);
+  }
 } // namespace BoundaryConditionsND
 namespace BoundaryConditions2D = BoundaryConditionsND;
 namespace BoundaryConditions3D = BoundaryConditionsND;

@@ -273,8 +273,19 @@ int b2f_clear_values(b2f_handle h, b2f_stream stream);
 int b2f_rhs_fill(b2f_handle h, double value, b2f_stream stream);
 /* BoundaryConditions{2D,3D}::applyConstantSourceToRhs (ArcaneFemFunctionsGpu.h:402-429,605,695). */
 int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream);
+/* Source term of the transient heat module (modules/heat/FemModule.cc:480-495): rhs[dof(n,0)] += (node_field[n] * scale) * |cell| / Nv
+ * over the cells around every own node that node_skip (m_node_is_temperature_fixed; may be NULL) does not exclude;
+ * node_field = last step's temperature, scale = 1/dt.  Triangles use the module's signed 2D area (:605-612). */
+int b2f_rhs_nodal_source(b2f_handle h, const double* node_field, double scale, const uint8_t* node_skip, b2f_stream stream);
 /* BoundaryConditions{2D,3D}::applyNeumannToRhs (ArcaneFemFunctionsGpu.h:621-677,711-768). */
 int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream);
+/* Convection (Robin) boundary term of the heat module, modules/heat/FemModule.cc:628-672 (_computeElementMatrixEDGE2) scattered
+ * by _assembleBilinearOperatorEDGE2 (:813-840): for every boundary face, K[a,b] += coefficient * |face| / (Nvf (Nvf+1)) * (1 + delta_ab)
+ * over the face's nodes, own rows only - edges of a 2D mesh: h L/6 [[2,1],[1,2]]; triangles of a 3D mesh (twin, not in the
+ * reference): h A/12 (1 + delta).  face_node: [nb_face * dim] device node ids.  Added to the current values (call after
+ * b2f_assemble); block_size 1.  b2f_stats.columns_not_found counts face edges that are not in the pattern.  The matching
+ * right-hand side h * Text * |face| / Nvf is b2f_rhs_neumann with value = h * Text (modules/heat/FemModule.cc:432-470). */
+int b2f_add_face_mass(b2f_handle h, int64_t nb_face, const int32_t* face_node, double coefficient, b2f_stream stream);
 /* applyDirichletToNodeGroupViaPenalty (ArcaneFemFunctionsGpu.h:434-456). */
 int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n, int32_t dof_index, double value, double penalty, b2f_stream stream);
 /* WeakPenalty (modules/testlab/FemModule.cc:687-717; CPU-only in the reference): a_ii += P at b2f_dirichlet_apply, rhs_i = P*g. */

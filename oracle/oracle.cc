@@ -546,6 +546,32 @@ void orc_rhs_constant_source(int nv, int bs, double qdot, int64_t nb_cell, const
 }
 
 // ---------------------------------------------------------------------------
+// RHS: nodal-field source of the transient heat module, modules/heat/FemModule.cc:480-495:
+// rhs[dof(node,0)] += (T_old[node] / dt) * area / 3 over every cell, for own nodes whose temperature is not fixed.
+// The area is the module's own signed 2D formula (_computeAreaTriangle3, :605-612); nv = 4 is the 3D twin (|det| / 6).
+// scale = 1 / dt, node_skip = m_node_is_temperature_fixed (may be null).
+// ---------------------------------------------------------------------------
+void orc_rhs_nodal_source(int nv, int bs, double scale, const double* node_field, const uint8_t* node_skip, int64_t nb_cell, const int32_t* cell_node,
+                          const double* coords, const uint8_t* node_is_own, double* rhs)
+{
+  for (int64_t cell = 0; cell < nb_cell; ++cell) {
+    const int32_t* cn = cell_node + cell * nv;
+    double domain;
+    if (nv == 3) {
+      R3 m0 = vtx(coords, cn[0]), m1 = vtx(coords, cn[1]), m2 = vtx(coords, cn[2]);
+      domain = 0.5 * ((m1.x - m0.x) * (m2.y - m0.y) - (m2.x - m0.x) * (m1.y - m0.y));
+    }
+    else
+      domain = volume_tetra4(cn, coords);
+    for (int a = 0; a < nv; ++a) {
+      if ((node_is_own && !node_is_own[cn[a]]) || (node_skip && node_skip[cn[a]]))
+        continue;
+      rhs[(int64_t)cn[a] * bs] += (node_field[cn[a]] * scale) * domain / nv;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // RHS: Neumann.  2D femutils/ArcaneFemFunctionsGpu.h:621-677 with computeLengthFace :132-138 and
 // computeNormalFace :149-165 ; 3D :711-768 with computeAreaTria :88-96 and computeNormalTriangle
 // :176-197.  face_outside[f] restates FaceInfoListView::isSubDomainBoundaryOutside (NULL = all true).
@@ -593,6 +619,48 @@ void orc_rhs_neumann(int nvf, int bs, int has_value, double value, double vx, do
       rhs[(int64_t)fn[a] * bs] += contrib;
     }
   }
+}
+
+// ---------------------------------------------------------------------------
+// Convection (Robin) boundary term of the heat module: modules/heat/FemModule.cc:628-672 (_computeElementMatrixEDGE2:
+// bT = L/3, b = 1/2, diagonal doubled, times h  =>  h * L/6 * [[2,1],[1,2]], L from x and y only, :617-623) scattered by
+// _assembleBilinearOperatorEDGE2 :813-840 into own rows.  nvf = 3 is the 3D twin (not in the reference):
+// h * A/12 * (1 + delta_ab) over the triangle's nodes, A by the 3D cross product.  BS = 1.
+// Returns the number of (row, col) pairs missing from the pattern.
+// ---------------------------------------------------------------------------
+int64_t orc_add_face_mass(int nvf, double h, int64_t nb_face, const int32_t* face_node, const double* coords, const uint8_t* node_is_own,
+                          const int32_t* row_index, const int32_t* columns, double* values)
+{
+  int64_t not_found = 0;
+  for (int64_t f = 0; f < nb_face; ++f) {
+    const int32_t* fn = face_node + f * nvf;
+    double measure;
+    if (nvf == 2) {
+      R3 m0 = vtx(coords, fn[0]), m1 = vtx(coords, fn[1]);
+      measure = std::sqrt((m1.x - m0.x) * (m1.x - m0.x) + (m1.y - m0.y) * (m1.y - m0.y));
+    }
+    else {
+      R3 p0 = vtx(coords, fn[0]), p1 = vtx(coords, fn[1]), p2 = vtx(coords, fn[2]);
+      measure = normL2(cross(sub(p1, p0), sub(p2, p0))) / 2.0;
+    }
+    const double off = (nvf == 2) ? (measure / 3.0) * 0.5 * h : (measure / 12.0) * h;
+    for (int a = 0; a < nvf; ++a) {
+      if (node_is_own && !node_is_own[fn[a]])
+        continue;
+      for (int b = 0; b < nvf; ++b) {
+        const double v = (a == b) ? off * 2.0 : off;
+        int64_t idx = -1;
+        for (int32_t q = row_index[fn[a]]; q < row_index[fn[a] + 1]; ++q)
+          if (columns[q] == fn[b])
+            idx = q;
+        if (idx < 0)
+          ++not_found;
+        else
+          values[idx] += v;
+      }
+    }
+  }
+  return not_found;
 }
 
 // ---------------------------------------------------------------------------

@@ -33,6 +33,7 @@ def lib():
         _LIB.orc_legacy_assemble_csr.restype = C.c_double
         _LIB.orc_assemble_cellwise.restype = C.c_int64
         _LIB.orc_assemble_nodewise.restype = C.c_int64
+        _LIB.orc_add_face_mass.restype = C.c_int64
         _LIB.orc_num_threads.restype = C.c_int
     return _LIB
 
@@ -111,6 +112,14 @@ def rhs_constant_source(cell_node, coords, bs, qdot, rhs, node_is_own=None):
     return rhs
 
 
+def rhs_nodal_source(cell_node, coords, bs, scale, node_field, rhs, node_skip=None, node_is_own=None):
+    """modules/heat/FemModule.cc:480-495: rhs[n] += (field[n] * scale) * |cell| / Nv (signed 2D area like the module)."""
+    cell_node = np.ascontiguousarray(cell_node, dtype=np.int32)
+    nc, nv = cell_node.shape
+    lib().orc_rhs_nodal_source(C.c_int(nv), C.c_int(bs), C.c_double(scale), _p(np.ascontiguousarray(node_field, dtype=np.float64)), _p(node_skip), C.c_int64(nc),
+                               _p(cell_node), _p(coords), _p(node_is_own), _p(rhs))
+
+
 def rhs_neumann(face_node, coords, bs, rhs, value=None, value_xyz=(0.0, 0.0, 0.0), face_outside=None, node_is_own=None):
     face_node = np.ascontiguousarray(face_node, dtype=np.int32)
     nf, nvf = face_node.shape
@@ -118,6 +127,14 @@ def rhs_neumann(face_node, coords, bs, rhs, value=None, value_xyz=(0.0, 0.0, 0.0
                           C.c_double(value_xyz[0]), C.c_double(value_xyz[1]), C.c_double(value_xyz[2]), C.c_int64(nf), _p(face_node), _p(face_outside),
                           _p(coords), _p(node_is_own), _p(rhs))
     return rhs
+
+
+def add_face_mass(face_node, coords, h, row_index, columns, values, node_is_own=None):
+    """Convection boundary term (modules/heat/FemModule.cc:628-672,813-840), BS = 1; returns the not-found count."""
+    face_node = np.ascontiguousarray(face_node, dtype=np.int32)
+    nf, nvf = face_node.shape
+    return int(lib().orc_add_face_mass(C.c_int(nvf), C.c_double(h), C.c_int64(nf), _p(face_node), _p(coords), _p(node_is_own), _p(row_index), _p(columns),
+                                       _p(values)))
 
 
 def dirichlet_flag_penalty(bs, dof_index, value, penalty, node_ids, forced_info, forced_value, rhs, node_is_own=None, weak=False):

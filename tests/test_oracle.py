@@ -178,3 +178,45 @@ def test_closed_form_patterns_equal_the_edge_key_algorithm(N):
     r2, c2 = gen.square_pattern(N)
     np.testing.assert_array_equal(ri, r2)
     np.testing.assert_array_equal(co, c2)
+
+
+@pytest.mark.parametrize("mesh_name", ["square9_shuffled", "square20", "cube5", "cube7_shuffled"])
+def test_heat_boundary_and_transient_terms_against_numpy(mesh_name):
+    """Convection face term (modules/heat/FemModule.cc:628-672,813-840) and the (T_old / dt) source (:480-495), restated
+    with numpy from the closed forms h |f| / (Nvf (Nvf + 1)) (1 + delta) and field * lumped mass."""
+    dim, cells, coords = MESHES[mesh_name]()
+    nn = coords.shape[0]
+    ri, co = orc.build_pattern(cells, nn)
+    faces = gen.boundary_faces(cells, coords, 0, coords[:, 0].max())
+    assert faces.shape[0] > 0
+    vals = np.zeros(co.shape[0])
+    assert orc.add_face_mass(faces, coords, 3.5, ri, co, vals) == 0
+    rows = np.repeat(np.arange(nn), np.diff(ri))
+    got = sp.csr_matrix((vals, (rows, co)), shape=(nn, nn)).toarray()
+    ref = np.zeros((nn, nn))
+    nvf = faces.shape[1]
+    for f in faces:
+        X = coords[f]
+        meas = np.hypot(*(X[1] - X[0])[:2]) if nvf == 2 else 0.5 * np.linalg.norm(np.cross(X[1] - X[0], X[2] - X[0]))
+        ref[np.ix_(f, f)] += 3.5 * meas / (nvf * (nvf + 1)) * (np.ones((nvf, nvf)) + np.eye(nvf))
+    np.testing.assert_allclose(got, ref, rtol=1e-13, atol=1e-15 * np.abs(ref).max())
+    # a face edge outside the pattern is reported, not written anywhere
+    far = np.array([[0, nn - 1] + ([1] if nvf == 3 else [])], dtype=np.int32)
+    before = vals.copy()
+    assert orc.add_face_mass(far, coords, 1.0, ri, co, vals) > 0
+    assert np.count_nonzero(vals != before) <= nvf * nvf
+    # transient source: field * scale * (sum of |cell| / Nv around the node), fixed nodes skipped
+    rng = np.random.default_rng(3)
+    field = rng.uniform(280.0, 320.0, size=nn)
+    skip = (rng.uniform(size=nn) < 0.2).astype(np.uint8)
+    rhs = np.zeros(nn)
+    orc.rhs_nodal_source(cells, coords, 1, 10.0, field, rhs, node_skip=skip)
+    X = coords[cells]
+    if dim == 2:
+        e1, e2 = X[:, 1] - X[:, 0], X[:, 2] - X[:, 0]
+        meas = 0.5 * (e1[:, 0] * e2[:, 1] - e2[:, 0] * e1[:, 1])
+    else:
+        meas = np.abs(np.einsum("ij,ij->i", X[:, 1] - X[:, 0], np.cross(X[:, 2] - X[:, 0], X[:, 3] - X[:, 0]))) / 6.0
+    lumped = np.zeros(nn)
+    np.add.at(lumped, cells.ravel(), np.repeat(meas / cells.shape[1], cells.shape[1]))
+    np.testing.assert_allclose(rhs, np.where(skip, 0.0, field * 10.0 * lumped), rtol=1e-12, atol=1e-13 * np.abs(rhs).max())
