@@ -139,6 +139,45 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
+def path_breakdown(torch, fem, gen, bsr, op, coords, sparsity_ms, assembly_ms, reps=5):
+    """CUDA-event time of every stage of the hot path on the bench workload (ms, mean of `reps` after one warm-up):
+    right-hand side, Dirichlet (penalty on the z = 0 plane: flagging + the solve() prelude), CSR view, own-row extraction for
+    HYPRE_IJMatrixSetValues, SpMV check, and the matrix + source fused in one walk."""
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn):
+        fn()
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(reps):
+            fn()
+        ev1.record()
+        torch.cuda.synchronize()
+        return round(ev0.elapsed_time(ev1) / reps, 4)
+
+    ls = fem.DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    ls.clearValues()
+    group = torch.as_tensor(gen.boundary_nodes(coords, 2, 0.0)).cuda()
+    x = torch.ones(coords.shape[0], dtype=torch.float64, device="cuda")
+    y = torch.empty_like(x)
+    out = {"sparsity": round(sparsity_ms, 3), "assembly": round(assembly_ms, 4)}
+    out["assembly_with_fused_source"] = timed(lambda: bsr.assembleBilinearWithSource(op, 5.5))
+    out["rhs_constant_source"] = timed(lambda: bsr.applyConstantSourceToRhs(5.5))
+    out["to_csr"] = timed(lambda: bsr.matrix().toCsr())
+    out["spmv"] = timed(lambda: bsr.spmv(x, y))
+
+    def dirichlet():
+        bsr.applyDirichletViaPenalty(group, 0.5, 1.0e30)
+        ls.applyDirichlet()
+
+    out["dirichlet_penalty_flag_and_apply"] = timed(dirichlet)
+    out["hypre_ij_own_rows"] = timed(lambda: bsr.toHypreIJ())
+    out["dirichlet_nodes"] = int(group.numel())
+    out["total_once"] = round(out["sparsity"] + out["assembly_with_fused_source"] + out["dirichlet_penalty_flag_and_apply"] + out["to_csr"] + out["hypre_ij_own_rows"], 3)
+    return out
+
+
 def run_b200(args):
     import torch
     import arcanefem_b200 as fem
@@ -281,6 +320,15 @@ def run_b200(args):
     e2e_value = own_nnz / e2e_s / 1e9
     checksum = float(values_host.sum().item())
 
+    # --- the rest of the path, each stage on its own (t_sparsity, t_dirichlet, t_tocsr, t_total); reported in
+    # config.path_breakdown_ms, outside the timed region of `value` (single GPU only)
+    path = None
+    if world == 1:
+        try:
+            path = path_breakdown(torch, fem, gen, bsr, op, coords, sparsity_ms, ms_step)
+        except Exception as e:  # a reporting extra must never cost the bench line
+            path = {"error": f"{type(e).__name__}: {e}"}
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -309,7 +357,7 @@ def run_b200(args):
                    "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
                    "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
                    "sparsity_build": "row-wise from node->cell lists" if stats["sparsity_by_lists"] else "global edge sort", "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
-                   "step_breakdown": breakdown, "exchange_overlapped": overlapped,
+                   "step_breakdown": breakdown, "exchange_overlapped": overlapped, "path_breakdown_ms": path,
                    "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
                    "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,

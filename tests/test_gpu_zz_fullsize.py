@@ -89,7 +89,7 @@ def test_config2_poisson3d_50m_tets():
     # constants are in the null space of the Laplacian: every row sums to zero up to rounding of its own entries
     y = bsr.spmv(torch.ones(counts[1], dtype=torch.float64, device="cuda"))
     scale = torch.zeros(counts[1], dtype=torch.float64, device="cuda").scatter_reduce_(0, owner, got.abs(), "amax")
-    assert bool((y.abs() <= 1e-13 * scale).all())
+    assert bool((y.abs() <= 1e-12 * scale).all())
     _assert_symmetric(bsr, counts[1], 1)
     # bitwise repeatable (no atomics on the default path)
     bsr.assembleBilinear(fem.Operator.laplace())
