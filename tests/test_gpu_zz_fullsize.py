@@ -2,7 +2,8 @@
 row elimination) and #4 (heat 2D, 50 M triangles, re-assembled per time step), through the C ABI on one B200.
 
 At these sizes the oracle's sequential value assembly still runs in 6-17 s, so the values are compared entry by entry
-(1e-12 relative with the row-scale floor of tests/util.py, evaluated on the device); the pattern is compared bit for bit
+(1e-12 relative with the row-scale floor of tests/util.py, evaluated on the device; the few entries of almost flat
+tetrahedra that no fp64 formula resolves to 1e-12 are settled against extended precision, see _adjudicate); the pattern is compared bit for bit
 with the closed-form lattice pattern (gen.kuhn_pattern / gen.square_pattern, pinned on the oracle's edge-key algorithm at
 small sizes by tests/test_oracle.py).  On top: the size-independent properties of the operators - constants in the null
 space, symmetry, bitwise repeatability, agreement of the atomic and the gather kernels, exact Dirichlet rows.
@@ -28,18 +29,67 @@ def _row_owner(ri, bs):
     return torch.repeat_interleave(torch.arange(counts.shape[0], device="cuda"), counts)
 
 
-def _assert_close_on_device(got, ref, owner, nb_row, what, rtol=RTOL):
-    """tests/util.py:assert_values_close on the device: |d| <= rtol * max(|a|, |b|, max |ref| over the block row)."""
+def _violations_on_device(got, ref, owner, nb_row, what, rtol=RTOL):
+    """tests/util.py:assert_values_close evaluated on the device: returns the (host) indices of the entries with
+    |d| > rtol * max(|a|, |b|, max |ref| over the block row)."""
     assert got.shape == ref.shape, (got.shape, ref.shape)
     assert bool(torch.isfinite(got).all()), f"{what}: non-finite entries"
     scale = torch.zeros(nb_row, dtype=torch.float64, device="cuda").scatter_reduce_(0, owner, ref.abs(), "amax")
     tol = rtol * torch.maximum(torch.maximum(got.abs(), ref.abs()), scale[owner])
-    d = (got - ref).abs()
-    bad = d > tol
-    nbad = int(bad.sum())
-    if nbad:
-        i = int(torch.argmax(d / tol.clamp_min(1e-300)))
-        raise AssertionError(f"{what}: {nbad} of {d.numel()} entries differ; worst idx {i}: got {got[i].item()!r} ref {ref[i].item()!r}")
+    return torch.nonzero((got - ref).abs() > tol).flatten().cpu().numpy()
+
+
+def _ke_extended(X, kind, p):
+    """Element matrix of one tetrahedron in x87 extended precision (64-bit mantissa) from the exact fp64 vertex coordinates:
+    true gradients G = cofactors / det, Laplace V G G^T, isotropic elasticity V (lambda G_ai G_bj + mu G_aj G_bi + mu d_ij G_a.G_b)."""
+    X = X.astype(np.longdouble)
+    e = X[1:] - X[0]
+    g = np.zeros((4, 3), np.longdouble)
+    g[1], g[2], g[3] = np.cross(e[1], e[2]), np.cross(e[2], e[0]), np.cross(e[0], e[1])
+    det = np.dot(e[0], g[1])
+    G = g / det
+    G[0] = -(G[1] + G[2] + G[3])
+    vol = abs(det) / 6
+    if kind == "laplace":
+        return vol * (G @ G.T)
+    lam, mu = np.longdouble(p["lambda_"]), np.longdouble(p["mu2"]) / 2
+    K = np.zeros((12, 12), np.longdouble)
+    for a in range(4):
+        for b in range(4):
+            dab = np.dot(G[a], G[b])
+            for i in range(3):
+                for j in range(3):
+                    K[3 * a + i, 3 * b + j] = vol * (lam * G[a, i] * G[b, j] + mu * G[a, j] * G[b, i] + (mu * dab if i == j else 0))
+    return K
+
+
+def _adjudicate(bad, got, ref, cells, coords, ri, co, bs, kind, p, what, max_fraction=1e-5):
+    """Entries outside the 1e-12 rule.  On the jittered 50 M-tet cube a handful of tetrahedra are almost flat (|det| thousands of
+    times below nominal): cancellation in the determinant alone costs them kappa * eps ~ 1e-12 relative in ANY fp64 formula,
+    the oracle's included, so neither side is the truth there.  Such entries are recomputed in extended precision (exact to
+    ~1e-16 here) and the CUDA value must be within 1e-12 of it or no further from it than 4x the oracle's own error.  They
+    must stay rare (< 1e-5 of the entries)."""
+    assert np.finfo(np.longdouble).eps < 1e-18, "needs x87 extended precision"
+    assert bad.size <= max_fraction * ref.numel(), f"{what}: {bad.size} of {ref.numel()} entries differ"
+    if bad.size == 0:
+        return 0
+    bs2 = bs * bs
+    r = np.searchsorted(ri.astype(np.int64) * bs2, bad, side="right") - 1
+    rb, k = ri[r].astype(np.int64), (ri[r + 1] - ri[r]).astype(np.int64)
+    local = bad - rb * bs2
+    i, rem = local // (bs * k), local % (bs * k)  # per-row layout, femutils/BSRFormat.h:162
+    x, j = rem // bs, rem % bs
+    c = co[rb + x]
+    sub = cells[np.isin(cells, np.unique(r)).any(axis=1)]
+    g, f = got[torch.as_tensor(bad).cuda()].cpu().numpy(), ref[torch.as_tensor(bad).cuda()].cpu().numpy()
+    for q in range(bad.size):
+        exact = np.longdouble(0)
+        for cn in sub[(sub == r[q]).any(axis=1) & (sub == c[q]).any(axis=1)]:
+            a, b = int(np.nonzero(cn == r[q])[0][0]), int(np.nonzero(cn == c[q])[0][0])
+            exact += _ke_extended(coords[cn], kind, p)[bs * a + i[q], bs * b + j[q]]
+        err_got, err_ref = abs(np.longdouble(g[q]) - exact), abs(np.longdouble(f[q]) - exact)
+        assert err_got <= max(4 * err_ref, RTOL * abs(exact)), (what, int(bad[q]), g[q], f[q], float(exact))
+    return int(bad.size)
 
 
 def _assert_pattern(mat, ri, co, counts):
@@ -85,7 +135,8 @@ def test_config2_poisson3d_50m_tets():
     ref = torch.as_tensor(ref).cuda()
     owner = _row_owner(ri, 1)
     got = mat.values().clone()
-    _assert_close_on_device(got, ref, owner, counts[1], "config #2 values (node gather)")
+    bad = _violations_on_device(got, ref, owner, counts[1], "config #2 values (node gather)")
+    _adjudicate(bad, got, ref, cells, coords, ri, co, 1, "laplace", None, "config #2 values (node gather)")
     # constants are in the null space of the Laplacian: every row sums to zero up to rounding of its own entries
     y = bsr.spmv(torch.ones(counts[1], dtype=torch.float64, device="cuda"))
     scale = torch.zeros(counts[1], dtype=torch.float64, device="cuda").scatter_reduce_(0, owner, got.abs(), "amax")
@@ -104,7 +155,9 @@ def test_config2_poisson3d_50m_tets():
     b1.assembleBilinear(fem.Operator.laplace())
     torch.cuda.synchronize()
     assert b1.stats()["columns_not_found"] == 0
-    _assert_close_on_device(b1.matrix().values(), ref, owner, counts[1], "config #2 values (cell atomic)")
+    got1 = b1.matrix().values()
+    bad = _violations_on_device(got1, ref, owner, counts[1], "config #2 values (cell atomic)")
+    _adjudicate(bad, got1, ref, cells, coords, ri, co, 1, "laplace", None, "config #2 values (cell atomic)")
 
 
 def test_config3_elasticity3d_20m_tets_with_row_elimination():
@@ -134,7 +187,8 @@ def test_config3_elasticity3d_20m_tets_with_row_elimination():
     assert not_found == 0
     owner = _row_owner(ri, bs)
     ref = torch.as_tensor(vals).cuda()
-    _assert_close_on_device(mat.values(), ref, owner, counts[1], "config #3 values")
+    bad0 = _violations_on_device(mat.values(), ref, owner, counts[1], "config #3 values")
+    _adjudicate(bad0, mat.values(), ref, cells, coords, ri, co, bs, "elasticity", p, "config #3 values")
     ndof = counts[1] * bs
     # rigid translations are in the null space; the operator is symmetric
     for c in range(bs):
@@ -165,7 +219,8 @@ def test_config3_elasticity3d_20m_tets_with_row_elimination():
     assert torch.equal(ls.getEliminationInfo(), torch.as_tensor(einfo).cuda())  # masks bit-exact
     assert torch.equal(ls.getEliminationValue(), torch.as_tensor(evalue).cuda())
     assert torch.equal(ls.rhsVariable(), torch.as_tensor(rhs).cuda())  # exact stores of g
-    _assert_close_on_device(mat.values(), torch.as_tensor(vals).cuda(), owner, counts[1], "config #3 values after row elimination")
+    bad1 = _violations_on_device(mat.values(), torch.as_tensor(vals).cuda(), owner, counts[1], "config #3 values after row elimination")
+    assert np.isin(bad1, bad0).all()  # eliminated rows are exact; elsewhere the values are the ones adjudicated above
     csr = mat.toCsr()
     assert torch.equal(csr.rowsWithEnd(), torch.as_tensor(rows).cuda())
     assert torch.equal(csr.columns(), torch.as_tensor(cols).cuda())
@@ -200,7 +255,7 @@ def test_config4_heat2d_50m_triangles_reassembled_per_step():
         torch.cuda.synchronize()
         if first is None:
             first = mat.values().clone()
-            _assert_close_on_device(first, ref, owner, nn, "config #4 values")
+            assert _violations_on_device(first, ref, owner, nn, "config #4 values").size == 0
         else:
             assert torch.equal(mat.values(), first)
     assert bsr.stats()["columns_not_found"] == 0
