@@ -720,6 +720,32 @@ __global__ void __launch_bounds__(128) k_fan_lockstep(const int32_t* __restrict_
   }
 }
 
+// Pivot hint for the select walk on tets: bit 12 of a (non-START) step word is set when, at that step index, some row of
+// the aligned group of 32 rows that a warp of k_node_fan walks together changes its pivot (O leaves, bit 10 clear).  The
+// walk can then branch around the pivot change on plain data instead of voting at every step (B2F_FAN_UNIFORM_PIVOT == 2);
+// kernels that vote ignore the bit.  One thread per row, the lanes of a warp replay their rows' words side by side.
+__global__ void __launch_bounds__(128) k_fan_pivot_hint(const int32_t* __restrict__ fan_ptr, long long nb_node, uint32_t* __restrict__ steps)
+{
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int32_t qb = 0, n = 0;
+  if (row < nb_node) {
+    qb = fan_ptr[row];
+    n = fan_ptr[row + 1] - qb;
+  }
+  int nmax = n;
+  for (int d = 16; d > 0; d >>= 1)
+    nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, d));
+  for (int p = 0; p < nmax; ++p) {
+    uint32_t w = 0x80000000u;
+    if (p < n)
+      w = steps[qb + p];
+    const bool emits = !(w & 0x80000000u);
+    const unsigned changes = __ballot_sync(0xffffffffu, emits && !((w >> 10) & 1u));
+    if (emits && changes != 0u)
+      steps[qb + p] = w | 4096u;
+  }
+}
+
 namespace {
   // Cells with a node id outside [0, nb_node): counted before anything indexes with them.
   __global__ void __launch_bounds__(256) k_validate_cells(const int32_t* __restrict__ cell_node, long long n_entries, long long nb_node, unsigned long long* __restrict__ counters)
@@ -1082,6 +1108,10 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
       k_pack_fan<4><<<grid_for(((nn + 31) / 32) * 32, 256), 256, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, h->fan_ptr.as<int32_t>(), nn, stage,
                                                                             h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>());
     B2F_CUDA(cudaGetLastError());
+    if (nv == 4 && nb_step > 0) {
+      k_fan_pivot_hint<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
+      B2F_CUDA(cudaGetLastError());
+    }
     tile_ptr = h->fan_ptr.as<int32_t>();
     // lockstep form of the step words, on request only (B2F_FAN_LOCKSTEP): measured slower than the select walk even
     // where the rows of a warp walk in step (N=203 Kuhn cube: 1.07 bodies per warp step, 1.08 ms against 0.98 ms) -

@@ -650,8 +650,10 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
       acc[value_index<BS, PER_BLOCK>(0, k, x, i, j)] = v[i * BS + j];
 }
 
+// 0: the pivot change is selected at every step; 1: behind a warp vote; 2 (default): behind bit 12 of the step word, which
+// the plan sets when some row of the warp changes its pivot at that step (0.980 -> 0.965 ms at N = 203 against the vote)
 #ifndef B2F_FAN_UNIFORM_PIVOT
-#define B2F_FAN_UNIFORM_PIVOT 1
+#define B2F_FAN_UNIFORM_PIVOT 2
 #endif
 // One step of the walk.  Window = (N, O): N the vertex that entered last, O the other one (tets only).  (eC, accC, sC)
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
@@ -750,7 +752,11 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
     for (int e = 0; e < BS2; ++e)
       leave[e] = dropN ? accN[e] : accO[e];
     store_block<BS, PER_BLOCK>(acc, k, dropN ? sN : sO, leave);
-#if B2F_FAN_UNIFORM_PIVOT
+#if B2F_FAN_UNIFORM_PIVOT == 2
+    // the plan says whether any row of this warp changes its pivot at this step (bit 12, sparsity.cu k_fan_pivot_hint):
+    // same branch as below, taken on plain data - no vote, no convergence check
+    if (wc & 4096u) {
+#elif B2F_FAN_UNIFORM_PIVOT
     // Rows of a warp mostly change their pivot O at the same steps (identical link structure on structured meshes), so
     // the pivot change sits behind a warp-uniform branch: when no lane changes, only the renaming m = h remains.
     if (__any_sync(__activemask(), !dropN)) {
@@ -826,6 +832,9 @@ struct FanCfg : SlotsCfg<Op>
 };
 #ifndef B2F_FAN_TILE_AHEAD
 #define B2F_FAN_TILE_AHEAD 0
+#endif
+#ifndef B2F_FAN_WORD_AHEAD
+#define B2F_FAN_WORD_AHEAD 0
 #endif
 #ifndef B2F_FAN_CARVEOUT
 #define B2F_FAN_CARVEOUT -1
@@ -1138,12 +1147,23 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       for (int d = 0; d < 3; ++d)
         e[d] = (NV == 4) ? Xn[d] - X0[d] : Xn[d];
     };
+#if B2F_FAN_WORD_AHEAD
+    // the step word is fetched two steps ahead, so the address chain of the coordinate prefetch (step word -> column id ->
+    // coordinates) starts from a register: one shared-memory round trip less in front of every gather
+    uint32_t w2 = nstep > 1 ? st[1] : 0u;
+#define B2F_NEXT_WORD(pp)      \
+  w = w2;                      \
+  if ((pp) + 2 < nstep)        \
+    w2 = st[(pp) + 2];
+#else
+#define B2F_NEXT_WORD(pp) w = st[(pp) + 1];
+#endif
     while (true) {
       // step p: P enters (Q is the newest)
       uint32_t wc = w;
       enter(eP);
       if (p + 1 < nstep) {
-        w = st[p + 1];
+        B2F_NEXT_WORD(p)
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
@@ -1155,7 +1175,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       wc = w;
       enter(eQ);
       if (p + 1 < nstep) {
-        w = st[p + 1];
+        B2F_NEXT_WORD(p)
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
@@ -1164,6 +1184,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       if (++p >= nstep)
         break;
     }
+#undef B2F_NEXT_WORD
     if (newest_is_Q) {
       if (sQ)
         store_block<BS, PER_BLOCK>(acc, k, sQ, accQ);

@@ -44,16 +44,26 @@
 
 namespace b2f {
 
-// 1/x to full double precision for normal x > 0: hardware seed (MUFU.RCP64H) + two Newton steps, without the range
-// checks and slow path of the compiler's division (cells with a measure outside the normal range are degenerate anyway).
+// 1/x to full double precision for normal x > 0: hardware seed (MUFU.RCP64H, from the upper 32 bits of x: relative error
+// about 2^-20) and ONE cubic correction y (1 + e + e^2), e = 1 - x y: the error becomes e^3, below half an ulp, with a chain
+// of three DFMAs where two Newton steps (B2F_RCP_CUBIC == 0) need four.  No range checks and no slow path like the
+// compiler's division has (cells with a measure outside the normal range are degenerate anyway).
+// tools/experiments/rcp_probe.cu measures both forms against 1.0 / x.
+#ifndef B2F_RCP_CUBIC
+#define B2F_RCP_CUBIC 1
+#endif
 __device__ __forceinline__ double fast_rcp(double x)
 {
   double y;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
   double e = fma(-x, y, 1.0);
+#if B2F_RCP_CUBIC
+  return fma(y, fma(e, e, e), y);
+#else
   y = fma(y, e, y);
   e = fma(-x, y, 1.0);
   return fma(y, e, y);
+#endif
 }
 
 struct TetGeom
