@@ -347,7 +347,7 @@ def run_b200(args):
     launches_per_step = (2 if overlapped else 1) + (2 if exchange is not None else 0)
 
     # --- CPU baseline: oracle port of the reference's legacy loop on this box's host cores (bounded sample)
-    cpu = cpu_baseline(cells, coords, mat, args.cpu_cells)
+    cpu = cpu_baseline(cells, coords, mat.rowIndexWithEnd().cpu().numpy(), mat.columns().cpu().numpy(), args.cpu_cells)
 
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -377,19 +377,35 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def cpu_baseline(cells, coords, mat, max_cells):
-    """Oracle port of modules/poisson/FemModule.cc:300-323 + CsrFormatMatrix.h:58-87 on all host threads."""
+def cpu_baseline(cells, coords, ri, co, max_cells):
+    """Oracle port of modules/poisson/FemModule.cc:300-323 + CsrFormatMatrix.h:58-87 on the host cores (variant B
+    = all threads is `value`; variant A = one thread and variant C = the sparsity build, K1-K5 of femutils/BSRFormat.h:602-744
+    executed sequentially, ride along on bounded samples)."""
     from oracle import oracle as orc
-    ri = mat.rowIndexWithEnd().cpu().numpy()
-    co = mat.columns().cpu().numpy()
     threads = orc.num_threads()
     nc = cells.shape[0]
     sample = min(nc, max_cells)
     vals = np.zeros(co.shape[0])
     threads, secs = best_cpu_threads(orc, cells[:sample], coords, ri, co, vals, threads)
     nnz_sample = co.shape[0] * (sample / nc)
-    return {"value": round(nnz_sample / secs / 1e9, 4), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"first {sample} of {nc} cells of the same mesh, one pass, {secs:.2f} s; nnz credited pro rata"}
+    out = {"value": round(nnz_sample / secs / 1e9, 4), "unit": UNIT, "cores": threads, "kind": "port",
+           "sample": f"first {sample} of {nc} cells of the same mesh, one pass, {secs:.2f} s; nnz credited pro rata"}
+    try:
+        one = min(sample, 10_000_000)
+        vals[:] = 0
+        s1 = orc.legacy_assemble_csr(cells[:one], coords, ri, co, vals, threads=1)
+        out["single_thread"] = {"value": round(co.shape[0] * (one / nc) / s1 / 1e9, 4), "unit": UNIT, "sample": f"first {one} cells, {s1:.2f} s"}
+        from arcanefem_b200 import mesh as gen
+        n_sp = 64
+        c_sp, x_sp = gen.cube_kuhn(n_sp)
+        t0 = time.perf_counter()
+        ri_sp, co_sp = orc.build_pattern(c_sp, x_sp.shape[0])
+        s_sp = time.perf_counter() - t0
+        out["sparsity_build"] = {"value": round(co_sp.shape[0] / s_sp / 1e9, 4), "unit": "GNNZ/s of pattern", "cores": 1,
+                                 "sample": f"Kuhn cube {n_sp}^3 ({c_sp.shape[0]} cells, {co_sp.shape[0]} blocks), {s_sp:.2f} s"}
+    except Exception as e:  # extras only
+        out["extras_error"] = f"{type(e).__name__}: {e}"
+    return out
 
 
 def best_cpu_threads(orc, cells, coords, ri, co, vals, max_threads):
