@@ -26,8 +26,8 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 # dram__bytes_read.sum + dram__bytes_write.sum of k_node_fan<LaplaceTet> at N=203, one ncu --set full capture (profiles/r01_fan_ncu.txt)
-NCU_TRAFFIC_BYTES = 2.591e9
-NCU_TRAFFIC_NOTE = "ncu --set full, k_node_fan<LaplaceTet,0>, N=203: dram read 1.614 GB + write 0.977 GB per launch (profiles/r01_fan_ncu.txt)"
+NCU_TRAFFIC_BYTES = 2.588e9
+NCU_TRAFFIC_NOTE = "ncu --set full, k_node_fan<LaplaceTet,0>, N=203: dram read 1.614 GB + write 0.974 GB per launch (profiles/r01_fan_ncu.txt)"
 METRIC = "bsr_assembly_gnnz_per_s"
 UNIT = "GNNZ/s"
 
