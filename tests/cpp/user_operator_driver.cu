@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #include "b2f/user_operator.cuh"
 #include "arcanefem_b200/BSRFormat.h"
+#include "arcanefem_b200/FemFunctionsGpu.cuh"
 
 template <class T> T* to_device(const std::vector<T>& v)
 {
@@ -79,6 +80,52 @@ struct DensityMass
         Ke[r][c] = (r % 3 == c % 3) ? m * ((r / 3 == c / 3) ? 2.0 : 1.0) : 0.0;
   }
 };
+
+// Callbacks written with the reference's element-kernel vocabulary (include/arcanefem_b200/FemFunctionsGpu.cuh): the body of a
+// module's callback (modules/poisson/FemModule.h:139-147,177-186) with the gathered vertices in place of (cell_lid, cn_cv, coords).
+struct PoissonTetra4Callback
+{
+  __host__ __device__ ArcaneFemB200::FixedMatrix<4, 4> operator()(long long, const double (&X)[4][3]) const
+  {
+    using namespace ArcaneFemB200;
+    const Real volume = Gpu::MeshOperation::computeVolumeTetra4(X);
+    const Real4 dxU = Gpu::FeOperation3D::computeGradientXTetra4(X);
+    const Real4 dyU = Gpu::FeOperation3D::computeGradientYTetra4(X);
+    const Real4 dzU = Gpu::FeOperation3D::computeGradientZTetra4(X);
+    return volume * (dxU ^ dxU) + volume * (dyU ^ dyU) + volume * (dzU ^ dzU);
+  }
+};
+
+// Host check of the vocabulary itself (runs without a device): the callback above against the normalised-gradient
+// stiffness, a triangle against its closed form, FixedMatrix arithmetic.
+static int host_check_vocabulary()
+{
+  using namespace ArcaneFemB200;
+  int bad = 0;
+  const double T[2][4][3] = { { { 0.1, 0.0, 0.2 }, { 1.2, 0.1, 0.0 }, { 0.3, 0.9, 0.1 }, { 0.2, 0.3, 1.1 } },
+                              { { 0.1, 0.0, 0.2 }, { 0.3, 0.9, 0.1 }, { 1.2, 0.1, 0.0 }, { 0.2, 0.3, 1.1 } } }; // second: negatively oriented
+  for (auto& X : T) {
+    double ref[4][4];
+    StiffnessFromNormalisedGradients{}(0, X, ref);
+    const FixedMatrix<4, 4> K = PoissonTetra4Callback{}(0, X);
+    for (int a = 0; a < 4; ++a)
+      for (int b = 0; b < 4; ++b)
+        if (std::fabs(K(a, b) - ref[a][b]) > 1e-13 * std::fabs(ref[0][0]))
+          ++bad;
+  }
+  const double P[3][3] = { { 0.0, 0.0, 0.0 }, { 2.0, 0.0, 0.0 }, { 0.0, 3.0, 0.0 } };
+  if (std::fabs(Gpu::MeshOperation::computeAreaTria3(P) - 3.0) > 1e-15)
+    ++bad;
+  const Real3 dx = Gpu::FeOperation2D::computeGradientXTria3(P), dy = Gpu::FeOperation2D::computeGradientYTria3(P);
+  const double gx[3] = { -0.5, 0.5, 0.0 }, gy[3] = { -1.0 / 3, 0.0, 1.0 / 3 };
+  for (int a = 0; a < 3; ++a)
+    if (std::fabs(dx[a] - gx[a]) > 1e-15 || std::fabs(dy[a] - gy[a]) > 1e-15)
+      ++bad;
+  const FixedMatrix<3, 3> L = 3.0 * (dx ^ dx) + (dy ^ dy) * 3.0; // area * (grad . grad)
+  if (std::fabs(L(0, 0) - 3.0 * (0.25 + 1.0 / 9)) > 1e-15 || std::fabs(L(1, 2)) > 1e-15 || std::fabs((L / 3.0 - L / 3.0)(1, 1)) != 0.0)
+    ++bad;
+  return bad;
+}
 
 // Host loop with the reference's scatter rule and value layouts (femutils/BSRFormat.h:145-171,807-836,862-897).
 template <int BS, class F>
@@ -183,6 +230,10 @@ int run_case(const b2f_mesh_view& mesh, const std::vector<int32_t>& cells, const
 
 int main()
 {
+  const int vocab_bad = host_check_vocabulary();
+  std::printf("element-kernel vocabulary (host): bad=%d\n", vocab_bad);
+  if (vocab_bad)
+    return 4;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     std::printf("no CUDA device: user operators need the GPU (no CPU fallback)\n");
@@ -242,6 +293,13 @@ int main()
     const int b = compare(to_host(bsr.matrix().values().data(), bsr.matrix().values().size()), user, "shim: built-in Laplace vs callback");
     std::printf("  shim BSRFormat<1>::assembleBilinear<4>(callback) bad=%d\n", b);
     bad += b;
+    // a callback that returns a FixedMatrix, written with the reference's helpers, against the built-in operator
+    if (ArcaneFemB200::assemble_with_fixed_matrix<4, 1>(bsr.handle(), PoissonTetra4Callback{}, false, nullptr) != B2F_OK)
+      ++bad;
+    cudaDeviceSynchronize();
+    const int b2 = compare(to_host(bsr.matrix().values().data(), bsr.matrix().values().size()), user, "reference-style FixedMatrix callback vs built-in Laplace");
+    std::printf("  assemble_with_fixed_matrix<4, 1>(PoissonTetra4Callback) bad=%d\n", b2);
+    bad += b2;
   }
   std::printf("user_operator_driver: nn=%lld nc=%lld bad=%d\n", nn, nc, bad);
   return bad == 0 ? 0 : 2;

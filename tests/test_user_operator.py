@@ -32,6 +32,7 @@ def test_user_operator_driver_compiles_and_refuses_to_run_without_a_device(tmp_p
     else:
         assert r.returncode == 3, r.stdout + r.stderr
         assert "no CUDA device" in r.stdout
+    assert "element-kernel vocabulary (host): bad=0" in r.stdout  # FixedMatrix / Real4 / computeGradient* checked on the host
 
 
 @pytest.mark.gpu
