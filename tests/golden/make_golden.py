@@ -137,6 +137,38 @@ def main_elasticity():
         print(name, cells.shape, coords.shape, exp.shape, os.path.getsize(path), "bytes")
 
 
+# Heat cases (modules/heat): transient, re-assembled every step.  The module ships NO result files (its ctest only runs the
+# cases, modules/heat/CMakeLists.txt:43-58), so these fixtures carry the mesh, the groups and the .arc parameters only.
+# Its "Penalty" method adds P to the diagonal (modules/heat/FemModule.cc:386-406), i.e. the WeakPenalty of the other modules;
+# penalty default 1e30 (modules/heat/Fem.axl:55).
+HEAT_CASES = {
+    # modules/heat/inputs/conduction.convection.arc
+    "heat_plate_convection": dict(mesh="plate", lam=1.75, dt=0.4, tmax=20.0, tinit=30.0, dirichlet=[("left", 10.0)],
+                                  convection=[("right", 1.0, 20.0), ("top", 1.0, 20.0), ("bottom", 1.0, 20.0)], penalty=1.0e30),
+}
+
+
+def main_heat():
+    for name, case in HEAT_CASES.items():
+        m = read_msh(os.path.join(REF, "meshes", "msh", case["mesh"] + ".msh"))
+        cells, coords = m.cells(), m.coords
+        out = dict(kind=np.array("heat"), dim=np.int32(m.dim), cells=cells, coords=coords, node_uid=m.node_tags, lam=np.float64(case["lam"]),
+                   dt=np.float64(case["dt"]), tmax=np.float64(case["tmax"]), tinit=np.float64(case["tinit"]), penalty=np.float64(case["penalty"]))
+        for i, (group, value) in enumerate(case["dirichlet"]):
+            out[f"dirichlet{i}_nodes"] = m.group_nodes(group)
+            out[f"dirichlet{i}_value"] = np.float64(value)
+        out["nb_dirichlet"] = np.int32(len(case["dirichlet"]))
+        for i, (group, h, text) in enumerate(case["convection"]):
+            out[f"convection{i}_faces"] = m.group_elements(group)
+            out[f"convection{i}_h"] = np.float64(h)
+            out[f"convection{i}_text"] = np.float64(text)
+        out["nb_convection"] = np.int32(len(case["convection"]))
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, **out)
+        print(name, cells.shape, coords.shape, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     main()
     main_elasticity()
+    main_heat()

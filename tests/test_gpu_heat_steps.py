@@ -91,3 +91,55 @@ def test_transient_heat_steps_match_oracle(mesh_name, dirichlet):
         assert np.isfinite(T).all()
         np.testing.assert_allclose(T[fixed], t_fixed, rtol=1e-12)
     assert T.min() > 250.0 and T.max() < 400.0  # a physical temperature field after three steps
+
+
+def test_reference_heat_case_on_device():
+    """modules/heat/inputs/conduction.convection.arc on the reference's own mesh (tests/golden/heat_plate_convection.npz): plate at 30,
+    left edge held at 10 by the module's "Penalty" (a_ii += P), convection h = 1, Text = 20 on the other three edges, dt = 0.4.
+    Every step's matrix and right-hand side from the device against the oracle (tests/test_oracle_golden.py pins that one on
+    an independent scheme); the temperatures advance with the device-assembled system."""
+    import arcanefem_b200 as fem
+    from arcanefem_b200.bsr import Mesh
+    from oracle import oracle as orc
+    from tests.test_oracle_golden import HEAT, heat_initial_temperature, heat_oracle_step, load_case
+    case = load_case([p for p in HEAT if p.endswith("heat_plate_convection.npz")][0])
+    cells, coords = case["cells"], case["coords"]
+    nn = coords.shape[0]
+    lam, dt, P = float(case["lam"]), float(case["dt"]), float(case["penalty"])
+    bsr = fem.BSRFormat(1)
+    bsr.initialize(Mesh.from_numpy(2, cells, coords), True)
+    bsr.computeSparsity()
+    ri, co = orc.build_pattern(cells, nn)
+    np.testing.assert_array_equal(bsr.matrix().rowIndexWithEnd().cpu().numpy(), ri)
+    np.testing.assert_array_equal(bsr.matrix().columns().cpu().numpy(), co)
+    ls = fem.DoFLinearSystem()
+    bsr.toLinearSystem(ls)
+    conv = [(torch.as_tensor(case[f"convection{i}_faces"]).cuda(), float(case[f"convection{i}_h"]), float(case[f"convection{i}_text"]))
+            for i in range(int(case["nb_convection"]))]
+    dirichlet = [(torch.as_tensor(case[f"dirichlet{i}_nodes"]).cuda(), float(case[f"dirichlet{i}_value"])) for i in range(int(case["nb_dirichlet"]))]
+    rows = np.repeat(np.arange(nn), np.diff(ri))
+    T = heat_initial_temperature(case)
+    d_skip = None
+    for step in range(6):
+        vals, rhs, fixed, finfo = heat_oracle_step(case, ri, co, T)
+        if d_skip is None:
+            d_skip = torch.as_tensor(fixed).cuda()
+        ls.clearValues()
+        bsr.assembleBilinear(fem.Operator.heat(lam, dt))
+        bsr.applyNodalSourceToRhs(torch.as_tensor(T).cuda(), 1.0 / dt, node_skip=d_skip)
+        for faces, h, text in conv:
+            bsr.addFaceMass(faces, h)
+            bsr.applyNeumannToRhs(faces, value=h * text)
+        for nodes, g in dirichlet:
+            bsr.applyDirichletViaWeakPenalty(nodes, g, P)
+        ls.applyDirichlet()
+        torch.cuda.synchronize()
+        assert bsr.stats()["columns_not_found"] == 0
+        got_vals, got_rhs = bsr.matrix().values().cpu().numpy(), ls.rhsVariable().cpu().numpy()
+        np.testing.assert_array_equal(ls.getForcedInfo().cpu().numpy(), finfo)
+        assert_values_close(got_vals, vals, ri, 1, what=f"plate step {step} values")
+        free = fixed == 0
+        assert_vec_close(got_rhs[free], rhs[free], what=f"plate step {step} rhs")
+        np.testing.assert_array_equal(got_rhs[~free], rhs[~free])
+        T = spla.spsolve(sp.csr_matrix((got_vals, (rows, co)), shape=(nn, nn)).tocsc(), got_rhs)
+    assert np.allclose(T[fixed == 1], 10.0, rtol=1e-12) and T.max() < 30.0

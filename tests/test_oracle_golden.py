@@ -16,7 +16,9 @@ import scipy.sparse.linalg as spl
 
 from oracle import oracle as orc
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+_ALL = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+HEAT = [p for p in _ALL if os.path.basename(p).startswith("heat_")]  # transient cases: no result file in the reference, replayed below
+GOLDEN = [p for p in _ALL if p not in HEAT]
 
 
 def load_case(path):
@@ -122,3 +124,85 @@ def test_oracle_reproduces_reference_solution(path):
 
 def test_golden_fixtures_present():
     assert len(GOLDEN) >= 12
+
+
+# ---------------------------------------------------------------------------------------------------
+# Heat (modules/heat): the reference runs its cases without comparing anything (modules/heat/CMakeLists.txt:43-58), so there
+# is no result file to pin on.  The case of inputs/conduction.convection.arc is replayed on the reference's own mesh with
+# the oracle (the module's time step: FemModule.cc:113-131,386-537,775-840) beside an independent scipy formulation of the
+# same scheme (dense element matrices from the P1 basis, test_oracle.py); both must give the same temperatures.
+# ---------------------------------------------------------------------------------------------------
+def heat_oracle_step(case, ri, co, T):
+    """Matrix and right-hand side of one implicit Euler step, the module's sequence: conduction + mass / dt, convection
+    faces, (T_old / dt) source on the free nodes, h * Text on the convection faces, then "Penalty" = a_ii += P, b_i = P * T."""
+    cells, coords = case["cells"], case["coords"]
+    nn = coords.shape[0]
+    vals, nf = orc.assemble(cells, coords, ri, co, bs=1, per_block=False, op=orc.OP_HEAT, lambda_=float(case["lam"]), inv_dt=1.0 / float(case["dt"]))
+    assert nf == 0
+    rhs = np.zeros(nn)
+    fixed = np.zeros(nn, np.uint8)
+    for i in range(int(case["nb_dirichlet"])):
+        fixed[case[f"dirichlet{i}_nodes"]] = 1
+    orc.rhs_nodal_source(cells, coords, 1, 1.0 / float(case["dt"]), T, rhs, node_skip=fixed)
+    for i in range(int(case["nb_convection"])):
+        faces, h, text = case[f"convection{i}_faces"], float(case[f"convection{i}_h"]), float(case[f"convection{i}_text"])
+        assert orc.add_face_mass(faces, coords, h, ri, co, vals) == 0
+        orc.rhs_neumann(faces, coords, 1, rhs, value=h * text)
+    finfo, fval = np.zeros(nn, np.uint8), np.zeros(nn)
+    einfo, ev = np.zeros(nn, np.uint8), np.zeros(nn)
+    for i in range(int(case["nb_dirichlet"])):
+        orc.dirichlet_flag_penalty(1, 0, float(case[f"dirichlet{i}_value"]), float(case["penalty"]), case[f"dirichlet{i}_nodes"], finfo, fval, rhs, weak=True)
+    orc.dirichlet_apply(ri, co, vals, einfo, ev, finfo, fval, rhs)
+    return vals, rhs, fixed, finfo
+
+
+def heat_initial_temperature(case):
+    T = np.full(case["coords"].shape[0], float(case["tinit"]))
+    for i in range(int(case["nb_dirichlet"])):
+        T[case[f"dirichlet{i}_nodes"]] = float(case[f"dirichlet{i}_value"])  # _initTemperature + _applyDirichletBoundaryConditions
+    return T
+
+
+@pytest.mark.parametrize("path", HEAT, ids=[os.path.basename(p)[:-4] for p in HEAT])
+def test_oracle_heat_case_against_independent_scheme(path):
+    from tests.test_oracle import p1_gradients
+    case = load_case(path)
+    cells, coords = case["cells"], case["coords"]
+    nn = coords.shape[0]
+    lam, dt, P = float(case["lam"]), float(case["dt"]), float(case["penalty"])
+    # independent: K (conduction), M (consistent mass), C (convection face mass), c (h * Text load) as dense-element scipy sums
+    K, M, Cm = sp.lil_matrix((nn, nn)), sp.lil_matrix((nn, nn)), sp.lil_matrix((nn, nn))
+    for cn in cells:
+        G, area = p1_gradients(coords[cn][:, :2])
+        K[np.ix_(cn, cn)] += lam * area * (G @ G.T)
+        M[np.ix_(cn, cn)] += area / 12.0 * (np.ones((3, 3)) + np.eye(3))
+    load = np.zeros(nn)
+    for i in range(int(case["nb_convection"])):
+        h, text = float(case[f"convection{i}_h"]), float(case[f"convection{i}_text"])
+        for f in case[f"convection{i}_faces"]:
+            L = np.hypot(*(coords[f[1]] - coords[f[0]])[:2])
+            Cm[np.ix_(f, f)] += h * L / 6.0 * (np.ones((2, 2)) + np.eye(2))
+            load[f] += h * text * L / 2.0
+    lumped = np.asarray(M.sum(axis=1)).ravel()  # the module's source uses area / 3 per cell node = the lumped mass
+    fixed = np.zeros(nn, bool)
+    g = np.zeros(nn)
+    for i in range(int(case["nb_dirichlet"])):
+        fixed[case[f"dirichlet{i}_nodes"]] = True
+        g[case[f"dirichlet{i}_nodes"]] = float(case[f"dirichlet{i}_value"])
+    A = (K + M / dt + Cm).tocsr() + sp.diags(np.where(fixed, P, 0.0))
+    ri, co = orc.build_pattern(cells, nn)
+    rows = np.repeat(np.arange(nn), np.diff(ri))
+    T = heat_initial_temperature(case)
+    T2 = T.copy()
+    nsteps = int(round(float(case["tmax"]) / dt))
+    assert nsteps == 50
+    for step in range(nsteps):
+        vals, rhs, _, _ = heat_oracle_step(case, ri, co, T)
+        T = spl.spsolve(sp.csr_matrix((vals, (rows, co)), shape=(nn, nn)).tocsc(), rhs)
+        b = np.where(fixed, P * g, lumped * T2 / dt + load)
+        T2 = spl.spsolve(A.tocsc(), b)
+        np.testing.assert_allclose(T, T2, rtol=1e-10)
+    # physics of the case: plate at 30 with the left edge held at 10 and air at 20 around it
+    assert np.allclose(T[fixed], 10.0, rtol=1e-12)
+    assert 10.0 - 1e-9 <= T.min() and T.max() < 30.0
+    assert T[coords[:, 0] > 0.9 * coords[:, 0].max()].mean() < 25.0  # the far side has been cooling towards the air temperature
