@@ -1,6 +1,7 @@
 // arcanefem_b200/ArcaneAdapter.h — glue between Arcane objects and the C ABI.  NEEDS THE ARCANE FRAMEWORK (>= 3.14.14,
-// reference CMakeLists.txt:10); it is not compiled in this repository (Arcane is not installed here) and is the code a
-// maintainer adds next to femutils/ when switching a module to libb200fem.so.
+// reference CMakeLists.txt:10), which is not installed here: in this repository it is compiled and run only against a stub
+// of the Arcane types it touches (tests/cpp/arcane_stub, tests/test_cpp_shim.py).  It is the code a maintainer adds next to
+// femutils/ when switching a module to libb200fem.so.
 //
 // It fills a b2f_mesh_view from the same Arcane views the reference kernels read (femutils/BSRFormat.h:789-792,
 // femutils/ArcaneFemFunctionsGpu.h:66-83): cellNode() connectivity, VariableNodeReal3 coordinates, isOwn flags.

@@ -39,3 +39,18 @@ def test_poisson_driver_on_device(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "bad=0" in r.stdout
+
+
+def test_arcane_adapter_against_a_stub_of_the_arcane_api(tmp_path):
+    """include/arcanefem_b200/ArcaneAdapter.h needs the Arcane framework, which is not installed here (nor on the GPU box).  A stub
+    of the few Arcane types it touches (tests/cpp/arcane_stub) lets it be compiled with -Wall -Werror and run on a five-node
+    mesh: connectivity, coordinates and own flags must arrive in the b2f_mesh_view, in the reference mode and in the
+    exchange mode."""
+    exe = str(tmp_path / "arcane_adapter_driver")
+    libdir = os.path.join(ROOT, "arcanefem_b200", "lib")
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Werror", f"-I{ROOT}/include", f"-I{ROOT}/tests/cpp/arcane_stub", f"-I{CUDA}/include",
+           os.path.join(ROOT, "tests", "cpp", "arcane_adapter_driver.cc"), "-o", exe, f"-L{libdir}", "-lb200fem", f"-L{CUDA}/lib64", "-lcudart",
+           f"-Wl,-rpath,{libdir}", f"-Wl,-rpath,{CUDA}/lib64"]
+    subprocess.check_call(cmd)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "bad=0" in r.stdout, r.stdout + r.stderr
