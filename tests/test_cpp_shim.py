@@ -9,10 +9,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CUDA = "/usr/local/cuda"
 
 
-def build_driver(tmp_path):
-    exe = str(tmp_path / "poisson_driver")
+def build_driver(tmp_path, name="poisson_driver"):
+    exe = str(tmp_path / name)
     libdir = os.path.join(ROOT, "arcanefem_b200", "lib")
-    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Werror", f"-I{ROOT}/include", f"-I{CUDA}/include", os.path.join(ROOT, "tests", "cpp", "poisson_driver.cc"), "-o", exe,
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Werror", f"-I{ROOT}/include", f"-I{CUDA}/include", os.path.join(ROOT, "tests", "cpp", name + ".cc"), "-o", exe,
            f"-L{libdir}", "-lb200fem", f"-L{CUDA}/lib64", "-lcudart", f"-Wl,-rpath,{libdir}", f"-Wl,-rpath,{CUDA}/lib64"]
     subprocess.check_call(cmd)
     return exe
@@ -54,3 +54,28 @@ def test_arcane_adapter_against_a_stub_of_the_arcane_api(tmp_path):
     subprocess.check_call(cmd)
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "bad=0" in r.stdout, r.stdout + r.stderr
+
+
+def test_heat_driver_compiles_and_refuses_to_run_without_a_device(tmp_path):
+    """tests/cpp/heat_driver.cc: the heat module's time step through the shim (Operator::Heat, applyConvectionToMatrix / ToRhs,
+    applyNodalSourceToRhs, the module's a_ii += P Dirichlet)."""
+    exe = build_driver(tmp_path, "heat_driver")
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    if has_gpu:
+        assert r.returncode == 0, r.stdout + r.stderr
+    else:
+        assert r.returncode == 3, r.stdout + r.stderr
+        assert "no CUDA device" in r.stdout
+
+
+@pytest.mark.gpu
+def test_heat_driver_on_device(tmp_path):
+    exe = build_driver(tmp_path, "heat_driver")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.rstrip().endswith("bad=0"), r.stdout
