@@ -123,8 +123,8 @@ int main()
     const double want_m = area / dt + h * Ly, want_r = src + h * Text * Ly;
     if (std::fabs(msum - want_m) > 1e-9 * want_m || std::fabs(rsum - want_r) > 1e-9 * want_r)
       ++bad;
-    if (step == 1 && msum != last_sum)
-      ++bad; // re-assembly on the same pattern gives the same bits
+    if (step == 1 && std::fabs(msum - last_sum) > 1e-12 * std::fabs(msum))
+      ++bad; // re-assembly on the same pattern reproduces the system (the face term uses atomics: equal up to their order)
     last_sum = msum;
     // the module's "Penalty": a_ii += P, b_i = P * T (FemModule.cc:386-406) = WeakPenalty here, flagged last
     Gpu::BoundaryConditions::applyDirichletViaWeakPenalty(ls, fixed, Tfix, P);
