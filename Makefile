@@ -6,7 +6,7 @@ NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -ccbin $(HOSTCXX) -Xcompiler -fPIC
 SRC       := $(wildcard arcanefem_b200/csrc/*.cu)
 OBJ       := $(patsubst arcanefem_b200/csrc/%.cu,build/%.o,$(SRC))
 LIB       := arcanefem_b200/lib/libb200fem.so
-HDR       := $(wildcard include/*.h include/b2f/*.cuh arcanefem_b200/csrc/*.h arcanefem_b200/csrc/*.cuh)
+HDR       := $(wildcard include/*.h include/b2f/*.h include/b2f/*.cuh arcanefem_b200/csrc/*.h arcanefem_b200/csrc/*.cuh)
 
 all: $(LIB) oracle
 

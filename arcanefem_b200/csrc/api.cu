@@ -42,6 +42,9 @@ using namespace b2f;
 #define B2F_NEED_PATTERN(h)                                        \
   if (!(h)->has_pattern)                                           \
   return fail(B2F_ERR_STATE, "%s: b2f_compute_sparsity has not been called", __func__)
+// every entry that launches, copies or allocates runs on the device the handle was created on (a single-process caller
+// with several devices may have another one current)
+#define B2F_ON_DEVICE(h) B2F_CUDA(cudaSetDevice((h)->device))
 
 #ifndef B2F_HOST_PIPELINE_CHUNKS
 #define B2F_HOST_PIPELINE_CHUNKS 8
@@ -90,6 +93,12 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_OVERFLOW, "nb_node=%lld does not fit Int32 node ids", (long long)mesh->nb_node);
   if (!mesh->cell_node && mesh->nb_cell > 0)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node is null");
+  // the kernels read a tetrahedron's four node ids with one 16-byte load and coordinates with 8-byte loads: a misaligned
+  // view (a sliced tensor, an offset connectivity span) would fault on the device and take the CUDA context with it
+  if (mesh->nodes_per_cell == 4 && (reinterpret_cast<uintptr_t>(mesh->cell_node) & 15u) != 0)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node of a tetrahedral mesh must be 16-byte aligned (got %p)", (const void*)mesh->cell_node);
+  if ((reinterpret_cast<uintptr_t>(mesh->cell_node) & 3u) != 0 || (reinterpret_cast<uintptr_t>(mesh->coords) & 7u) != 0)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: cell_node must be 4-byte and coords 8-byte aligned");
   if (options->assembly_variant < B2F_ASM_DEFAULT || options->assembly_variant > B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
   if (options->sparsity_build < B2F_SPARSITY_AUTO || options->sparsity_build > B2F_SPARSITY_LISTS)
@@ -118,7 +127,7 @@ int b2f_destroy(b2f_handle h)
     return B2F_OK;
   DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
-                     &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals,
+                     &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_dst, &h->ghost.recv_src,
                      &h->ij_flag, &h->ij_off, &h->ij_ncols, &h->ij_rows, &h->ij_row_local, &h->ij_cols, &h->ij_values, &h->ij_rhs };
   for (DevBuf* b : bufs)
     b->release();
@@ -140,6 +149,8 @@ int b2f_destroy(b2f_handle h)
 int b2f_set_coords(b2f_handle h, const double* coords)
 {
   B2F_CHECK_HANDLE(h);
+  if ((reinterpret_cast<uintptr_t>(coords) & 7u) != 0)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_set_coords: coords must be 8-byte aligned");
   h->mesh.coords = coords;
   return B2F_OK;
 }
@@ -147,12 +158,14 @@ int b2f_set_coords(b2f_handle h, const double* coords)
 int b2f_compute_sparsity(b2f_handle h, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
+  B2F_ON_DEVICE(h);
   return build_pattern(h, (cudaStream_t)stream);
 }
 
 int b2f_release_workspace(b2f_handle h)
 {
   B2F_CHECK_HANDLE(h);
+  B2F_ON_DEVICE(h);
   h->ws_keys_a.release();
   h->ws_keys_b.release();
   h->ws_tmp.release();
@@ -165,6 +178,7 @@ int b2f_assemble(b2f_handle h, const b2f_operator* op, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!op)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble: null operator");
   if (!h->mesh.coords)
@@ -176,6 +190,7 @@ int b2f_assemble_with_source(b2f_handle h, const b2f_operator* op, double qdot, 
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!op)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_with_source: null operator");
   if (!h->mesh.coords)
@@ -188,6 +203,7 @@ int b2f_user_assemble_begin(b2f_handle h, int32_t nodes_per_cell, int32_t block_
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!args_out || !variant_out || !per_block_out || !nb_values_out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: null output");
   if (args_size != sizeof(AssembleArgs))
@@ -198,7 +214,6 @@ int b2f_user_assemble_begin(b2f_handle h, int32_t nodes_per_cell, int32_t block_
                 block_size, h->nv, h->bs);
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: mesh coordinates are null");
-  B2F_CUDA(cudaSetDevice(h->device));
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, (cudaStream_t)stream));
   fill_assemble_args(h, static_cast<AssembleArgs*>(args_out));
   *variant_out = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
@@ -211,6 +226,7 @@ int b2f_reset_values(b2f_handle h, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)h->nb_nz, (cudaStream_t)stream));
   return B2F_OK;
 }
@@ -219,6 +235,7 @@ int b2f_get_bsr(b2f_handle h, b2f_bsr_view* out)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_bsr: null output");
   out->block_size = h->bs;
@@ -238,6 +255,7 @@ int b2f_to_csr(b2f_handle h, b2f_csr_view* out, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_to_csr: null output");
   if (!h->has_csr) {
@@ -265,6 +283,7 @@ int b2f_csr_global_numbering(b2f_handle h, const int32_t* dof_number, int32_t* r
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!dof_number)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_csr_global_numbering: null numbering");
   return csr_global_numbering(h, dof_number, rows_global_out, cols_global_out, (cudaStream_t)stream);
@@ -274,6 +293,7 @@ int b2f_to_hypre_ij(b2f_handle h, const int32_t* dof_number, b2f_ij_view* out, b
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_to_hypre_ij: null output");
   return to_hypre_ij(h, dof_number, out, (cudaStream_t)stream);
@@ -283,6 +303,7 @@ int b2f_get_system(b2f_handle h, b2f_system_view* out)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_system: null output");
   out->nb_dof = h->nb_dof;
@@ -298,6 +319,7 @@ int b2f_get_plan(b2f_handle h, b2f_plan_view* out)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_plan: null output");
   out->nb_node = h->mesh.nb_node;
@@ -316,6 +338,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   B2F_CHECK_HANDLE(h);
   if (!out)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_stats: null output");
+  B2F_ON_DEVICE(h);
   memset(out, 0, sizeof(*out));
   out->nb_edge = h->nb_edge;
   out->nb_col = h->nb_col;
@@ -367,6 +390,7 @@ int b2f_set_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double value)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   int64_t idx = 0;
   int rc = find_value_index(h, row_dof, col_dof, &idx);
   if (rc != B2F_OK)
@@ -379,6 +403,7 @@ int b2f_get_value(b2f_handle h, int64_t row_dof, int64_t col_dof, double* value)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!value)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_get_value: null output");
   int64_t idx = 0;
@@ -394,6 +419,7 @@ int b2f_dump(b2f_handle h, const char* filename)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!filename)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dump: null filename");
   const int64_t nn = h->mesh.nb_node;
@@ -425,6 +451,7 @@ int b2f_clear_values(b2f_handle h, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   return clear_values(h, (cudaStream_t)stream);
 }
 
@@ -432,6 +459,7 @@ int b2f_rhs_fill(b2f_handle h, double value, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   return rhs_fill(h, value, (cudaStream_t)stream);
 }
 
@@ -439,6 +467,7 @@ int b2f_rhs_constant_source(b2f_handle h, double qdot, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_constant_source: mesh coordinates are null");
   return rhs_constant_source(h, qdot, (cudaStream_t)stream);
@@ -448,11 +477,11 @@ int b2f_rhs_nodal_source(b2f_handle h, const double* node_field, double scale, c
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!node_field)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_nodal_source: null node field");
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_nodal_source: mesh coordinates are null");
-  B2F_CUDA(cudaSetDevice(h->device));
   return rhs_nodal_source(h, node_field, scale, node_skip, (cudaStream_t)stream);
 }
 
@@ -460,6 +489,7 @@ int b2f_rhs_neumann(b2f_handle h, const b2f_neumann* bc, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!bc || (bc->nb_face > 0 && !bc->face_node))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_rhs_neumann: null boundary condition / face list");
   return rhs_neumann(h, bc, (cudaStream_t)stream);
@@ -469,13 +499,13 @@ int b2f_add_face_mass(b2f_handle h, int64_t nb_face, const int32_t* face_node, d
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (h->bs != 1)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass needs block_size 1 (got %d)", h->bs);
   if (nb_face < 0 || (nb_face > 0 && !face_node))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass: bad face list");
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_add_face_mass: mesh coordinates are null");
-  B2F_CUDA(cudaSetDevice(h->device));
   return add_face_mass(h, nb_face, face_node, coefficient, (cudaStream_t)stream);
 }
 
@@ -483,6 +513,7 @@ int b2f_dirichlet_flag_penalty(b2f_handle h, const int32_t* node_ids, int64_t n,
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_penalty: bad arguments (dof_index=%d, n=%lld)", dof_index, (long long)n);
   return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, 0, (cudaStream_t)stream);
@@ -492,6 +523,7 @@ int b2f_dirichlet_flag_weak_penalty(b2f_handle h, const int32_t* node_ids, int64
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_weak_penalty: bad arguments (dof_index=%d, n=%lld)", dof_index, (long long)n);
   return dirichlet_flag_penalty(h, node_ids, n, dof_index, value, penalty, 1, (cudaStream_t)stream);
@@ -501,6 +533,7 @@ int b2f_dirichlet_flag_elimination(b2f_handle h, const int32_t* node_ids, int64_
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (dof_index < 0 || dof_index >= h->bs || n < 0 || (n > 0 && !node_ids) || (mode != B2F_ELIMINATE_ROW && mode != B2F_ELIMINATE_ROW_COLUMN))
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_dirichlet_flag_elimination: bad arguments (dof_index=%d, n=%lld, mode=%d)", dof_index, (long long)n, mode);
   return dirichlet_flag_elimination(h, node_ids, n, dof_index, value, mode, (cudaStream_t)stream);
@@ -510,6 +543,7 @@ int b2f_dirichlet_apply(b2f_handle h, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   return dirichlet_apply(h, (cudaStream_t)stream);
 }
 
@@ -517,6 +551,7 @@ int b2f_spmv(b2f_handle h, const double* x, double* y, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!x || !y)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_spmv: null vector");
   return spmv(h, x, y, (cudaStream_t)stream);
@@ -526,6 +561,7 @@ int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!op || !coords_host)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_host: null argument");
   cudaStream_t s = (cudaStream_t)stream;
@@ -616,6 +652,7 @@ int b2f_ghost_plan(b2f_handle h, void* nccl_comm, int32_t rank, int32_t world, c
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (h->mesh.node_is_own)
     return fail(B2F_ERR_STATE, "b2f_ghost_plan: the exchange mode assembles every local row; mesh.node_is_own must be NULL");
   return ghost_plan(h, nccl_comm, rank, world, node_owner_rank_host, node_global_id_host, (cudaStream_t)stream);
@@ -625,6 +662,7 @@ int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream)
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   return ghost_exchange(h, nccl_comm, (cudaStream_t)stream);
 }
 
@@ -632,6 +670,7 @@ int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm,
 {
   B2F_CHECK_HANDLE(h);
   B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
   if (!op)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_exchange: null operator");
   cudaStream_t s = (cudaStream_t)stream;

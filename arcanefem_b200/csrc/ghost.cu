@@ -18,6 +18,7 @@
 // itself has no link-time dependency on it and loads on hosts without NCCL.
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <type_traits>
 #include <dlfcn.h>
 #include <nccl.h>
@@ -42,27 +43,21 @@ namespace {
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
   };
 
-  NcclApi* nccl_api()
+  bool nccl_bind(NcclApi& api)
   {
-    static NcclApi api;
-    static bool tried = false;
-    if (tried)
-      return api.lib ? &api : nullptr;
-    tried = true;
     const char* names[] = { "libnccl.so.2", "libnccl.so" };
+    void* lib = nullptr;
     for (const char* n : names) {
-      api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
-      if (api.lib)
+      lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (lib)
         break;
     }
-    if (!api.lib)
-      return nullptr;
-#define B2F_SYM(field, name)                                              \
-  api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.lib, name)); \
-  if (!api.field) {                                                       \
-    api.lib = nullptr;                                                    \
-    return nullptr;                                                       \
-  }
+    if (!lib)
+      return false;
+#define B2F_SYM(field, name)                                          \
+  api.field = reinterpret_cast<decltype(api.field)>(dlsym(lib, name)); \
+  if (!api.field)                                                     \
+    return false;
     B2F_SYM(GetUniqueId, "ncclGetUniqueId")
     B2F_SYM(CommInitRank, "ncclCommInitRank")
     B2F_SYM(CommDestroy, "ncclCommDestroy")
@@ -72,7 +67,17 @@ namespace {
     B2F_SYM(GroupEnd, "ncclGroupEnd")
     B2F_SYM(GetErrorString, "ncclGetErrorString")
 #undef B2F_SYM
-    return &api;
+    api.lib = lib; // published last: a table with a library handle is complete
+    return true;
+  }
+
+  // Bound once per process (std::call_once: several host threads may create handles concurrently).
+  NcclApi* nccl_api()
+  {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] { nccl_bind(api); });
+    return api.lib ? &api : nullptr;
   }
 
   int fail_nccl(ncclResult_t r, const char* what)
@@ -89,6 +94,62 @@ namespace {
   } while (0)
 
   inline unsigned grid_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+  // An open ncclGroupStart() section.  Calls inside it go through call(): the first failure is remembered and the later calls
+  // are skipped, and end() ALWAYS closes the group before the error is reported - a return from inside an open group would
+  // leave the thread's NCCL state in group mode and make later NCCL calls misbehave or hang.
+  struct NcclGroup
+  {
+    NcclApi* api;
+    ncclResult_t first = ncclSuccess;
+    const char* what = "";
+    bool open = false;
+    explicit NcclGroup(NcclApi* a) : api(a)
+    {
+      first = api->GroupStart();
+      what = "ncclGroupStart";
+      open = first == ncclSuccess;
+    }
+    void call(ncclResult_t r, const char* w)
+    {
+      if (first == ncclSuccess && r != ncclSuccess) {
+        first = r;
+        what = w;
+      }
+    }
+    bool ok() const { return first == ncclSuccess; }
+    int end()
+    {
+      if (open) {
+        open = false;
+        const ncclResult_t r = api->GroupEnd();
+        if (first == ncclSuccess && r != ncclSuccess) {
+          first = r;
+          what = "ncclGroupEnd";
+        }
+      }
+      return first == ncclSuccess ? B2F_OK : fail_nccl(first, what);
+    }
+    ~NcclGroup()
+    {
+      if (open)
+        api->GroupEnd();
+    }
+  };
+#define B2F_IN_GROUP(g, expr) \
+  do {                        \
+    if ((g).ok())             \
+      (g).call((expr), #expr); \
+  } while (0)
+
+  // Temporary device buffer of b2f_ghost_plan: released on every return path.
+  struct TmpBuf : DevBuf
+  {
+    TmpBuf() = default;
+    TmpBuf(const TmpBuf&) = delete;
+    TmpBuf& operator=(const TmpBuf&) = delete;
+    ~TmpBuf() { release(); }
+  };
 
   // metadata of the rows this rank sends: global row id, block count, global column ids (block offsets = row_off)
   __global__ void k_ghost_meta(const int32_t* __restrict__ send_rows, const long long* __restrict__ row_off, long long nrows, const int32_t* __restrict__ row_index,
@@ -191,14 +252,30 @@ namespace {
     values[q] = 0.0; // ghost rows end up zero, like the reference leaves them (BSRFormat.h:815)
   }
 
-  __global__ void k_ghost_add(const long long* __restrict__ recv_index, long long n, const double* __restrict__ recvbuf, double* __restrict__ values)
+  // Owner side.  The incoming scalars are visited in the order of a stable sort by destination (built once by the plan):
+  // the thread at the head of a run adds the whole run into its entry, peer by peer in ascending rank order (the packed
+  // buffer lists the peers in that order) - a fixed summation order, so a node shared by three or more ranks still gives
+  // bitwise reproducible owner rows (an atomicAdd per incoming scalar would not).
+  __global__ void k_ghost_add(const long long* __restrict__ dst_sorted, const long long* __restrict__ src_sorted, long long n, const double* __restrict__ recvbuf,
+                              double* __restrict__ values)
+  {
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n)
+      return;
+    const long long q = dst_sorted[j];
+    if (q < 0 || (j > 0 && dst_sorted[j - 1] == q))
+      return;
+    double v = values[q];
+    for (long long t = j; t < n && dst_sorted[t] == q; ++t)
+      v += recvbuf[src_sorted[t]];
+    values[q] = v;
+  }
+
+  __global__ void k_iota_i64(long long* p, long long n)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n)
-      return;
-    const long long q = recv_index[i];
-    if (q >= 0)
-      atomicAdd(values + q, recvbuf[i]); // several peers may contribute to one owner row
+    if (i < n)
+      p[i] = i;
   }
 
   __global__ void k_iota_i32(int32_t* p, long long n)
@@ -293,7 +370,7 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
   }
   const long long nsend_blocks = row_off[(size_t)nsend_rows];
 
-  DevBuf d_send_rows, d_row_off, d_gid, d_ghost, d_cnt;
+  TmpBuf d_send_rows, d_row_off, d_gid, d_ghost, d_cnt;
   B2F_CUDA(d_send_rows.alloc(sizeof(int32_t) * (size_t)std::max<long long>(nsend_rows, 1)));
   B2F_CUDA(d_row_off.alloc(sizeof(long long) * (size_t)(nsend_rows + 1)));
   B2F_CUDA(d_gid.alloc(sizeof(long long) * (size_t)nn));
@@ -313,14 +390,18 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
   long long* dc = d_cnt.as<long long>();
   B2F_CUDA(cudaMemcpyAsync(dc, cnt.data(), sizeof(long long) * 2 * (size_t)world, cudaMemcpyHostToDevice, stream));
   B2F_CUDA(cudaMemsetAsync(dc + 2 * world, 0, sizeof(long long) * 2 * (size_t)world, stream));
-  B2F_NCCL(api->GroupStart());
-  for (int p = 0; p < world; ++p) {
-    if (p == rank)
-      continue;
-    B2F_NCCL(api->Send(dc + 2 * p, 2, ncclInt64, p, comm, stream));
-    B2F_NCCL(api->Recv(dc + 2 * world + 2 * p, 2, ncclInt64, p, comm, stream));
+  {
+    NcclGroup g(api);
+    for (int p = 0; p < world; ++p) {
+      if (p == rank)
+        continue;
+      B2F_IN_GROUP(g, api->Send(dc + 2 * p, 2, ncclInt64, p, comm, stream));
+      B2F_IN_GROUP(g, api->Recv(dc + 2 * world + 2 * p, 2, ncclInt64, p, comm, stream));
+    }
+    const int rc_g = g.end();
+    if (rc_g != B2F_OK)
+      return rc_g;
   }
-  B2F_NCCL(api->GroupEnd());
   B2F_CUDA(cudaMemcpyAsync(cnt.data() + 2 * world, dc + 2 * world, sizeof(long long) * 2 * (size_t)world, cudaMemcpyDeviceToHost, stream));
   B2F_CUDA(cudaStreamSynchronize(stream));
   P.recv_rows_n.assign((size_t)world, 0);
@@ -336,7 +417,7 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
   const long long nrecv_blocks = P.recv_off[(size_t)world];
 
   // 4. metadata to the owners
-  DevBuf ms_row, ms_k, ms_col, mr_row, mr_k, mr_col, mr_off;
+  TmpBuf ms_row, ms_k, ms_col, mr_row, mr_k, mr_col, mr_off;
   B2F_CUDA(ms_row.alloc(sizeof(long long) * (size_t)std::max<long long>(nsend_rows, 1)));
   B2F_CUDA(ms_k.alloc(sizeof(long long) * (size_t)std::max<long long>(nsend_rows, 1)));
   B2F_CUDA(ms_col.alloc(sizeof(long long) * (size_t)std::max<long long>(nsend_blocks, 1)));
@@ -350,26 +431,28 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
                                                                 ms_col.as<long long>());
   B2F_CUDA(cudaGetLastError());
   B2F_CUDA(cudaMemsetAsync(mr_k.p, 0, sizeof(long long) * (size_t)(nrecv_rows + 1), stream));
-  B2F_NCCL(api->GroupStart());
   {
+    NcclGroup g(api);
     long long sr = 0, rr = 0;
     for (int p = 0; p < world; ++p) {
       const long long ns = P.send_rows_n[(size_t)p], nr = P.recv_rows_n[(size_t)p];
       if (p != rank && ns > 0) {
-        B2F_NCCL(api->Send(ms_row.as<long long>() + sr, (size_t)ns, ncclInt64, p, comm, stream));
-        B2F_NCCL(api->Send(ms_k.as<long long>() + sr, (size_t)ns, ncclInt64, p, comm, stream));
-        B2F_NCCL(api->Send(ms_col.as<long long>() + P.send_off[(size_t)p], (size_t)P.send_blocks[(size_t)p], ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Send(ms_row.as<long long>() + sr, (size_t)ns, ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Send(ms_k.as<long long>() + sr, (size_t)ns, ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Send(ms_col.as<long long>() + P.send_off[(size_t)p], (size_t)P.send_blocks[(size_t)p], ncclInt64, p, comm, stream));
       }
       if (p != rank && nr > 0) {
-        B2F_NCCL(api->Recv(mr_row.as<long long>() + rr, (size_t)nr, ncclInt64, p, comm, stream));
-        B2F_NCCL(api->Recv(mr_k.as<long long>() + rr, (size_t)nr, ncclInt64, p, comm, stream));
-        B2F_NCCL(api->Recv(mr_col.as<long long>() + P.recv_off[(size_t)p], (size_t)P.recv_blocks[(size_t)p], ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Recv(mr_row.as<long long>() + rr, (size_t)nr, ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Recv(mr_k.as<long long>() + rr, (size_t)nr, ncclInt64, p, comm, stream));
+        B2F_IN_GROUP(g, api->Recv(mr_col.as<long long>() + P.recv_off[(size_t)p], (size_t)P.recv_blocks[(size_t)p], ncclInt64, p, comm, stream));
       }
       sr += ns;
       rr += nr;
     }
+    const int rc_g = g.end();
+    if (rc_g != B2F_OK)
+      return rc_g;
   }
-  B2F_NCCL(api->GroupEnd());
 
   // 5. owner side: block offsets of the incoming rows, global -> local table, value indices
   {
@@ -378,7 +461,7 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
     B2F_CUDA(h->ws_tmp.alloc(tb));
     B2F_CUDA(cub::DeviceScan::ExclusiveSum(h->ws_tmp.p, tb, mr_k.as<long long>(), mr_off.as<long long>(), nrecv_rows + 1, stream));
   }
-  DevBuf lid_in, gid_sorted, lid_sorted, errs;
+  TmpBuf lid_in, gid_sorted, lid_sorted, errs;
   B2F_CUDA(lid_in.alloc(sizeof(int32_t) * (size_t)nn));
   B2F_CUDA(gid_sorted.alloc(sizeof(long long) * (size_t)nn));
   B2F_CUDA(lid_sorted.alloc(sizeof(int32_t) * (size_t)nn));
@@ -415,12 +498,25 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
   });
   if (rc != B2F_OK)
     return rc;
+  // destinations in a stable sorted order (k_ghost_add); entries that found no slot (-1) sort last as unsigned keys
+  B2F_CUDA(P.recv_dst.alloc(sizeof(long long) * (size_t)std::max<long long>(P.total_recv, 1)));
+  B2F_CUDA(P.recv_src.alloc(sizeof(long long) * (size_t)std::max<long long>(P.total_recv, 1)));
+  if (P.total_recv > 0) {
+    TmpBuf iota;
+    B2F_CUDA(iota.alloc(sizeof(long long) * (size_t)P.total_recv));
+    k_iota_i64<<<grid_for(P.total_recv, 256), 256, 0, stream>>>(iota.as<long long>(), P.total_recv);
+    B2F_CUDA(cudaGetLastError());
+    size_t tb = 0;
+    const unsigned long long* kin = reinterpret_cast<const unsigned long long*>(P.recv_index.as<long long>());
+    unsigned long long* kout = reinterpret_cast<unsigned long long*>(P.recv_dst.as<long long>());
+    B2F_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, kin, kout, iota.as<long long>(), P.recv_src.as<long long>(), P.total_recv, 0, 64, stream));
+    B2F_CUDA(h->ws_tmp.alloc(tb));
+    B2F_CUDA(cub::DeviceRadixSort::SortPairs(h->ws_tmp.p, tb, kin, kout, iota.as<long long>(), P.recv_src.as<long long>(), P.total_recv, 0, 64, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream)); // iota is released at the end of this scope
+  }
   unsigned long long nerr = 0;
   B2F_CUDA(cudaMemcpyAsync(&nerr, errs.p, sizeof(nerr), cudaMemcpyDeviceToHost, stream));
   B2F_CUDA(cudaStreamSynchronize(stream));
-  DevBuf* tmp[] = { &d_send_rows, &d_row_off, &d_gid, &d_ghost, &d_cnt, &ms_row, &ms_k, &ms_col, &mr_row, &mr_k, &mr_col, &mr_off, &lid_in, &gid_sorted, &lid_sorted, &errs };
-  for (DevBuf* b : tmp)
-    b->release();
   h->ws_tmp.release();
   if (nerr != 0)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_ghost_plan: %llu incoming ghost rows / columns are not owned rows / pattern entries of rank %d (the local mesh must hold "
@@ -445,17 +541,16 @@ int ghost_send_recv(b2f_context_s* h, void* comm_v, cudaStream_t stream)
   if (P.total_send > 0)
     k_ghost_pack<<<grid_for(P.total_send, 256), 256, 0, stream>>>(P.send_index.as<long long>(), P.total_send, h->values.as<double>(), P.send_vals.as<double>());
   B2F_CUDA(cudaGetLastError());
-  B2F_NCCL(api->GroupStart());
+  NcclGroup g(api);
   for (int p = 0; p < P.world; ++p) {
     if (p == P.rank)
       continue;
     if (P.send_blocks[(size_t)p] > 0)
-      B2F_NCCL(api->Send(P.send_vals.as<double>() + P.send_off[(size_t)p] * bs2, (size_t)(P.send_blocks[(size_t)p] * bs2), ncclDouble, p, comm, stream));
+      B2F_IN_GROUP(g, api->Send(P.send_vals.as<double>() + P.send_off[(size_t)p] * bs2, (size_t)(P.send_blocks[(size_t)p] * bs2), ncclDouble, p, comm, stream));
     if (P.recv_blocks[(size_t)p] > 0)
-      B2F_NCCL(api->Recv(P.recv_vals.as<double>() + P.recv_off[(size_t)p] * bs2, (size_t)(P.recv_blocks[(size_t)p] * bs2), ncclDouble, p, comm, stream));
+      B2F_IN_GROUP(g, api->Recv(P.recv_vals.as<double>() + P.recv_off[(size_t)p] * bs2, (size_t)(P.recv_blocks[(size_t)p] * bs2), ncclDouble, p, comm, stream));
   }
-  B2F_NCCL(api->GroupEnd());
-  return B2F_OK;
+  return g.end();
 }
 
 // Second half: the received partial sums are added into the owner rows.
@@ -463,7 +558,8 @@ int ghost_add(b2f_context_s* h, cudaStream_t stream)
 {
   GhostPlan& P = h->ghost;
   if (P.total_recv > 0)
-    k_ghost_add<<<grid_for(P.total_recv, 256), 256, 0, stream>>>(P.recv_index.as<long long>(), P.total_recv, P.recv_vals.as<double>(), h->values.as<double>());
+    k_ghost_add<<<grid_for(P.total_recv, 256), 256, 0, stream>>>(P.recv_dst.as<long long>(), P.recv_src.as<long long>(), P.total_recv, P.recv_vals.as<double>(),
+                                                                 h->values.as<double>());
   B2F_CUDA(cudaGetLastError());
   return B2F_OK;
 }

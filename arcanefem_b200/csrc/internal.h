@@ -59,6 +59,7 @@ struct GhostPlan
   std::vector<int64_t> send_rows_n, recv_rows_n, send_blocks, recv_blocks;
   std::vector<int64_t> send_off, recv_off; // offsets (in blocks) of every peer's part of the packed buffers
   DevBuf send_index, recv_index, send_vals, recv_vals; // value index per exchanged scalar; packed values
+  DevBuf recv_dst, recv_src; // recv_index in a stable sorted order + the position of each entry in recv_vals (fixed summation order)
   int64_t total_send = 0, total_recv = 0; // scalars
   int64_t send_row_lo = 0, send_row_hi = 0; // span of the local rows that are sent (ghost rows an assembled cell touches)
 };

@@ -966,10 +966,13 @@ static int pattern_by_sort(b2f_context_s* h, cudaStream_t stream)
   return B2F_OK;
 }
 
-static int node_cell_lists(b2f_context_s* h, cudaStream_t stream)
+// all_cells: ghost cells (cell_is_own == 0) are listed too - the lists the row-wise pattern build reads in the exchange mode;
+// the lists the gather plan is built from hold the assembled cells only.
+static int node_cell_lists(b2f_context_s* h, cudaStream_t stream, bool all_cells = false)
 {
   const long long nc = h->mesh.nb_cell, nn = h->mesh.nb_node;
   const int nv = h->nv;
+  const uint8_t* cell_mask = all_cells ? nullptr : h->mesh.cell_is_own;
   // --- node -> cell lists (the reference takes them from Arcane's nodeCell() connectivity, BSRFormat.h:942)
   B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
   int32_t* cnt = h->ws_i32a.as<int32_t>();
@@ -977,7 +980,7 @@ static int node_cell_lists(b2f_context_s* h, cudaStream_t stream)
   int rc = B2F_OK;
   B2F_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
   if (nc > 0)
-    k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nv, nc * nv, cnt);
+    k_count_node_cells<<<grid_for(nc * nv, 256), 256, 0, stream>>>(h->mesh.cell_node, cell_mask, nv, nc * nv, cnt);
   B2F_CUDA(cudaGetLastError());
   B2F_CUDA(h->nc_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
   long long nb_adj = 0;
@@ -989,9 +992,9 @@ static int node_cell_lists(b2f_context_s* h, cudaStream_t stream)
   B2F_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (size_t)(nn + 1), stream));
   if (nc > 0) {
     if (nv == 3)
-      k_fill_node_cells<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+      k_fill_node_cells<3><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, cell_mask, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
     else
-      k_fill_node_cells<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, h->mesh.cell_is_own, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
+      k_fill_node_cells<4><<<grid_for(nc, 256), 256, 0, stream>>>(h->mesh.cell_node, cell_mask, nc, h->nc_ptr.as<int32_t>(), cursor, h->nc_list.as<uint32_t>());
   }
   k_sort_segments<uint32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->nc_ptr.as<int32_t>(), nn, 0, h->nc_list.as<uint32_t>());
   B2F_CUDA(cudaGetLastError());
@@ -1008,6 +1011,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
 
   h->has_pattern = false;
   h->has_csr = false;
+  h->ghost.ready = false; // an exchange plan indexes the values of the pattern it was built for
   h->chunk_row.clear();
   B2F_CUDA(h->counters.alloc(sizeof(unsigned long long) * 12));
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 4, stream));
@@ -1029,9 +1033,12 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   // build runs when ghost cells only take part in the pattern (the lists hold the assembled cells), on request, or when a
   // row is too long for the row-wise kernel.
   h->pattern_by_lists = false;
-  bool lists_first = h->mesh.cell_is_own == nullptr && h->opt.sparsity_build != B2F_SPARSITY_SORT;
+  const bool exchange_mode = h->mesh.cell_is_own != nullptr;
+  bool lists_first = h->opt.sparsity_build != B2F_SPARSITY_SORT;
   if (lists_first) {
-    rc = node_cell_lists(h, stream);
+    // exchange mode: the pattern covers the ghost-cell layer, so its lists hold every cell; the lists of the assembled
+    // cells are built afterwards (a second 6 ms pass instead of the 25 ms of the global sort)
+    rc = node_cell_lists(h, stream, exchange_mode);
     if (rc != B2F_OK)
       return rc;
     bool fallback = false;
@@ -1045,6 +1052,11 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     }
     else
       h->pattern_by_lists = true;
+    if (exchange_mode) {
+      rc = node_cell_lists(h, stream, false);
+      if (rc != B2F_OK)
+        return rc;
+    }
   }
   else {
     rc = pattern_by_sort(h, stream);

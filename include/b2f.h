@@ -96,8 +96,9 @@ typedef enum b2f_fan_mode { B2F_FAN_AUTO = 0, B2F_FAN_SELECT = 1, B2F_FAN_LOCKST
 
 /* How b2f_compute_sparsity forms the pattern.  SORT: the reference's algorithm (femutils/BSRFormat.h:602-744): cell -> edge
  * keys, global radix sort, run ends, degree scan, column fill.  LISTS: node -> cell lists first, then every row gathers
- * the vertices of its cells into a sorted set - no edge keys and no global sort, same pattern bit for bit.  AUTO = LISTS,
- * except in the cell_is_own exchange mode and for rows with more than 64 neighbours, which take SORT. */
+ * the vertices of its cells into a sorted set - no edge keys and no global sort, same pattern bit for bit.  AUTO = LISTS
+ * (in the cell_is_own exchange mode the lists of the pattern hold the ghost cells too and the lists of the assembled cells
+ * are built in a second pass), except for rows with more than 64 neighbours, which take SORT. */
 typedef enum b2f_sparsity_build { B2F_SPARSITY_AUTO = 0, B2F_SPARSITY_SORT = 1, B2F_SPARSITY_LISTS = 2 } b2f_sparsity_build;
 
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
