@@ -34,10 +34,11 @@ def plane_coords(n_hex, nz_total, k, L=1.0, perturb=0.25, seed=1234):
     return c
 
 
-def global_mesh(n_hex, world, L=1.0, perturb=0.25, seed=1234):
+def global_mesh(n_hex, world, L=1.0, perturb=0.25, seed=1234, nz_total=None):
     """The undecomposed mesh (cells, coords) of the same cube, global lexicographic node ids (tests only: small sizes)."""
     n1 = n_hex + 1
-    nz_total = n_hex * world
+    if nz_total is None:
+        nz_total = n_hex * world
     coords = np.concatenate([plane_coords(n_hex, nz_total, k, L, perturb, seed) for k in range(nz_total + 1)], axis=0)
     hi = np.arange(n_hex, dtype=np.int64)
     kk, jj, ii = np.meshgrid(np.arange(nz_total, dtype=np.int64), hi, hi, indexing="ij")
@@ -47,34 +48,93 @@ def global_mesh(n_hex, world, L=1.0, perturb=0.25, seed=1234):
     return np.ascontiguousarray(cells), np.ascontiguousarray(coords)
 
 
-def slab_partition(n_hex, rank, world, L=1.0, perturb=0.25, seed=1234):
-    """Local mesh of `rank` for the global cube of n_hex x n_hex x (n_hex*world) hexes split into z-slabs.
+def slab_bounds(nz_total, world):
+    """Hex layers of every rank for a z-slab split of nz_total layers: world + 1 boundaries, the first nz_total % world
+    ranks take one layer more (406 layers: 2 x 203; 102 102 101 101; 6 x 51 + 2 x 50)."""
+    base, extra = divmod(nz_total, world)
+    b = [0]
+    for r in range(world):
+        b.append(b[-1] + base + (1 if r < extra else 0))
+    return b
+
+
+def slab_partition(n_hex, rank, world, L=1.0, perturb=0.25, seed=1234, nz_total=None, max_layers=None):
+    """Local mesh of `rank` for the global box of n_hex x n_hex x nz_total hexes split into z-slabs (slab_bounds).
+    nz_total = None: n_hex layers per rank (weak scaling: the cube grows with the ranks); nz_total = n_hex: one fixed cube
+    cut into `world` slabs (strong scaling, BASELINE config #5).  max_layers keeps only the first layers of the slab (the
+    bounded CPU sample of bench.py; the top plane's rows are then incomplete).
 
     Returns dict(cells int32 [nc,4], coords [nn,3], cell_is_own uint8 [nc], node_owner int32 [nn], node_gid int64 [nn],
-    nb_own_cell, z0 = first local plane)."""
+    nb_own_cell, z0 = first local plane, layers = (first, last+1) own hex layers)."""
     n1 = n_hex + 1
     plane = n1 * n1
-    nz_total = n_hex * world
-    lay0, lay1 = rank * n_hex, (rank + 1) * n_hex  # own hex layers [lay0, lay1)
+    if nz_total is None:
+        nz_total = n_hex * world
+    bounds = slab_bounds(nz_total, world)
+    lay0, lay1 = bounds[rank], bounds[rank + 1]  # own hex layers [lay0, lay1)
     ghost_top = 1 if rank < world - 1 else 0
+    if max_layers is not None and lay1 - lay0 > max_layers:
+        lay1, ghost_top = lay0 + max_layers, 0
     z0, z1 = lay0, lay1 + ghost_top  # local planes z0 .. z1 inclusive
+    h_xy = L / n_hex  # cubic hexes: the box is L x L x (nz_total * h)
     coords = np.concatenate([plane_coords(n_hex, nz_total, k, L, perturb, seed) for k in range(z0, z1 + 1)], axis=0)
-    # cells of the local layers, local lexicographic node ids
-    hi = np.arange(n_hex, dtype=np.int64)
+    del h_xy
+    # cells of the local layers, local lexicographic node ids (built layer by layer: int32 throughout, 200 M cells fit)
     nlay = z1 - z0
-    kk, jj, ii = np.meshgrid(np.arange(nlay, dtype=np.int64), hi, hi, indexing="ij")
-    base = (ii + n1 * (jj + n1 * kk)).ravel()
+    hi = np.arange(n_hex, dtype=np.int32)
+    jj, ii = np.meshgrid(hi, hi, indexing="ij")
+    base0 = (ii + n1 * jj).ravel().astype(np.int32)
     corner = np.array([dx + n1 * (dy + n1 * dz) for dz in (0, 1) for dy in (0, 1) for dx in (0, 1)], dtype=np.int64)
-    off = corner[gen.kuhn_table()]
-    cells = (base[:, None, None] + off[None, :, :]).reshape(-1, 4).astype(np.int32)
-    cell_layer = np.repeat(kk.ravel(), 6) + z0
-    cell_is_own = (cell_layer < lay1).astype(np.uint8)
+    off = corner[gen.kuhn_table()].astype(np.int32)
+    per_layer = (base0[:, None, None] + off[None, :, :]).reshape(-1, 4)
+    ncl = per_layer.shape[0]
+    cells = np.empty((nlay * ncl, 4), dtype=np.int32)
+    for k in range(nlay):
+        np.add(per_layer, np.int32(k * plane), out=cells[k * ncl:(k + 1) * ncl])
+    cell_is_own = np.ones(nlay * ncl, dtype=np.uint8)
+    if ghost_top:
+        cell_is_own[(nlay - 1) * ncl:] = 0
     node_plane = np.repeat(np.arange(z0, z1 + 1, dtype=np.int64), plane)
     # owner = lowest rank whose own cells touch the node: plane k belongs to the slab below when it is a slab boundary
-    node_owner = np.clip((node_plane - 1) // n_hex, 0, world - 1).astype(np.int32)
+    node_owner = (np.searchsorted(np.asarray(bounds[1:], dtype=np.int64), node_plane, side="left")).clip(0, world - 1).astype(np.int32)
     node_gid = (np.arange(coords.shape[0], dtype=np.int64) + z0 * plane)
-    return dict(cells=np.ascontiguousarray(cells), coords=np.ascontiguousarray(coords), cell_is_own=cell_is_own, node_owner=node_owner, node_gid=node_gid,
-                nb_own_cell=int(cell_is_own.sum()), z0=z0, plane=plane)
+    return dict(cells=cells, coords=np.ascontiguousarray(coords), cell_is_own=cell_is_own, node_owner=node_owner, node_gid=node_gid,
+                nb_own_cell=int(cell_is_own.sum()), z0=z0, plane=plane, layers=(lay0, lay1), bounds=bounds)
+
+
+def partition_by_cell_rank(cells, coords, cell_rank, rank, world):
+    """Arcane-style local mesh of `rank` for ANY assignment of the cells of a global mesh to ranks (tests: block
+    decompositions where a node is shared by three or more ranks).  Own cells = cell_rank == rank; a node is owned by the
+    lowest rank among the cells that touch it; the local mesh holds the own cells plus every cell touching a node this
+    rank owns (what b2f_ghost_plan requires of the ghost layer).  Local node ids ascend with the global id."""
+    cells = np.asarray(cells)
+    cell_rank = np.asarray(cell_rank)
+    nn = coords.shape[0]
+    owner = np.full(nn, world, dtype=np.int64)
+    for a in range(cells.shape[1]):
+        np.minimum.at(owner, cells[:, a], cell_rank)
+    own_cell = cell_rank == rank
+    touches_owned = (owner[cells] == rank).any(axis=1)
+    keep = own_cell | touches_owned
+    lcells_g = cells[keep]
+    gid = np.unique(lcells_g)
+    lid = np.full(nn, -1, dtype=np.int64)
+    lid[gid] = np.arange(gid.shape[0])
+    return dict(cells=np.ascontiguousarray(lid[lcells_g].astype(np.int32)), coords=np.ascontiguousarray(coords[gid]),
+                cell_is_own=own_cell[keep].astype(np.uint8), node_owner=owner[gid].astype(np.int32), node_gid=gid.astype(np.int64),
+                nb_own_cell=int(own_cell.sum()))
+
+
+def block_cell_rank(n_hex, py, pz, nz_total=None):
+    """Rank of every cell of global_mesh(n_hex, ., nz_total=...) for a py x pz block split in y and z (rank = by + py * bz):
+    the nodes on the lines where four blocks meet are shared by four ranks."""
+    if nz_total is None:
+        nz_total = n_hex
+    hi = np.arange(n_hex, dtype=np.int64)
+    kk, jj, _ = np.meshgrid(np.arange(nz_total, dtype=np.int64), hi, hi, indexing="ij")
+    by = (jj * py) // n_hex
+    bz = (kk * pz) // nz_total
+    return np.repeat((by + py * bz).ravel(), 6)
 
 
 def exchange_reference(part, ri, co, vals, rank, world, dist):
@@ -128,25 +188,36 @@ def exchange_reference(part, ri, co, vals, rank, world, dist):
 class GhostExchange:
     """NCCL ghost-row exchange bound to one BSRFormat (one rank = one GPU)."""
 
-    def __init__(self, bsr, rank, world, node_owner, node_gid):
+    def __init__(self, bsr, rank, world, node_owner, node_gid, comm=None):
+        """comm: an ncclComm_t (ctypes c_void_p) made by make_comm() to share one communicator between several exchanges;
+        None creates one that close() destroys."""
         import torch
-        import torch.distributed as dist
         self._lib = _lib.load_library()
         self._bsr = bsr
-        self._comm = C.c_void_p()
-        ident = torch.zeros(128, dtype=torch.uint8)
-        if rank == 0:
-            buf = (C.c_ubyte * 128)()
-            check(self._lib.b2f_nccl_unique_id(buf))
-            ident = torch.tensor(list(buf), dtype=torch.uint8)
-        ident = ident.cuda()
-        dist.broadcast(ident, 0)
-        raw = bytes(ident.cpu().tolist())
-        check(self._lib.b2f_nccl_comm_init(C.c_char_p(raw), int(rank), int(world), C.byref(self._comm)))
+        self._owns_comm = comm is None
+        self._comm = comm if comm is not None else self.make_comm(rank, world)
         owner = np.ascontiguousarray(node_owner, dtype=np.int32)
         gid = np.ascontiguousarray(node_gid, dtype=np.int64)
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         check(self._lib.b2f_ghost_plan(bsr._h, self._comm, int(rank), int(world), owner.ctypes.data_as(C.c_void_p), gid.ctypes.data_as(C.c_void_p), stream))
+
+    @staticmethod
+    def make_comm(rank, world):
+        """ncclComm_t of libb200fem.so's own NCCL binding; the unique id travels over torch.distributed."""
+        import torch
+        import torch.distributed as dist
+        lib = _lib.load_library()
+        comm = C.c_void_p()
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_ubyte * 128)()
+            check(lib.b2f_nccl_unique_id(buf))
+            ident = torch.tensor(list(buf), dtype=torch.uint8)
+        ident = ident.cuda()
+        dist.broadcast(ident, 0)
+        raw = bytes(ident.cpu().tolist())
+        check(lib.b2f_nccl_comm_init(C.c_char_p(raw), int(rank), int(world), C.byref(comm)))
+        return comm
 
     def run(self):
         import torch
@@ -160,6 +231,6 @@ class GhostExchange:
         check(self._lib.b2f_assemble_exchange(self._bsr._h, C.byref(d), self._comm, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
     def close(self):
-        if self._comm:
+        if self._comm and self._owns_comm:
             self._lib.b2f_nccl_comm_destroy(self._comm)
-            self._comm = C.c_void_p()
+        self._comm = C.c_void_p()

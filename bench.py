@@ -1,19 +1,26 @@
 #!/usr/bin/env python
-"""bench.py — BSR assembly throughput (GNNZ/s) + fraction of the HBM roofline, 3D P1 Poisson on a synthetic
-structured Kuhn tetrahedral cube (BASELINE.json metric; workload = configs[1]: ~50M tets, BS=1, 1 B200).
+"""bench.py — BSR assembly throughput (GNNZ/s) + fraction of the HBM roofline (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--n N_HEX] [--variant 1|2|3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload W] [--scaling auto|weak|strong]
 
-A step = one values assembly (zero-fill + element matrices + scatter-add) of the whole mesh on an existing pattern
-(SURVEY.md §8d).  `value` times it with device-resident inputs (CUDA events on the launching stream); `e2e` times the
-host-buffer entry point b2f_assemble_host (pinned coordinates H2D + assembly + values D2H every step).
-`--impl reference` times the CPU restatement of the reference's legacy assembly loop (the reference itself needs the
-Arcane framework and cannot be built here) on all host cores.  Multi-GPU (N > 1): one rank per GPU, the cube is
-extended to N slabs of N_HEX hex layers (weak scaling); ghost-plane rows are exchanged over NCCL.
+Workloads (BASELINE.json configs):
+  N = 1   poisson3d (default, configs[1]: Poisson 3D P1 tets, Kuhn cube 203^3, 50.2 M tets, BSR 1x1), elasticity3d (configs[2],
+          149^3, BS = 3, + Dirichlet row elimination on z = 0), heat3d / heat2d (configs[3], mass + stiffness re-assembly), poisson2d
+  N > 1   poisson3d only.  --scaling auto (default) = configs[4] as written: ONE 406^3 cube (401.5 M tets, 1.007e9 nnz) cut
+          into N z-slabs (102/102/101/101, 6 x 51 + 2 x 50 layers), "scaling": "strong"; the weak-scaling run (203^3 hexes
+          per GPU, the cube grows with N) rides along in "weak_scaling".  --scaling weak / strong runs one mode only.
+A step = one values assembly (zero-fill + element matrices + scatter-add [+ ghost-row exchange]) on an existing pattern
+(SURVEY.md 8d).  `value`: device-resident inputs, CUDA events on the launching stream, max over ranks.  `e2e`: the host-buffer
+entry (pinned coordinates H2D + assembly + values D2H every step).  `parity_sample`: >= 10^4 own rows per rank recomputed on
+the host in extended precision from the same coordinates (numpy, independent of oracle/) and compared entry by entry.
+`--impl reference`: the CPU restatement of the reference's legacy assembly loop (the reference needs the Arcane framework and
+cannot be built here) on all host cores, on a bounded sample of the same workload.
 """
 import argparse
+import hashlib
 import json
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -25,16 +32,26 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum of k_node_fan<LaplaceTet> at N=203, one ncu --set full capture (profiles/r01_fan_ncu.txt)
-NCU_TRAFFIC_BYTES = 2.588e9
-NCU_TRAFFIC_NOTE = "ncu --set full, k_node_fan<LaplaceTet,0>, N=203: dram read 1.614 GB + write 0.974 GB per launch (profiles/r01_fan_ncu.txt)"
 METRIC = "bsr_assembly_gnnz_per_s"
 UNIT = "GNNZ/s"
 
+# name -> (dim, block size, hexes / quads per side at N = 1, operator, BASELINE.json config)
+WORKLOADS = {
+    "poisson3d": (3, 1, 203, "laplace", "configs[1]"),
+    "elasticity3d": (3, 3, 149, "elasticity", "configs[2]"),
+    "heat3d": (3, 1, 203, "heat", "configs[3] (3D)"),
+    "heat2d": (2, 1, 5000, "heat", "configs[3] (2D)"),
+    "poisson2d": (2, 1, 5000, "laplace", "2D twin of configs[1]"),
+}
+KERNEL = {"poisson3d": "k_node_fan<LaplaceTet>", "elasticity3d": "k_node_fan<ElasticityTet>", "heat3d": "k_node_fan<HeatTet>", "heat2d": "k_node_fan<HeatTri>",
+          "poisson2d": "k_node_fan<LaplaceTri>"}
+NCU_FILES = {"poisson3d": ["profiles/r02_fan_ncu.txt", "profiles/r01_fan_ncu.txt"], "elasticity3d": ["profiles/r02_fan_elasticity_ncu.txt"],
+             "heat3d": ["profiles/r02_fan_heat3d_ncu.txt"], "heat2d": ["profiles/r02_fan_heat2d_ncu.txt"], "poisson2d": ["profiles/r02_fan_poisson2d_ncu.txt"]}
 
-def algorithmic_bytes(nv, nc, nn, nnzb, bs):
-    """B_asm of SURVEY.md §8(d): connectivity + coordinates + row_index + columns + values, each touched once."""
-    return 4 * nv * nc + 24 * nn + 4 * (nn + 1) + 4 * nnzb + 8 * bs * bs * nnzb
+
+def algorithmic_bytes(nv, nc, nn, nnzb, bs, per_cell_bytes=0):
+    """B_asm of SURVEY.md 8(d): connectivity + coordinates + row_index + columns + values (+ per-cell data), each touched once."""
+    return 4 * nv * nc + 24 * nn + 4 * (nn + 1) + 4 * nnzb + 8 * bs * bs * nnzb + per_cell_bytes * nc
 
 
 def measured_peak():
@@ -45,6 +62,35 @@ def measured_peak():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the workload's kernel from the committed ncu --set full summary
+    (per launch), with the file's git blob hash; (None, None) when no capture of the kernel is committed."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for rel in NCU_FILES.get(workload, []):
+        path = os.path.join(ROOT, rel)
+        if not os.path.exists(path):
+            continue
+        raw = open(path, "rb").read()
+        total, found = 0.0, 0
+        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            m = re.search(re.escape(key) + r"\s*=\s*([0-9.eE+-]+)\s*([KMG]?byte)", raw.decode("utf-8", "replace"))
+            if m:
+                total += float(m.group(1)) * unit[m.group(2)]
+                found += 1
+        if found == 2:
+            blob = hashlib.sha1(b"blob %d\0" % len(raw) + raw).hexdigest()
+            return total, f"{rel} (git blob {blob[:12]}): dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of {KERNEL[workload]}"
+    return None, None
+
+
+def host_threads():
+    """Host cores this process may use.  Not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
 
 
 class ClockSampler:
@@ -178,55 +224,162 @@ def path_breakdown(torch, fem, gen, bsr, op, coords, sparsity_ms, assembly_ms, r
     return out
 
 
-def run_b200(args):
+def workload_text(workload, mode, n, world, nz_total):
+    """The one description of the job both arms print (config.workload)."""
+    dim, bs, _, opname, cfg = WORKLOADS[workload]
+    if workload != "poisson3d" or world == 1:
+        shape = f"{n}^3 hexes" if dim == 3 else f"{n}^2 quads"
+        what = {"laplace": "Poisson", "elasticity": "linear elasticity", "heat": "heat (mass + stiffness)"}[opname]
+        return f"BASELINE {cfg}: {what} {dim}D P1 {'tets' if dim == 3 else 'triangles'}, structured {'Kuhn cube' if dim == 3 else 'square'} {shape}, BSR {bs}x{bs} values assembly, 1 GPU"
+    if mode == "strong":
+        return (f"BASELINE configs[4]: Poisson 3D P1 tets, ONE structured Kuhn cube {n}^3 hexes ({6 * n ** 3} cells) cut into {world} z-slabs of "
+                f"{'/'.join(str(b - a) for a, b in zip(slab_bounds_of(nz_total, world)[:-1], slab_bounds_of(nz_total, world)[1:]))} hex layers, BSR 1x1 values assembly + ghost-row exchange")
+    return f"Poisson 3D P1 tets, structured Kuhn box {n} x {n} x {nz_total} hexes = {n}^3 per GPU on {world} GPUs (weak scaling of BASELINE configs[1]), BSR 1x1 values assembly + ghost-row exchange"
+
+
+def slab_bounds_of(nz_total, world):
+    from arcanefem_b200 import multigpu as mg
+    return mg.slab_bounds(nz_total, world)
+
+
+def laplace_tet_rows_reference(cells, coords, ri, co, rows):
+    """Rows `rows` of the P1 Laplace matrix from the cells that touch them, in extended precision (numpy longdouble), from the
+    reference's formula Ke[a][b] = V grad_a . grad_b with grad = cofactor / (6V) (femutils/ArcaneFemFunctionsGpu.h:110-122,280-392,
+    modules/poisson/FemModule.h:177-186).  Independent of oracle/ and of the CUDA formulation.  Returns (ref [n, kmax], mask)."""
+    rows = np.asarray(rows, dtype=np.int64)
+    nn = coords.shape[0]
+    pos = np.full(nn, -1, dtype=np.int32)
+    pos[rows] = np.arange(rows.shape[0], dtype=np.int32)
+    touch = (pos[cells] >= 0).any(axis=1)
+    sel = cells[touch].astype(np.int64)
+    X = coords[sel].astype(np.longdouble)  # [m, 4, 3]
+    e1, e2, e3 = X[:, 1] - X[:, 0], X[:, 2] - X[:, 0], X[:, 3] - X[:, 0]
+    g = np.empty((sel.shape[0], 4, 3), dtype=np.longdouble)
+    g[:, 1], g[:, 2], g[:, 3] = np.cross(e2, e3), np.cross(e3, e1), np.cross(e1, e2)
+    g[:, 0] = -(g[:, 1] + g[:, 2] + g[:, 3])
+    det = (e1 * g[:, 1]).sum(axis=1)
+    K = np.einsum("mad,mbd->mab", g, g) / (6 * np.abs(det))[:, None, None]
+    k = (ri[rows + 1] - ri[rows]).astype(np.int64)
+    kmax = int(k.max())
+    cols = np.full((rows.shape[0], kmax), -1, dtype=np.int64)
+    mask = np.arange(kmax)[None, :] < k[:, None]
+    cols[mask] = co[(ri[rows].astype(np.int64)[:, None] + np.arange(kmax)[None, :])[mask]]
+    ref = np.zeros((rows.shape[0], kmax), dtype=np.longdouble)
+    missing = 0
+    for a in range(4):
+        p = pos[sel[:, a]]
+        m = p >= 0
+        for b in range(4):
+            hit = cols[p[m]] == sel[m, b][:, None]
+            missing += int((~hit.any(axis=1)).sum())
+            slot = hit.argmax(axis=1)
+            np.add.at(ref, (p[m], slot), K[m, a, b])
+    return ref, mask, missing
+
+
+def parity_sample(cells, coords, mat, own_rows, receiving_rows, nrows=10000, seed=99):
+    """Compares a fixed sample of this rank's own rows (half of them rows that receive ghost contributions, when there are
+    any) with the host recomputation.  max_rel = max |d| / max(|ref|, 1e-3 row max) (row-norm floor only for entries that
+    cancel to ~0); max_rel_pure = max |d| / |ref| over the entries with |ref| > 1e-6 row max."""
+    rng = np.random.default_rng(seed)
+    pick = []
+    if receiving_rows is not None and receiving_rows.shape[0] > 0:
+        pick.append(rng.choice(receiving_rows, size=min(nrows // 2, receiving_rows.shape[0]), replace=False))
+    rest = nrows - sum(p.shape[0] for p in pick)
+    pick.append(rng.choice(own_rows, size=min(rest, own_rows.shape[0]), replace=False))
+    rows = np.unique(np.concatenate(pick))
+    ri = mat.rowIndexWithEnd().cpu().numpy()
+    co = mat.columns().cpu().numpy()
+    ref, mask, missing = laplace_tet_rows_reference(cells, coords, ri, co, rows)
     import torch
+    idx = torch.as_tensor((ri[rows][:, None] + np.arange(ref.shape[1])[None, :])[mask]).cuda()
+    got = np.zeros(ref.shape, dtype=np.longdouble)
+    got[mask] = mat.values()[idx].cpu().numpy()
+    d = np.abs(got - ref)
+    rowmax = np.abs(ref).max(axis=1, keepdims=True)
+    rel = (d / np.maximum(np.abs(ref), 1e-3 * rowmax))[mask]
+    big = mask & (np.abs(ref) > 1e-6 * rowmax)
+    pure = (d[big] / np.abs(ref[big]))
+    return {"rows": int(rows.shape[0]), "entries": int(mask.sum()), "max_rel": float(rel.max()), "max_rel_pure": float(pure.max()), "over_1e-12": int((rel > 1e-12).sum()),
+            "columns_missing": missing, "receiving_rows": int(pick[0].shape[0]) if len(pick) > 1 else 0,
+            "rule": "|d| / max(|ref|, 1e-3 * row max); ref = extended-precision host recomputation of the sampled rows (numpy longdouble, reference formula)"}
+
+
+def build_workload(args, workload, mode, rank, world):
+    """Mesh + operator of one run.  Returns a dict; the mesh arrays are numpy (host) - they stand in for Arcane's views."""
+    import torch
+    import arcanefem_b200 as fem
+    from arcanefem_b200 import mesh as gen
+    from arcanefem_b200 import multigpu as mg
+    dim, bs, n_default, opname, _ = WORKLOADS[workload]
+    keep = []
+    if workload == "poisson3d":
+        if world == 1:
+            n, nz_total = (args.n or n_default), None
+        elif mode == "strong":
+            n = args.n_global
+            nz_total = n
+        else:
+            n, nz_total = (args.n or n_default), None
+        part = mg.slab_partition(n, rank, world, nz_total=nz_total)
+        cells, coords = part["cells"], part["coords"]
+        nz = nz_total if nz_total is not None else n * world
+    else:
+        n = args.n or n_default
+        cells, coords = gen.cube_kuhn(n) if dim == 3 else gen.square(n)
+        part, nz = None, n
+    if opname == "laplace":
+        op = fem.Operator.laplace()
+    elif opname == "elasticity":
+        op = fem.Operator.elasticity(21.0e5, 0.28)
+    else:
+        lam = torch.as_tensor(np.random.default_rng(5).uniform(0.5, 2.0, size=cells.shape[0])).cuda()
+        keep.append(lam)
+        op = fem.Operator.heat(1.75, 0.1, cell_lambda=lam)
+    return dict(dim=dim, bs=bs, n=n, nz_total=nz, cells=cells, coords=coords, part=part, op=op, opname=opname, keep=keep)
+
+
+def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, full=True):
+    """One measured configuration.  full = False (the ride-along mode at N > 1): device-timed value, parity sample and
+    sparsity time only."""
     import arcanefem_b200 as fem
     from arcanefem_b200.bsr import Mesh
     from arcanefem_b200 import mesh as gen
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    n = args.n
-    t0 = time.time()
     from arcanefem_b200 import multigpu as mg
-    part = mg.slab_partition(n, rank, world)  # world == 1: the plain cube, every cell and node own
-    cells, coords = part["cells"], part["coords"]
+    t0 = time.time()
+    W = build_workload(args, workload, mode, rank, world)
     gen_s = time.time() - t0
-    nc, nn = cells.shape[0], coords.shape[0]
-    mesh = Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"] if world > 1 else None)
-    bsr = fem.BSRFormat(1)
+    cells, coords, part, op, dim, bs = W["cells"], W["coords"], W["part"], W["op"], W["dim"], W["bs"]
+    nc, nn, nv = cells.shape[0], coords.shape[0], cells.shape[1]
+    mesh = Mesh.from_numpy(dim, cells, coords, cell_is_own=part["cell_is_own"] if world > 1 else None)
+    bsr = fem.BSRFormat(bs)
     bsr.initialize(mesh, True, assembly_variant=args.variant, fan_mode=args.fan_mode, sparsity_build=args.sparsity_build)
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    bsr.computeSparsity()
-    ev1.record()
-    torch.cuda.synchronize()
-    sparsity_cold_ms = ev0.elapsed_time(ev1)
-    ev0.record()
-    bsr.computeSparsity()  # second build: no module load / local-memory set-up inside the timed region
-    ev1.record()
-    torch.cuda.synchronize()
-    sparsity_ms = ev0.elapsed_time(ev1)
+    sp = []
+    for _ in range(2):  # second build: no module load / local-memory set-up inside the timed region
+        ev0.record()
+        bsr.computeSparsity()
+        ev1.record()
+        torch.cuda.synchronize()
+        sp.append(ev0.elapsed_time(ev1))
     mat = bsr.matrix()
-    nnzb = mat.nbCol()
-    nnz = mat.nbNz()
-    op = fem.Operator.laplace()
-
-    exchange = None
-    if world > 1:
-        exchange = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"])
+    nnzb, nnz = mat.nbCol(), mat.nbNz()
+    exchange = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"], comm=comm) if world > 1 else None
+    ls = group = None
+    if workload == "elasticity3d":
+        ls = fem.DoFLinearSystem()
+        bsr.toLinearSystem(ls)
+        group = torch.as_tensor(gen.boundary_nodes(coords, dim - 1, 0.0)).cuda()
 
     def step():
         if exchange is None:
             bsr.assembleBilinear(op)
+            if ls is not None:  # configs[2]: Dirichlet row elimination on z = 0, every component
+                ls.clearValues()
+                for comp in range(bs):
+                    bsr.applyDirichletViaRowElimination(group, 0.0, dof_index=comp)
+                ls.applyDirichlet()
         elif args.no_overlap:
             bsr.assembleBilinear(op)
             exchange.run()
@@ -236,7 +389,8 @@ def run_b200(args):
     if exchange is not None:
         for _ in range(10):  # untimed: NCCL channel / proxy set-up for the neighbour pattern
             exchange.run()
-    for _ in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
         step()
     torch.cuda.synchronize()
     # the sampler is started before the barrier: starting it takes milliseconds on rank 0 alone, and a rank that enters
@@ -262,10 +416,46 @@ def run_b200(args):
         dist.barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
+    stats = bsr.stats()  # error counters of the timed workload itself
+
+    # nonzeros the whole job produced = rows owned by some rank (ghost copies are not counted twice)
+    own_nnz, own_cells_job = nnz, nc
+    own_rows_np = np.arange(nn, dtype=np.int64)
+    receiving = None
+    if world > 1:
+        own_mask = part["node_owner"] == rank
+        own_rows_np = np.nonzero(own_mask)[0]
+        t = torch.stack([mat.nbNzPerRow()[torch.as_tensor(own_mask).cuda()].sum().to(torch.float64), torch.tensor(float(part["nb_own_cell"]), device="cuda", dtype=torch.float64)])
+        dist.all_reduce(t)
+        own_nnz, own_cells_job = int(t[0].item()), int(t[1].item())
+        if rank < world - 1:  # the top own plane is touched by the cells of the rank above: its rows receive partial sums
+            plane = part["plane"]
+            top = part["bounds"][rank + 1] - part["z0"]
+            receiving = np.arange(top * plane, (top + 1) * plane, dtype=np.int64)
+    out = dict(W=W, ms_step=ms_step, own_nnz=own_nnz, own_cells_job=own_cells_job, nnz=nnz, nnzb=nnzb, nc=nc, nn=nn, nv=nv, sparsity_ms=sp[1], sparsity_cold_ms=sp[0], gen_s=gen_s,
+               clocks=clocks, stats=stats, value=own_nnz / (ms_step * 1e-3) / 1e9, overlapped=exchange is not None and not args.no_overlap)
+
+    # --- parity of the matrix the timed loop left behind: a fixed sample of own rows against the host recomputation
+    out["parity"] = None
+    if workload == "poisson3d" and not args.no_parity:
+        try:
+            ps = parity_sample(cells, coords, mat, own_rows_np, receiving)
+            if dist is not None:  # worst rank
+                t = torch.tensor([ps["max_rel"], ps["max_rel_pure"], float(ps["over_1e-12"]), float(ps["columns_missing"])], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                r = torch.tensor([float(ps["rows"]), float(ps["entries"]), float(ps["receiving_rows"])], device="cuda", dtype=torch.float64)
+                dist.all_reduce(r)
+                ps.update({"max_rel": float(t[0]), "max_rel_pure": float(t[1]), "over_1e-12": int(t[2]), "columns_missing": int(t[3]), "rows": int(r[0]), "entries": int(r[1]),
+                           "receiving_rows": int(r[2]), "ranks": world})
+            out["parity"] = ps
+        except Exception as e:
+            out["parity"] = {"error": f"{type(e).__name__}: {e}"}
+            if dist is not None:  # keep the collectives of the other ranks matched
+                raise
 
     # where a multi-GPU step goes: assembly alone and exchange alone, same protocol (reported, not part of `value`)
-    breakdown = None
-    if exchange is not None:
+    out["breakdown"] = None
+    if exchange is not None and full:
         parts = {}
         for name, fn in (("assemble", lambda: bsr.assembleBilinear(op)), ("exchange", exchange.run)):
             torch.cuda.synchronize()
@@ -278,210 +468,274 @@ def run_b200(args):
             t = torch.tensor([ev0.elapsed_time(ev1) / args.steps], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             parts[name + "_ms"] = round(float(t.item()), 4)
-        breakdown = parts
+        out["breakdown"] = parts
 
-    # nonzeros the whole job produced = rows owned by some rank (ghost copies are not counted twice)
-    own_nnz = nnz
-    if world > 1:
-        own_rows = torch.as_tensor(part["node_owner"] == rank).cuda()
-        t = mat.nbNzPerRow()[own_rows].sum().to(torch.float64).reshape(1)
-        dist.all_reduce(t)
-        own_nnz = int(t.item())
-    value = own_nnz / (ms_step * 1e-3) / 1e9
+    out["e2e"] = out["e2e_resident"] = out["path"] = out["cpu"] = None
+    if full:
+        # --- end to end through the host-buffer entry point (rank-local; max over ranks)
+        coords_host = torch.as_tensor(coords).pin_memory()
+        values_host = torch.empty(nnz, dtype=torch.float64).pin_memory()
+        e2e_steps = max(2, min(args.steps, 5))
+        coords_dev = mesh.coords
 
-    # --- end to end through the host-buffer entry point (rank-local; max over ranks)
-    coords_host = torch.as_tensor(coords).pin_memory()
-    values_host = torch.empty(nnz, dtype=torch.float64).pin_memory()
-    e2e_steps = max(2, min(args.steps, 5))
-    coords_dev = mesh.coords
+        def e2e_step(read_back=True):
+            if exchange is None and ls is None:
+                bsr.assembleBilinearHost(op, coords_host, values_host if read_back else None)  # C ABI b2f_assemble_host; synchronises before returning
+            else:
+                coords_dev.copy_(coords_host, non_blocking=True)
+                step()
+                if read_back:
+                    values_host.copy_(mat.values(), non_blocking=True)
+                torch.cuda.synchronize()
 
-    def e2e_step():
-        if exchange is None:
-            bsr.assembleBilinearHost(op, coords_host, values_host)  # C ABI b2f_assemble_host; synchronises before returning
-        else:
-            coords_dev.copy_(coords_host, non_blocking=True)
-            step()
-            values_host.copy_(mat.values(), non_blocking=True)
+        def timed_host(fn):
+            fn()
             torch.cuda.synchronize()
-
-    e2e_step()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
-    if dist is not None:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = own_nnz / e2e_s / 1e9
-    checksum = float(values_host.sum().item())
-
-    # the reference's own data flow keeps the matrix on the device for the Hypre solve (BASELINE.json north_star): same call
-    # with the read-back skipped, coordinates in from pinned host memory, one 8-byte checksum of the values out (reported
-    # beside `e2e`, never instead of it)
-    e2e_resident = None
-    if exchange is None:
-        try:
-            def resident_step():
-                bsr.assembleBilinearHost(op, coords_host, None)
-                return float(mat.values().sum().item())
-
-            resident_step()
-            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
             t0 = time.perf_counter()
             for _ in range(e2e_steps):
-                rs = resident_step()
+                r = fn()
             torch.cuda.synchronize()
-            rs_s = (time.perf_counter() - t0) / e2e_steps
-            e2e_resident = {"value": round(own_nnz / rs_s / 1e9, 3), "unit": UNIT, "ms_per_step": round(rs_s * 1e3, 3), "h2d_bytes_per_step": int(coords_host.numel() * 8),
-                            "d2h_bytes_per_step": 8, "checksum_matches": bool(abs(rs - checksum) <= 1e-9 * max(1.0, float(values_host.abs().sum().item()))),
-                            "api": "b2f_assemble_host(values_host = NULL) + 8-byte checksum read-back: matrix stays device resident for the solver"}
-        except Exception as e:
-            e2e_resident = {"error": f"{type(e).__name__}: {e}"}
+            sec = (time.perf_counter() - t0) / e2e_steps
+            if dist is not None:
+                t = torch.tensor([sec], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                sec = float(t.item())
+            return sec, r
 
-    # --- the rest of the path, each stage on its own (t_sparsity, t_dirichlet, t_tocsr, t_total); reported in
-    # config.path_breakdown_ms, outside the timed region of `value` (single GPU only)
-    path = None
-    if world == 1:
+        e2e_s, _ = timed_host(e2e_step)
+        checksum = float(values_host.sum().item())
+        out["checksum"] = checksum
+        out["e2e"] = {"value": round(own_nnz / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(coords_host.numel() * 8), "d2h_bytes_per_step": int(values_host.numel() * 8),
+                      "ms_per_step": round(e2e_s * 1e3, 3),
+                      "api": "b2f_assemble_host (pinned host coordinates in, values out, pipelined over row chunks)" if exchange is None and ls is None else
+                             "pinned coordinates H2D + the timed step + values D2H, per rank, max over ranks"}
+        # the reference's own data flow keeps the matrix on the device for the Hypre solve (BASELINE.json north_star): same call
+        # with the read-back skipped, coordinates in from pinned host memory, one 8-byte checksum of the values out (reported
+        # beside `e2e`, never instead of it)
         try:
-            path = path_breakdown(torch, fem, gen, bsr, op, coords, sparsity_ms, ms_step)
-        except Exception as e:  # a reporting extra must never cost the bench line
-            path = {"error": f"{type(e).__name__}: {e}"}
+            def resident_step():
+                e2e_step(read_back=False)
+                return float(mat.values().sum().item())
 
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
+            rs_s, rs = timed_host(resident_step)
+            out["e2e_resident"] = {"value": round(own_nnz / rs_s / 1e9, 3), "unit": UNIT, "ms_per_step": round(rs_s * 1e3, 3), "h2d_bytes_per_step": int(coords_host.numel() * 8),
+                                   "d2h_bytes_per_step": 8, "checksum_matches": bool(abs(rs - checksum) <= 1e-9 * max(1.0, float(values_host.abs().sum().item()))),
+                                   "api": "same call with the values read-back skipped + 8-byte checksum read-back: the matrix stays device resident for the solver"}
+        except Exception as e:
+            out["e2e_resident"] = {"error": f"{type(e).__name__}: {e}"}
+            if dist is not None:
+                raise
+        del coords_host, values_host
+        # --- the rest of the path, each stage on its own (t_sparsity, t_dirichlet, t_tocsr, t_total)
+        if world == 1 and workload == "poisson3d":
+            try:
+                out["path"] = path_breakdown(torch, fem, gen, bsr, op, coords, sp[1], ms_step)
+            except Exception as e:  # a reporting extra must never cost the bench line
+                out["path"] = {"error": f"{type(e).__name__}: {e}"}
+        if rank == 0 and world == 1:
+            out["cpu"] = cpu_baseline(workload, W, mat.rowIndexWithEnd().cpu().numpy(), mat.columns().cpu().numpy(), args.cpu_cells)
+    if exchange is not None:
+        exchange.close()
+    del bsr, mesh, mat
+    torch.cuda.empty_cache()
+    return out
 
-    peak, peak_src = measured_peak()
-    stats = bsr.stats()
-    b_alg = algorithmic_bytes(4, nc, nn, nnzb, 1)
-    achieved = b_alg / (ms_step * 1e-3) / 1e9
-    variant_names = {0: "node_gather_fan", 1: "cell_atomic", 2: "cell_atomic_warpagg", 3: "node_gather_fan", 4: "node_gather_slots"}
-    kernel_names = {0: "k_node_fan<LaplaceTet>", 1: "memset + k_cell_atomic<LaplaceTet>", 2: "memset + k_cell_atomic<LaplaceTet,warpagg>", 3: "k_node_fan<LaplaceTet>",
-                    4: "k_node_gather_slots<LaplaceTet>"}
-    # our kernels per step: the assembly kernel (+ pack and add kernels of the ghost exchange; NCCL's own kernels not counted)
-    # (overlapped step: the ghost-row tiles and the remaining rows are two launches of the assembly kernel)
-    overlapped = exchange is not None and not args.no_overlap
-    launches_per_step = (2 if overlapped else 1) + (2 if exchange is not None else 0)
 
-    # --- CPU baseline: oracle port of the reference's legacy loop on this box's host cores (bounded sample)
-    cpu = cpu_baseline(cells, coords, mat.rowIndexWithEnd().cpu().numpy(), mat.columns().cpu().numpy(), args.cpu_cells)
-
-    line = {
-        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"Poisson 3D P1 tets, structured Kuhn cube {n}^3 hexes per GPU ({nc} cells, {nn} nodes, {nnzb} nnz per GPU), BSR 1x1 values assembly",
-                   "variant": variant_names.get(args.variant, str(args.variant)), "n_hex": n, "cells_per_gpu": nc, "nnz_per_gpu": nnz, "nnz_job": own_nnz,
-                   "jitter": 0.25, "cache": "inputs larger than L2 (2.5 GB touched per step vs 126 MB L2)",
-                   "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
-                   "sparsity_build": "row-wise from node->cell lists" if stats["sparsity_by_lists"] else "global edge sort", "sparsity_build_ms": round(sparsity_ms, 3), "sparsity_build_first_call_ms": round(sparsity_cold_ms, 3), "mesh_gen_s": round(gen_s, 2), "values_checksum": checksum,
-                   "step_breakdown": breakdown, "exchange_overlapped": overlapped, "path_breakdown_ms": path,
-                   "fan_walk": ("lockstep" if stats["fan_lockstep"] else "select") if args.variant in (0, 3) else None,
-                   "fan_lockstep_bodies_per_warp_step": stats["fan_lockstep_bodies_milli"] / 1000.0},
-        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC_BYTES if args.variant in (0, 3) and n == 203 and world == 1 else None,
-                     "peak_source": peak_src, "algorithmic_bytes_per_launch": b_alg, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "kernel": kernel_names.get(args.variant, "?"),
-                     "traffic_source": NCU_TRAFFIC_NOTE if args.variant in (0, 3) and n == 203 and world == 1 else None},
-        "cpu_baseline": cpu,
-        "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(coords_host.numel() * 8), "d2h_bytes_per_step": int(values_host.numel() * 8),
-                "ms_per_step": round(e2e_s * 1e3, 3),
-                "api": "b2f_assemble_host (pinned host coordinates in, values out)" if exchange is None else
-                       "pinned coordinates H2D + b2f_assemble_exchange + values D2H, per rank, max over ranks"},
-        "e2e_matrix_resident": e2e_resident,
-        "gpu_launches": launches_per_step * args.steps,
-        "clocks": clocks,
-    }
-    print(json.dumps(line))
+def run_b200(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dist = comm = None
+    workload = args.workload
+    if world > 1:
+        import torch.distributed as dist
+        from arcanefem_b200 import multigpu as mg
+        if workload != "poisson3d":
+            raise SystemExit("multi-GPU runs are defined for --workload poisson3d (BASELINE configs[4])")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        comm = mg.GhostExchange.make_comm(rank, world)
+    mode = "weak" if world == 1 else ("strong" if args.scaling in ("auto", "strong") else "weak")
+    R = run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, full=True)
+    other = None
+    if world > 1 and args.scaling == "auto":
+        other = run_mode(args, workload, "weak", torch, dist, comm, rank, world, local_rank, full=False)
+    if rank == 0:
+        print(json.dumps(make_line(args, workload, mode, world, R, other)))
     if dist is not None:
+        dist.barrier()
         dist.destroy_process_group()
 
 
-def cpu_baseline(cells, coords, ri, co, max_cells):
-    """Oracle port of modules/poisson/FemModule.cc:300-323 + CsrFormatMatrix.h:58-87 on the host cores (variant B
-    = all threads is `value`; variant A = one thread and variant C = the sparsity build, K1-K5 of femutils/BSRFormat.h:602-744
-    executed sequentially, ride along on bounded samples)."""
-    from oracle import oracle as orc
-    threads = orc.num_threads()
-    nc = cells.shape[0]
-    sample = min(nc, max_cells)
+def mode_summary(R, world):
+    return {"value": round(R["value"], 3), "unit": UNIT, "ms_per_step": round(R["ms_step"], 4), "gnnz_per_s_per_gpu": round(R["value"] / world, 3), "nnz_job": R["own_nnz"],
+            "cells_job": R["own_cells_job"], "cells_on_rank0": R["nc"], "sparsity_build_ms": round(R["sparsity_ms"], 3), "parity_sample": R["parity"],
+            "columns_not_found": R["stats"]["columns_not_found"], "gather_fallback_tiles": R["stats"]["gather_fallback_tiles"]}
+
+
+def make_line(args, workload, mode, world, R, other):
+    W = R["W"]
+    dim, bs, _, opname, _ = WORKLOADS[workload]
+    peak, peak_src = measured_peak()
+    per_cell = 8 if opname == "heat" else 0
+    b_alg = algorithmic_bytes(R["nv"], R["nc"], R["nn"], R["nnzb"], bs, per_cell)  # rank 0's launch (the largest slab)
+    achieved = b_alg / (R["ms_step"] * 1e-3) / 1e9
+    variant_names = {0: "node_gather_fan", 1: "cell_atomic", 2: "cell_atomic_warpagg", 3: "node_gather_fan", 4: "node_gather_slots"}
+    default_kernel = args.variant in (0, 3)
+    kernel = KERNEL[workload] if default_kernel else {1: "memset + k_cell_atomic", 2: "memset + k_cell_atomic<warpagg>", 4: "k_node_gather_slots"}.get(args.variant, "?")
+    traffic, traffic_src = ncu_traffic(workload) if (default_kernel and world == 1 and not args.n) else (None, None)
+    # our kernels per step: the assembly kernel (+ pack and add kernels of the ghost exchange; NCCL's own kernels not counted;
+    # overlapped step: the travelling rows, the rows before them and the rows after them are separate launches of the kernel)
+    if world > 1:
+        launches = (3 if R["overlapped"] else 1) + 2
+    else:
+        launches = 6 if workload == "elasticity3d" else 1  # + 3 flag kernels + k_any_rowcol + k_dirichlet_rows
+    stats = R["stats"]
+    line = {
+        "metric": METRIC, "value": round(R["value"], 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": round(R["ms_step"], 4), "higher_is_better": True, "scaling": mode, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_text(workload, mode, W["n"], world, W["nz_total"]), "name": workload, "n_hex": W["n"], "nz_hex_total": W["nz_total"],
+                   "variant": variant_names.get(args.variant, str(args.variant)), "cells_on_rank0": R["nc"], "nnz_on_rank0": R["nnz"], "nnz_job": R["own_nnz"], "cells_job": R["own_cells_job"],
+                   "jitter": 0.25, "cache": "inputs larger than L2 (GBs touched per step vs 126 MB L2)",
+                   "parallelism": "1 rank per GPU, z-slab decomposition with a ghost-cell layer (Arcane style), own cells assembled once, NCCL ghost-row exchange" if world > 1 else "single GPU",
+                   "sparsity_build": "row-wise from node->cell lists" if stats["sparsity_by_lists"] else "global edge sort", "sparsity_build_ms": round(R["sparsity_ms"], 3),
+                   "sparsity_build_first_call_ms": round(R["sparsity_cold_ms"], 3), "mesh_gen_s": round(R["gen_s"], 2), "values_checksum": R.get("checksum"),
+                   "columns_not_found": stats["columns_not_found"], "gather_fallback_tiles": stats["gather_fallback_tiles"],
+                   "step_breakdown": R["breakdown"], "exchange_overlapped": R["overlapped"], "path_breakdown_ms": R["path"],
+                   "step": "values assembly + Dirichlet row elimination on z = 0 (3 components)" if workload == "elasticity3d" else "values assembly" + (" + ghost-row exchange" if world > 1 else "")},
+        "parity_sample": R["parity"],
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": b_alg, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "kernel": kernel, "traffic_source": traffic_src,
+                     "note": None if world == 1 else "rank 0's slab; the step time includes the exchange"},
+        "cpu_baseline": R["cpu"],
+        "e2e": R["e2e"],
+        "e2e_matrix_resident": R["e2e_resident"],
+        "gpu_launches": launches * args.steps,
+        "clocks": R["clocks"],
+    }
+    if world > 1:
+        line["per_gpu"] = {"gnnz_per_s": round(R["value"] / world, 3), "cells": R["own_cells_job"] // world}
+        line["cpu_baseline"] = {"value": None, "note": "timed by the reference arm (bench.py --impl reference) and at N = 1; not repeated on every rank"}
+        if other is not None:
+            line["weak_scaling"] = dict(mode_summary(other, world), workload=workload_text(workload, "weak", other["W"]["n"], world, other["W"]["nz_total"]), scaling="weak")
+    return line
+
+
+def cpu_seconds(orc, workload, cells, coords, ri, co, threads):
+    """One pass of the CPU port over `cells` (seconds).  Laplace / heat: the reference's legacy loop (modules/poisson/FemModule.cc:300-323
+    + CSR add femutils/CsrFormatMatrix.h:58-87), OpenMP over cells + atomics (Arcane -A,T=n analogue).  Elasticity BS = 3 has no
+    legacy twin in the reference: the oracle's sequential cell-wise BSR assembly (femutils/BSRFormat.h:786-837 semantics)."""
+    dim, bs, _, opname, _ = WORKLOADS[workload]
+    if opname == "elasticity":
+        E, nu = 21.0e5, 0.28
+        t0 = time.perf_counter()
+        orc.assemble(cells, coords, ri, co, bs=bs, per_block=False, op=orc.OP_ELASTICITY, lambda_=E * nu / ((1 + nu) * (1 - 2 * nu)), mu2=E / (1 + nu))
+        return time.perf_counter() - t0, 1
     vals = np.zeros(co.shape[0])
-    threads, secs = best_cpu_threads(orc, cells[:sample], coords, ri, co, vals, threads)
-    nnz_sample = co.shape[0] * (sample / nc)
-    out = {"value": round(nnz_sample / secs / 1e9, 4), "unit": UNIT, "cores": threads, "kind": "port",
+    kw = dict(op=orc.OP_HEAT, lambda_=1.75, inv_dt=10.0) if opname == "heat" else {}
+    return orc.legacy_assemble_csr(cells, coords, ri, co, vals, threads=threads, **kw), threads
+
+
+def best_cpu_threads(orc, workload, cells, coords, ri, co, max_threads):
+    """The threaded loop uses fp64 atomics like Arcane's thread runner; on some hosts fewer threads are faster: probe."""
+    if WORKLOADS[workload][3] == "elasticity":
+        return 1
+    probe = cells[:min(cells.shape[0], 400000)]
+    best_t, best_rate = 1, 0.0
+    for t in sorted({1, max(1, max_threads // 2), max_threads}):
+        s, _ = cpu_seconds(orc, workload, probe, coords, ri, co, t)
+        if probe.shape[0] / s > best_rate:
+            best_t, best_rate = t, probe.shape[0] / s
+    return best_t
+
+
+def cpu_baseline(workload, W, ri, co, max_cells):
+    """Oracle port of the reference's CPU assembly on the host cores, bounded sample of the same mesh (variant B =
+    all threads is `value`; variant A = one thread and variant C = the sparsity build ride along)."""
+    from oracle import oracle as orc
+    cells, coords = W["cells"], W["coords"]
+    bs = W["bs"]
+    nc = cells.shape[0]
+    sample = min(nc, max_cells if WORKLOADS[workload][3] != "elasticity" else min(max_cells, 2_000_000))
+    threads = best_cpu_threads(orc, workload, cells[:sample], coords, ri, co, host_threads())
+    secs, threads = cpu_seconds(orc, workload, cells[:sample], coords, ri, co, threads)
+    nnz = co.shape[0] * bs * bs
+    out = {"value": round(nnz * (sample / nc) / secs / 1e9, 4), "unit": UNIT, "cores": threads, "kind": "port", "host_cores": host_threads(),
            "sample": f"first {sample} of {nc} cells of the same mesh, one pass, {secs:.2f} s; nnz credited pro rata"}
     try:
-        one = min(sample, 10_000_000)
-        vals[:] = 0
-        s1 = orc.legacy_assemble_csr(cells[:one], coords, ri, co, vals, threads=1)
-        out["single_thread"] = {"value": round(co.shape[0] * (one / nc) / s1 / 1e9, 4), "unit": UNIT, "sample": f"first {one} cells, {s1:.2f} s"}
-        from arcanefem_b200 import mesh as gen
-        n_sp = 64
-        c_sp, x_sp = gen.cube_kuhn(n_sp)
-        t0 = time.perf_counter()
-        ri_sp, co_sp = orc.build_pattern(c_sp, x_sp.shape[0])
-        s_sp = time.perf_counter() - t0
-        out["sparsity_build"] = {"value": round(co_sp.shape[0] / s_sp / 1e9, 4), "unit": "GNNZ/s of pattern", "cores": 1,
-                                 "sample": f"Kuhn cube {n_sp}^3 ({c_sp.shape[0]} cells, {co_sp.shape[0]} blocks), {s_sp:.2f} s"}
+        if workload == "poisson3d":
+            one = min(sample, 5_000_000)
+            s1, _ = cpu_seconds(orc, workload, cells[:one], coords, ri, co, 1)
+            out["single_thread"] = {"value": round(nnz * (one / nc) / s1 / 1e9, 4), "unit": UNIT, "sample": f"first {one} cells, {s1:.2f} s"}
+            from arcanefem_b200 import mesh as gen
+            c_sp, x_sp = gen.cube_kuhn(64)
+            t0 = time.perf_counter()
+            _, co_sp = orc.build_pattern(c_sp, x_sp.shape[0])
+            s_sp = time.perf_counter() - t0
+            out["sparsity_build"] = {"value": round(co_sp.shape[0] / s_sp / 1e9, 4), "unit": "GNNZ/s of pattern", "cores": 1,
+                                     "sample": f"Kuhn cube 64^3 ({c_sp.shape[0]} cells, {co_sp.shape[0]} blocks), {s_sp:.2f} s"}
     except Exception as e:  # extras only
         out["extras_error"] = f"{type(e).__name__}: {e}"
     return out
 
 
-def best_cpu_threads(orc, cells, coords, ri, co, vals, max_threads):
-    """The threaded loop uses fp64 atomics like Arcane's thread runner; on some hosts one thread is faster.
-    Probe on a small prefix, then time the whole sample with the faster setting."""
-    probe = cells[:min(cells.shape[0], 400000)]
-    best_t, best_rate = 1, 0.0
-    for t in sorted({1, max(1, max_threads // 2), max_threads}):
-        vals[:] = 0
-        s = orc.legacy_assemble_csr(probe, coords, ri, co, vals, threads=t)
-        if probe.shape[0] / s > best_rate:
-            best_t, best_rate = t, probe.shape[0] / s
-    vals[:] = 0
-    secs = orc.legacy_assemble_csr(cells, coords, ri, co, vals, threads=best_t)
-    return best_t, secs
-
-
 def run_reference(args):
-    """CPU restatement of the reference's own CPU assembly (legacy loop), all host threads, same workload."""
+    """CPU restatement of the reference's own CPU assembly, all host threads, on a bounded sample of the b200 arm's job:
+    the first hex layers (poisson3d) / the first cells (other workloads) of the same mesh.  Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
     from arcanefem_b200 import mesh as gen
-    from oracle import oracle as orc
-    n = args.n
     from arcanefem_b200 import multigpu as mg
-    part = mg.slab_partition(n, 0, 1)  # the same mesh as rank 0 of the b200 arm at N = 1
-    cells, coords = part["cells"], part["coords"]
-    nc, nn = cells.shape[0], coords.shape[0]
-    threads = orc.num_threads()
+    from oracle import oracle as orc
+    workload = args.workload
+    dim, bs, n_default, opname, _ = WORKLOADS[workload]
+    mode = "weak" if world == 1 else ("strong" if args.scaling in ("auto", "strong") else "weak")
+    if workload == "poisson3d":
+        if world > 1 and mode == "strong":
+            n = nz_total = args.n_global
+        else:
+            n, nz_total = (args.n or n_default), (args.n or n_default) * world
+        layers = max(1, min(nz_total, args.cpu_cells // (6 * n * n)))
+        part = mg.slab_partition(n, 0, 1, nz_total=nz_total, max_layers=layers)  # the first `layers` hex layers of the job's mesh
+        cells, coords = part["cells"], part["coords"]
+        job_cells = 6 * n * n * nz_total
+        nnz_job = None
+        sample_txt = f"the first {layers} of {nz_total} hex layers of the job's mesh ({cells.shape[0]} of {job_cells} cells) per step"
+    else:
+        n = nz_total = args.n or n_default
+        cells, coords = gen.cube_kuhn(n) if dim == 3 else gen.square(n)
+        job_cells = cells.shape[0]
+        keep = min(job_cells, args.cpu_cells if opname != "elasticity" else min(args.cpu_cells, 2_000_000))
+        sample_txt = f"the first {keep} of {job_cells} cells of the job's mesh per step"
+        # a prefix of the cells only touches a prefix of the nodes (lexicographic numbering): pattern over those
+        cells = cells[:keep]
+        nn_used = int(cells.max()) + 1
+        coords = coords[:nn_used]
+    nn = coords.shape[0]
     ri, co = orc.build_pattern(cells, nn)  # untimed: the metric is the values assembly on an existing pattern
-    nnz = co.shape[0]
-    sample = min(nc, args.cpu_cells)
-    vals = np.zeros(nnz)
-    threads, _ = best_cpu_threads(orc, cells[:min(sample, 400000)], coords, ri, co, vals, threads)
+    nnz_sample = co.shape[0] * bs * bs
+    threads = best_cpu_threads(orc, workload, cells, coords, ri, co, host_threads())
     times = []
-    for it in range(max(args.warmup, 1) + args.steps):
-        vals[:] = 0
-        s = orc.legacy_assemble_csr(cells[:sample], coords, ri, co, vals, threads=threads)
-        if it >= max(args.warmup, 1):
+    warm = max(args.warmup, 1)
+    for it in range(warm + args.steps):
+        s, used = cpu_seconds(orc, workload, cells, coords, ri, co, threads)
+        if it >= warm:
             times.append(s)
     sec = float(np.mean(times))
-    nnz_sample = nnz * (sample / nc)
     value = nnz_sample / sec / 1e9
-    sample_txt = f"first {sample} of {nc} cells per step, {threads} threads; nnz credited pro rata"
     line = {
-        "impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
-        "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"Poisson 3D P1 tets, structured Kuhn cube {n}^3 hexes ({nc} cells, {nn} nodes, {nnz} nnz), CSR values assembly on host cores",
-                   "n_hex": n, "note": "CPU restatement of modules/poisson/FemModule.cc:300-323 (the reference needs Arcane and cannot be built here)"},
-        "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_txt},
+        "impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
+        "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True, "scaling": mode, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_text(workload, mode, n, world, nz_total), "name": workload, "n_hex": n, "nz_hex_total": nz_total, "cells_job": job_cells,
+                   "nnz_of_sample": nnz_sample, "cells_of_sample": int(cells.shape[0]),
+                   "note": "CPU restatement of modules/poisson/FemModule.cc:300-323 (the reference needs Arcane and cannot be built here); value = nonzeros of the "
+                           "sample's matrix / time of one pass over the sample: a throughput, so it compares with the b200 arm's whole-job GNNZ/s"},
+        "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": used, "kind": "port", "host_cores": host_threads(), "sample": sample_txt + f", {used} threads"},
         "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -494,12 +748,16 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=203, help="hexes per side of the per-GPU cube (203 -> 50.2M tets)")
+    ap.add_argument("--workload", default="poisson3d", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="auto", choices=["auto", "weak", "strong"], help="N > 1: auto = strong (configs[4]) with the weak run nested in the line")
+    ap.add_argument("--n", type=int, default=0, help="hexes per side (per GPU in the weak mode); 0 = the workload's BASELINE size (203 -> 50.2M tets)")
+    ap.add_argument("--n-global", type=int, default=406, help="hexes per side of the one cube of the strong mode (406 -> 401.5M tets)")
     ap.add_argument("--variant", type=int, default=3, help="1 cell atomic, 2 cell atomic warp-aggregated, 3 node gather")
     ap.add_argument("--fan-mode", type=int, default=0, help="node gather walk on tets: 0 chosen from the plan, 1 select walk, 2 lockstep walk")
     ap.add_argument("--no-overlap", action="store_true", help="N > 1: b2f_assemble then b2f_ghost_exchange in sequence instead of b2f_assemble_exchange")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity sample")
     ap.add_argument("--sparsity-build", type=int, default=0, help="0 default (row-wise from the node->cell lists), 1 global edge sort (the reference's algorithm)")
-    ap.add_argument("--cpu-cells", type=int, default=50_192_562, help="cells of the bounded CPU sample")
+    ap.add_argument("--cpu-cells", type=int, default=20_000_000, help="cells of the bounded CPU sample")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -20,14 +20,19 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, n_hex, q):
+def _worker(rank, world, port, n_hex, q, decomposition="slab", nz_total=None):
     try:
         os.environ["MASTER_ADDR"] = "127.0.0.1"
         os.environ["MASTER_PORT"] = str(port)
         dist.init_process_group("gloo", rank=rank, world_size=world)
         from arcanefem_b200 import multigpu as mg
         from oracle import oracle as orc
-        part = mg.slab_partition(n_hex, rank, world)
+        if decomposition == "slab":
+            part = mg.slab_partition(n_hex, rank, world, nz_total=nz_total)
+            gcells, gcoords = mg.global_mesh(n_hex, world, nz_total=nz_total)
+        else:  # 2 x 2 blocks in y and z: the centre line is shared by four ranks
+            gcells, gcoords = mg.global_mesh(n_hex, 1, nz_total=n_hex)
+            part = mg.partition_by_cell_rank(gcells, gcoords, mg.block_cell_rank(n_hex, 2, world // 2), rank, world)
         cells, coords = part["cells"], part["coords"]
         nn = coords.shape[0]
         ri, co = orc.build_pattern(cells, nn)  # pattern from own + ghost cells
@@ -36,7 +41,6 @@ def _worker(rank, world, port, n_hex, q):
         assert nf == 0
         vals = mg.exchange_reference(part, ri, co, vals, rank, world, dist)
         # undecomposed assembly
-        gcells, gcoords = mg.global_mesh(n_hex, world)
         gri, gco = orc.build_pattern(gcells, gcoords.shape[0])
         gvals, _ = orc.assemble(gcells, gcoords, gri, gco)
         gid = part["node_gid"]
@@ -80,3 +84,26 @@ def test_slab_decomposition_and_ghost_exchange_reproduce_global_assembly(world):
         p.join(timeout=60)
     for rank, msg in res:
         assert msg == "ok", f"rank {rank}: {msg}"
+
+
+def _spawn(world, n_hex, **kw):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_hex, q), kwargs=kw) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in res:
+        assert msg == "ok", f"rank {rank}: {msg}"
+
+
+def test_one_cube_cut_into_uneven_slabs():
+    """BASELINE configs[4] in small: one 7^3 cube, 3 slabs of 3/2/2 layers."""
+    _spawn(3, 7, nz_total=7)
+
+
+def test_block_decomposition_with_a_node_shared_by_four_ranks():
+    _spawn(4, 4, decomposition="block")

@@ -17,18 +17,38 @@ def row_scale(values, row_index, bs):
     return scale[owner]
 
 
+PURE_RTOL = 1e-11  # pure relative error allowed on the entries that do not cancel (|ref| > PURE_FLOOR * row scale)
+PURE_FLOOR = 1e-3
+
+
 def assert_values_close(got, ref, row_index, bs, rtol=RTOL, what="values"):
-    """|d| <= rtol*max(|a|,|b|)  or  |d| <= rtol*||block row||_inf (entries that cancel to ~0; SURVEY.md §7 hard parts)."""
+    """Two checks, both asserted, the measured figures printed and returned:
+    (1) row-norm-relative: |d| <= rtol * max(|a|, |b|, ||block row||_inf) - the floor is what lets entries that cancel to ~0
+        pass (SURVEY.md §7 hard parts); by itself it would also let a small genuine entry carry a large relative error, so
+    (2) pure relative: |d| / |ref| <= PURE_RTOL on every entry with |ref| > PURE_FLOOR * row scale (entries that do not
+        cancel).  The worst pure relative error over |ref| > 1e-6 * row scale is reported too (not asserted: an entry a
+        million times below its row's scale legitimately carries eps * 1e6 of relative error in ANY fp64 summation)."""
     got = np.asarray(got, dtype=np.float64)
     ref = np.asarray(ref, dtype=np.float64)
     assert got.shape == ref.shape, (got.shape, ref.shape)
     assert np.isfinite(got).all(), f"{what}: non-finite entries"
     d = np.abs(got - ref)
-    tol = rtol * np.maximum(np.maximum(np.abs(got), np.abs(ref)), row_scale(ref, row_index, bs))
+    scale = row_scale(ref, row_index, bs)
+    tol = rtol * np.maximum(np.maximum(np.abs(got), np.abs(ref)), scale)
     bad = d > tol
     if bad.any():
         i = int(np.argmax(d / np.maximum(tol, 1e-300)))
         raise AssertionError(f"{what}: {int(bad.sum())} of {d.size} entries differ; worst idx {i}: got {got[i]!r} ref {ref[i]!r} |d|={d[i]:.3e} tol={tol[i]:.3e}")
+    aref = np.abs(ref)
+    stats = {"entries": int(d.size), "worst_row_norm_relative": float((d / np.maximum(scale, 1e-300)).max()) if d.size else 0.0}
+    for name, floor in (("worst_pure_relative", PURE_FLOOR), ("worst_pure_relative_1e-6", 1e-6)):
+        m = aref > floor * scale
+        stats[name] = float((d[m] / aref[m]).max()) if m.any() else 0.0
+        stats[name + "_entries"] = int(m.sum())
+    stats["passing_only_through_the_floor"] = int((d > rtol * np.maximum(np.abs(got), aref)).sum())
+    print(f"[parity] {what}: {stats}")
+    assert stats["worst_pure_relative"] <= PURE_RTOL, f"{what}: pure relative error {stats['worst_pure_relative']:.3e} on an entry above {PURE_FLOOR} of its row scale"
+    return stats
 
 
 def assert_vec_close(got, ref, rtol=RTOL, what="vector"):
