@@ -273,6 +273,9 @@ namespace {
   // The walk is built greedily (next = unvisited face neighbour with the fewest unvisited neighbours, Warnsdorff's
   // rule), restarting with a START word when it gets stuck; nearly every row is a single chain.  Rows with more than
   // FAN_MAXC incident cells or more than 1023 blocks use one START + EMIT per cell / clear the `ok` flag.
+#ifndef B2F_FAN_KEEP_PIVOT
+#define B2F_FAN_KEEP_PIVOT 1
+#endif
   constexpr int FAN_MAXC = 64;
   constexpr unsigned FAN_START = 0x80000000u;
 
@@ -423,16 +426,26 @@ namespace {
         d += (nb[i][f] >= 0 && !((visited >> nb[i][f]) & 1ull));
       return d;
     };
-    // best unvisited neighbour of i: returns the omitted-vertex index f (neighbour = nb[i][f]) or -1
-    auto best_next = [&](int i) {
-      int best = -1, bd = 99;
+    // best unvisited neighbour of i: returns the omitted-vertex index f (neighbour = nb[i][f]) or -1.  keep_slot (tets, a
+    // continuing step): slot of the newest window vertex N - the neighbour that omits N keeps the pivot O, and a step that
+    // keeps its pivot skips the ~15 selects of the pivot change in k_node_fan (46 % of the steps changed pivot on the Kuhn
+    // cube with Warnsdorff's rule alone, tools/fan_plan_stats.py).  It is preferred; Warnsdorff's rule (fewest onward moves)
+    // and the slot key order the other candidates and break ties.
+    auto best_next = [&](int i, uint32_t keep_slot) {
+      int best = -1, bd = 99, bp = 9;
       for (int f = 0; f < NO; ++f) {
         const int j = nb[i][f];
         if (j < 0 || ((visited >> j) & 1ull))
           continue;
         const int d = unvisited_degree(j);
-        if (d < bd || (d == bd && key(j) < key(nb[i][best]))) {
+#if B2F_FAN_KEEP_PIVOT
+        const int pc = (NV == 4 && keep_slot != 0u && v[i][f] == keep_slot) ? 0 : 1;
+#else
+        const int pc = 1;
+#endif
+        if (pc < bp || (pc == bp && (d < bd || (d == bd && key(j) < key(nb[i][best]))))) {
           bd = d;
+          bp = pc;
           best = f;
         }
       }
@@ -473,7 +486,7 @@ namespace {
         if (inwin != NO - 1)
           start = true;
       }
-      int fnext = best_next(cur); // vertex of cur that the next cell does not contain (dropped after this cell)
+      int fnext = best_next(cur, start ? 0u : win[0]); // vertex of cur that the next cell does not contain (dropped after this cell)
       if (!start && fnext == fc)
         fnext = -1;
       if (start) {

@@ -833,6 +833,10 @@ struct FanCfg : SlotsCfg<Op>
 #ifndef B2F_FAN_TILE_AHEAD
 #define B2F_FAN_TILE_AHEAD 0
 #endif
+// 0: one tile per CTA.  n > 0: persistent CTAs, n x (SMs x resident CTAs per SM) of them, each walking every gridDim.x-th tile
+#ifndef B2F_FAN_PERSIST
+#define B2F_FAN_PERSIST 0
+#endif
 #ifndef B2F_FAN_WORD_AHEAD
 #define B2F_FAN_WORD_AHEAD 0
 #endif
@@ -849,7 +853,7 @@ struct FanCfg : SlotsCfg<Op>
 // price of one multi-way branch per step.  Rows of a warp that sit in different variants are serialised.  Opt-in
 // (B2F_FAN_LOCKSTEP, plan converted by k_fan_lockstep in sparsity.cu): on B200 it measured slower than the select walk.
 template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC, bool LOCKSTEP>
-__global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap)
+__global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap, long long nb_tiles)
 {
   using C = FanCfg<Op>;
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
@@ -864,7 +868,15 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   uint32_t* steps_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
 
   const int t = threadIdx.x;
-  const long long row0 = ((long long)blockIdx.x + A.first_tile) * C::ROWS;
+  // Persistent form (B2F_FAN_PERSIST, launch_assemble_layout): the grid holds one CTA per resident slot of the device and
+  // every CTA takes the tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the mbarrier is initialised once and its phase
+  // parity alternates.  Non-persistent form: one tile per CTA (nb_tiles == gridDim.x), the loop runs once.
+  if (t == 0)
+    mbar_init(bar, 1);
+  __syncthreads();
+  uint32_t phase = 0;
+  for (long long tile = blockIdx.x; tile < nb_tiles; tile += gridDim.x) {
+  const long long row0 = (tile + A.first_tile) * C::ROWS;
   const long long left = A.nb_node - row0;
   const int nrows = left < C::ROWS ? (int)left : C::ROWS;
   const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
@@ -880,13 +892,13 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       if (t < nrows && (A.node_is_own == nullptr || A.node_is_own[row0 + t] != 0))
         A.rhs[(row0 + t) * BS] += A.rhs_factor * row_measure<NV>(A, row0 + t);
     }
-    return;
+    continue;
   }
 
-  if (t == 0)
-    mbar_init(bar, 1);
-  __syncthreads();
   if (t == 0) {
+    // the previous tile's reads of the staging areas (generic proxy) are ordered before the bulk copies that overwrite
+    // them (async proxy); the __syncthreads at the end of the previous iteration has collected those reads
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     mbar_expect_tx(bar, (uint32_t)(ncols_cp + nstep_cp) * 4u);
     if (ncols_cp > 0)
       tma_load_1d(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
@@ -930,7 +942,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     }
   }
 #endif
-  mbar_wait(bar, 0);
+  mbar_wait(bar, phase);
+  phase ^= 1u;
   __syncthreads();
 
   if (nstep > 0) {
@@ -1245,6 +1258,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   const int tail = head + 2 * nvec;
   if (t == 0 && tail < nval)
     A.values[base + tail] = acc_s[tail] + (add_old ? A.values[base + tail] : 0.0);
+  __syncthreads(); // the next tile of a persistent CTA clears the accumulators and overwrites the staging areas
+  } // tiles of this CTA
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -1292,8 +1307,26 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     long long grid = all - A.first_tile;
     if (A.nb_tile >= 0 && A.nb_tile < grid)
       grid = A.nb_tile;
-    if (grid > 0)
-      kern<<<(unsigned)grid, C::ROWS, smem, stream>>>(A, op, acc_blocks, step_cap);
+    if (grid > 0) {
+      long long ctas = grid;
+#if B2F_FAN_PERSIST
+      // one CTA per resident slot (B2F_FAN_PERSIST = waves of such CTAs; 1 = exactly the resident set)
+      static int sm_count = 0;
+      if (sm_count == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+      }
+      int per_sm = 0;
+      cudaError_t eo = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, C::ROWS, smem);
+      if (eo != cudaSuccess)
+        return eo;
+      const long long resident = (long long)sm_count * (per_sm > 0 ? per_sm : 1) * B2F_FAN_PERSIST;
+      if (resident < ctas)
+        ctas = resident;
+#endif
+      kern<<<(unsigned)ctas, C::ROWS, smem, stream>>>(A, op, acc_blocks, step_cap, grid);
+    }
     return cudaGetLastError();
   }
   if (A.first_tile != 0 || A.nb_tile >= 0)
