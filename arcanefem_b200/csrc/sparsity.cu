@@ -429,8 +429,8 @@ namespace {
     // best unvisited neighbour of i: returns the omitted-vertex index f (neighbour = nb[i][f]) or -1.  keep_slot (tets, a
     // continuing step): slot of the newest window vertex N - the neighbour that omits N keeps the pivot O, and a step that
     // keeps its pivot skips the ~15 selects of the pivot change in k_node_fan (46 % of the steps changed pivot on the Kuhn
-    // cube with Warnsdorff's rule alone, tools/fan_plan_stats.py).  It is preferred; Warnsdorff's rule (fewest onward moves)
-    // and the slot key order the other candidates and break ties.
+    // cube with slot-key tie-breaks, tools/fan_plan_stats.py).  Warnsdorff's rule (fewest onward moves) still decides
+    // first - preferring the pivot outright left a few rows with a second chain - the pivot breaks its ties, then the slot key.
     auto best_next = [&](int i, uint32_t keep_slot) {
       int best = -1, bd = 99, bp = 9;
       for (int f = 0; f < NO; ++f) {
@@ -443,7 +443,7 @@ namespace {
 #else
         const int pc = 1;
 #endif
-        if (pc < bp || (pc == bp && (d < bd || (d == bd && key(j) < key(nb[i][best]))))) {
+        if (d < bd || (d == bd && (pc < bp || (pc == bp && key(j) < key(nb[i][best]))))) {
           bd = d;
           bp = pc;
           best = f;

@@ -757,7 +757,7 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="N > 1: b2f_assemble then b2f_ghost_exchange in sequence instead of b2f_assemble_exchange")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity sample")
     ap.add_argument("--sparsity-build", type=int, default=0, help="0 default (row-wise from the node->cell lists), 1 global edge sort (the reference's algorithm)")
-    ap.add_argument("--cpu-cells", type=int, default=20_000_000, help="cells of the bounded CPU sample")
+    ap.add_argument("--cpu-cells", type=int, default=60_000_000, help="cells of the bounded CPU sample (the N = 1 mesh has 50.2 M: one whole pass)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
