@@ -242,19 +242,20 @@ def slab_bounds_of(nz_total, world):
     return mg.slab_bounds(nz_total, world)
 
 
-def laplace_tet_rows_reference(cells, coords, ri, co, rows):
+def laplace_tet_rows_reference(cells, coords, ri, co, rows, extended=True):
     """Rows `rows` of the P1 Laplace matrix from the cells that touch them, in extended precision (numpy longdouble), from the
     reference's formula Ke[a][b] = V grad_a . grad_b with grad = cofactor / (6V) (femutils/ArcaneFemFunctionsGpu.h:110-122,280-392,
     modules/poisson/FemModule.h:177-186).  Independent of oracle/ and of the CUDA formulation.  Returns (ref [n, kmax], mask)."""
     rows = np.asarray(rows, dtype=np.int64)
+    real = np.longdouble if extended else np.float64
     nn = coords.shape[0]
     pos = np.full(nn, -1, dtype=np.int32)
     pos[rows] = np.arange(rows.shape[0], dtype=np.int32)
     touch = (pos[cells] >= 0).any(axis=1)
     sel = cells[touch].astype(np.int64)
-    X = coords[sel].astype(np.longdouble)  # [m, 4, 3]
+    X = coords[sel].astype(real)  # [m, 4, 3]
     e1, e2, e3 = X[:, 1] - X[:, 0], X[:, 2] - X[:, 0], X[:, 3] - X[:, 0]
-    g = np.empty((sel.shape[0], 4, 3), dtype=np.longdouble)
+    g = np.empty((sel.shape[0], 4, 3), dtype=real)
     g[:, 1], g[:, 2], g[:, 3] = np.cross(e2, e3), np.cross(e3, e1), np.cross(e1, e2)
     g[:, 0] = -(g[:, 1] + g[:, 2] + g[:, 3])
     det = (e1 * g[:, 1]).sum(axis=1)
@@ -264,7 +265,7 @@ def laplace_tet_rows_reference(cells, coords, ri, co, rows):
     cols = np.full((rows.shape[0], kmax), -1, dtype=np.int64)
     mask = np.arange(kmax)[None, :] < k[:, None]
     cols[mask] = co[(ri[rows].astype(np.int64)[:, None] + np.arange(kmax)[None, :])[mask]]
-    ref = np.zeros((rows.shape[0], kmax), dtype=np.longdouble)
+    ref = np.zeros((rows.shape[0], kmax), dtype=real)
     missing = 0
     for a in range(4):
         p = pos[sel[:, a]]
@@ -300,7 +301,12 @@ def parity_sample(cells, coords, mat, own_rows, receiving_rows, nrows=10000, see
     rel = (d / np.maximum(np.abs(ref), 1e-3 * rowmax))[mask]
     big = mask & (np.abs(ref) > 1e-6 * rowmax)
     pure = (d[big] / np.abs(ref[big]))
+    # the same formula in plain fp64 on the host: what ANY fp64 evaluation loses on the sample's worst-conditioned cells (a jittered
+    # mesh holds a few nearly flat tetrahedra, where the determinant alone costs kappa * eps)
+    ref64, _, _ = laplace_tet_rows_reference(cells, coords, ri, co, rows, extended=False)
+    rel64 = (np.abs(ref64.astype(np.longdouble) - ref) / np.maximum(np.abs(ref), 1e-3 * rowmax))[mask]
     return {"rows": int(rows.shape[0]), "entries": int(mask.sum()), "max_rel": float(rel.max()), "max_rel_pure": float(pure.max()), "over_1e-12": int((rel > 1e-12).sum()),
+            "host_fp64_same_formula_max_rel": float(rel64.max()), "host_fp64_over_1e-12": int((rel64 > 1e-12).sum()),
             "columns_missing": missing, "receiving_rows": int(pick[0].shape[0]) if len(pick) > 1 else 0,
             "rule": "|d| / max(|ref|, 1e-3 * row max); ref = extended-precision host recomputation of the sampled rows (numpy longdouble, reference formula)"}
 
@@ -441,11 +447,12 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
         try:
             ps = parity_sample(cells, coords, mat, own_rows_np, receiving)
             if dist is not None:  # worst rank
-                t = torch.tensor([ps["max_rel"], ps["max_rel_pure"], float(ps["over_1e-12"]), float(ps["columns_missing"])], device="cuda", dtype=torch.float64)
+                t = torch.tensor([ps["max_rel"], ps["max_rel_pure"], float(ps["over_1e-12"]), float(ps["columns_missing"]), ps["host_fp64_same_formula_max_rel"],
+                                  float(ps["host_fp64_over_1e-12"])], device="cuda", dtype=torch.float64)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 r = torch.tensor([float(ps["rows"]), float(ps["entries"]), float(ps["receiving_rows"])], device="cuda", dtype=torch.float64)
                 dist.all_reduce(r)
-                ps.update({"max_rel": float(t[0]), "max_rel_pure": float(t[1]), "over_1e-12": int(t[2]), "columns_missing": int(t[3]), "rows": int(r[0]), "entries": int(r[1]),
+                ps.update({"max_rel": float(t[0]), "max_rel_pure": float(t[1]), "over_1e-12": int(t[2]), "columns_missing": int(t[3]), "host_fp64_same_formula_max_rel": float(t[4]), "host_fp64_over_1e-12": int(t[5]), "rows": int(r[0]), "entries": int(r[1]),
                            "receiving_rows": int(r[2]), "ranks": world})
             out["parity"] = ps
         except Exception as e:

@@ -14,6 +14,7 @@
 // A2 (signed, triangles) or V6 = |det| (tetrahedra, like the reference: the sign drops out of every quadratic form).
 #pragma once
 #include <cmath>
+#include <initializer_list>
 #include "../b2f/user_operator.cuh"
 
 #define B2F_HD __host__ __device__ __forceinline__
@@ -39,9 +40,20 @@ template <int N, int M>
 struct FixedMatrix // femutils/FemUtils.h:53-186
 {
   Real m_values[N * M];
+  static constexpr int totalNbElement() { return N * M; }
+  static constexpr int rows = N, cols = M;
   B2F_HD FixedMatrix()
   {
     for (int q = 0; q < N * M; ++q)
+      m_values[q] = 0.0;
+  }
+  // femutils/FemUtils.h:62: row-major list; entries the list does not reach stay zero
+  B2F_HD FixedMatrix(std::initializer_list<Real> init_list)
+  {
+    int q = 0;
+    for (auto it = init_list.begin(); it != init_list.end() && q < N * M; ++it)
+      m_values[q++] = *it;
+    for (; q < N * M; ++q)
       m_values[q] = 0.0;
   }
   B2F_HD Real& operator()(int i, int j) { return m_values[i * M + j]; }
@@ -89,6 +101,56 @@ B2F_HD FixedMatrix<N, M> operator/(const FixedMatrix<N, M>& a, Real f)
   for (int q = 0; q < N * M; ++q)
     r.m_values[q] = a.m_values[q] / f;
   return r;
+}
+template <int N, int M>
+B2F_HD FixedMatrix<N, M> operator-(const FixedMatrix<N, M>& a) // femutils/FemUtils.h:126-135
+{
+  FixedMatrix<N, M> r;
+  for (int q = 0; q < N * M; ++q)
+    r.m_values[q] = -a.m_values[q];
+  return r;
+}
+// femutils/FemUtils.h:217-226: column ^ row = outer product
+template <int N>
+B2F_HD FixedMatrix<N, N> operator^(const FixedMatrix<N, 1>& lhs, const FixedMatrix<1, N>& rhs)
+{
+  FixedMatrix<N, N> r;
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j)
+      r(i, j) = lhs(i, 0) * rhs(0, j);
+  return r;
+}
+// femutils/FemUtils.h:266-276, :281-297, :302-313
+template <int N, int M>
+B2F_HD FixedMatrix<N, N> matrixAddition(const FixedMatrix<N, M>& a, const FixedMatrix<M, N>& b)
+{
+  FixedMatrix<N, N> r;
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j)
+      r(i, j) = a(i, j) + b(i, j);
+  return r;
+}
+template <int N, int M>
+B2F_HD FixedMatrix<N, N> matrixMultiplication(const FixedMatrix<N, M>& a, const FixedMatrix<M, N>& b)
+{
+  FixedMatrix<N, N> r;
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j) {
+      Real x = 0.0;
+      for (int k = 0; k < M; ++k)
+        x += a(i, k) * b(k, j);
+      r(i, j) += x;
+    }
+  return r;
+}
+template <int N, int M>
+B2F_HD FixedMatrix<M, N> matrixTranspose(const FixedMatrix<N, M>& a)
+{
+  FixedMatrix<M, N> t;
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < M; ++j)
+      t(j, i) = a(i, j);
+  return t;
 }
 // femutils/FemUtils.h:191-226: u ^ v = u v^T
 B2F_HD FixedMatrix<3, 3> operator^(const Real3& u, const Real3& v)

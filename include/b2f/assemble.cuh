@@ -1274,9 +1274,25 @@ template <class Op>
 struct uses_fan<Op, std::enable_if_t<Op::NO_FAN>> : std::false_type
 {};
 
+// Operators whose callback is addressed by the cell id alone and answers in the cell's OWN vertex order (the reference's
+// `FixedMatrix f(CellLocalId)`, which gathers through its own connectivity view) declare `static constexpr bool OWN_ORDER =
+// true`: the node gather hands cells over in a permuted order, so such operators always run on the cell-wise kernel
+// (the reference's own algorithm, femutils/BSRFormat.h:786-898), whatever variant the handle was created with.
+template <class Op, class = void>
+struct own_order : std::false_type
+{};
+template <class Op>
+struct own_order<Op, std::enable_if_t<Op::OWN_ORDER>> : std::true_type
+{};
+
 template <class Op, bool PER_BLOCK>
 inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, int variant, long long nb_values, cudaStream_t stream)
 {
+  if constexpr (own_order<Op>::value) {
+    if (A.first_tile != 0 || A.nb_tile >= 0)
+      return cudaErrorInvalidValue;
+    variant = VARIANT_CELL_ATOMIC;
+  }
   if constexpr (uses_fan<Op>::value)
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
     using C = FanCfg<Op>;

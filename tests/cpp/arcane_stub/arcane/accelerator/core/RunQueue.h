@@ -1,11 +1,3 @@
+// forwards to the model of the Arcane types (tests/cpp/arcane_stub/arcane_mock.h); Arcane itself is not installed here
 #pragma once
-#include "../../core/IMesh.h"
-namespace Arcane { namespace Accelerator {
-// stub of RunQueue: the two members the adapter uses
-class RunQueue
-{
- public:
-  eMemoryRessource memoryRessource() const { return eMemoryRessource::UnifiedMemory; }
-  void* platformStream() const { return nullptr; }
-};
-}} // namespace Arcane::Accelerator
+#include "../../../arcane_mock.h"

@@ -1,2 +1,3 @@
+// forwards to the model of the Arcane types (tests/cpp/arcane_stub/arcane_mock.h); Arcane itself is not installed here
 #pragma once
-#include "IMesh.h" // stub: groups live with the mesh
+#include "../../arcane_mock.h"
