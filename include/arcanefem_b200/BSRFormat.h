@@ -6,7 +6,7 @@
 //   femutils/ArcaneFemFunctionsGpu.h  FemUtils::Gpu::BoundaryConditions* (:434-768)
 // so a module's FemModule code reads unchanged.  Differences forced by the C ABI:
 //   * Arcane handles (ITraceMng*, RunQueue&, IMesh*, node/face groups) become a b2f_mesh_view, a stream and device id
-//     lists; arcanefem_b200/ArcaneAdapter.h (needs Arcane, not compilable without it) builds them from Arcane objects;
+//     lists; the Arcane-typed signatures live in arcanefem_b200/arcane/*.h (they need Arcane or the model of tests/cpp/arcane_stub);
 //   * the element lambda of assembleBilinear becomes an Operator descriptor (Laplace / Elasticity / Heat);
 //   * NumArray accessors return non-owning device spans.
 // Errors: the reference throws ArgumentException / NotImplementedException / std::runtime_error; here every non-zero
@@ -190,6 +190,7 @@ class BSRFormat
     opt.use_csr = does_linear_system_use_csr ? 1 : 0;
     opt.assembly_variant = (assembly_variant == B2F_ASM_DEFAULT && use_atomic_free) ? B2F_ASM_NODE_GATHER : assembly_variant;
     check(b2f_create(&mesh, &opt, &m_h));
+    m_use_csr_in_linear_system = does_linear_system_use_csr;
   }
   void computeSparsity() { check(b2f_compute_sparsity(m_h, m_stream)); } // BSRFormat.h:775-781
   void assembleBilinear(const Operator& op) { check(b2f_assemble(m_h, &op.desc, m_stream)); } // BSRFormat.h:1105-1111
@@ -216,12 +217,17 @@ class BSRFormat
   }
   void assembleBilinearAndExchange(const Operator& op) { check(b2f_assemble_exchange(m_h, &op.desc, m_comm, m_stream)); }
   // BSRFormat.h:414-430: hands the CSR view to the linear system (views stay valid until the next computeSparsity)
+  // A CSR consumer (m_use_csr_in_linear_system, :416-427) gets the CSR view; any other linear system (the per-block branch,
+  // BSRMatrix::toLinearSystem :261-280, which adds entry by entry on the host) is attached to the same device-resident
+  // values: the Dirichlet / rhs entries of the C ABI handle both layouts.
   void toLinearSystem(DoFLinearSystem& linear_system)
   {
-    if (!linear_system.hasSetCSRValues())
-      throw std::invalid_argument("BSRFormat(toLinearSystem): Linear system was set to use CSR but is incompatible");
-    linear_system.m_h = &m_h;
-    linear_system.setCSRValues(m_matrix.toCsr(m_stream));
+    linear_system.m_h = &m_h; // attached first: applyDirichlet / rhsVariable / clearValues work for either layout
+    if (m_use_csr_in_linear_system || NB_DOF == 1) {
+      if (!linear_system.hasSetCSRValues())
+        throw std::invalid_argument("BSRFormat(toLinearSystem): Linear system was set to use CSR but is incompatible");
+      linear_system.setCSRValues(m_matrix.toCsr(m_stream));
+    }
   }
   BSRMatrix<NB_DOF>& matrix() { return m_matrix; } // BSRFormat.h:1116
   void resetMatrixValues() { check(b2f_reset_values(m_h, m_stream)); } // :1120-1123
@@ -233,6 +239,7 @@ class BSRFormat
   b2f_handle m_h = nullptr;
   b2f_stream m_stream;
   void* m_comm = nullptr; // ncclComm_t of setGhostExchange
+  bool m_use_csr_in_linear_system = true;
   BSRMatrix<NB_DOF> m_matrix;
 };
 

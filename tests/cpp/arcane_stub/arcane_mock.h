@@ -120,7 +120,12 @@ class CommandLineArguments
   StringList m_args;
 };
 
-struct Real2 { Real x, y; };
+struct Real2
+{
+  Real x = 0, y = 0;
+  Real2() = default;
+  ARCCORE_HOST_DEVICE Real2(Real ax, Real ay) : x(ax), y(ay) {}
+};
 struct Real3
 {
   Real x, y, z;

@@ -112,6 +112,25 @@ int main()
   bool threw = false;
   try { M.getValue(0, nn - 1); } catch (const std::runtime_error&) { threw = true; }
   if (!threw) ++bad;
+  // The per-block branch of toLinearSystem (femutils/BSRFormat.h:261-280,416-427): BSRFormat<3> built for a linear system that
+  // does not take CSR - no CSR view is made, the system is attached all the same and the Dirichlet entries work on it.
+  {
+    BSRFormat<3> el;
+    el.initialize(mesh, /*does_linear_system_use_csr=*/false);
+    el.computeSparsity();
+    el.assembleBilinear(Operator::Elasticity(21.0e5, 0.28));
+    DoFLinearSystem els;
+    el.toLinearSystem(els); // must not throw (round 1: B2F_ERR_STATE from toCsr)
+    if (!el.matrix().orderValuePerBlock() || els.getCSRValues().nbValue() != 0) ++bad;
+    els.clearValues();
+    check(b2f_rhs_fill(els.handle(), 0.0, nullptr));
+    Gpu::BoundaryConditions::applyDirichletViaRowEliminationVectorial(els, g, 1, 0.25);
+    els.applyDirichlet();
+    cudaDeviceSynchronize();
+    auto erhs = to_host(els.rhsVariable().data(), 3 * nn);
+    if (el.matrix().getValue(3 * 5 + 1, 3 * 5 + 1) != 1.0 || el.matrix().getValue(3 * 5 + 1, 3 * 5 + 0) != 0.0 || erhs[3 * 5 + 1] != 0.25) ++bad;
+    if (el.matrix().getValue(3 * 5 + 0, 3 * 5 + 0) == 1.0) ++bad; // the other components keep their rows
+  }
   std::printf("poisson_driver: nn=%lld nc=%lld nnz=%d rhs_sum=%.12g bad=%d\n", (long long)nn, (long long)nc, M.nbNz(), total, bad);
   return bad == 0 ? 0 : 2;
 }

@@ -45,21 +45,22 @@ NVCC = os.path.join(CUDA, "bin", "nvcc")
 BODY_BLOCKS = None
 
 
-def build_unchanged_module(tmp_path):
+def build_unchanged_module(tmp_path, name="poisson_module_unchanged"):
     """tests/cpp/poisson_module_unchanged.cu: the reference's Poisson module text (tests/cpp/poisson_module_body.inc) against the
     Arcane-typed drop-in headers include/arcanefem_b200/arcane/*.h and the model of the Arcane types (tests/cpp/arcane_stub),
     compiled as CUDA with warnings as errors - the reference compiles its modules as CUDA too (femutils/CMakeLists.txt:3-7)."""
-    exe = str(tmp_path / "poisson_module_unchanged")
+    exe = str(tmp_path / name)
     libdir = os.path.join(ROOT, "arcanefem_b200", "lib")
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O1", "--extended-lambda", "-Xcompiler", "-Wall,-Werror", f"-I{ROOT}/include",
-           f"-I{ROOT}/tests/cpp/arcane_stub", f"-I{ROOT}/tests/cpp", os.path.join(ROOT, "tests", "cpp", "poisson_module_unchanged.cu"), "-o", exe, f"-L{libdir}", "-lb200fem",
+           f"-I{ROOT}/tests/cpp/arcane_stub", f"-I{ROOT}/tests/cpp", os.path.join(ROOT, "tests", "cpp", name + ".cu"), "-o", exe, f"-L{libdir}", "-lb200fem",
            "-Xlinker", f"-rpath={libdir}"]
     subprocess.check_call(cmd)
     return exe
 
 
-def test_unchanged_poisson_module_compiles_against_the_drop_in_headers(tmp_path):
-    exe = build_unchanged_module(tmp_path)
+@pytest.mark.parametrize("name", ["poisson_module_unchanged", "elasticity_callback_unchanged"])
+def test_unchanged_reference_text_compiles_against_the_drop_in_headers(tmp_path, name):
+    exe = build_unchanged_module(tmp_path, name)
     try:
         import torch
         has_gpu = torch.cuda.is_available()
@@ -84,13 +85,24 @@ def test_unchanged_poisson_module_on_device(tmp_path):
     print(r.stdout)
 
 
-def test_module_text_is_verbatim():
-    """Every block of tests/cpp/poisson_module_body.inc equals the cited lines of the reference (skipped where /root/reference is
+@pytest.mark.gpu
+def test_unchanged_elasticity_callback_on_device(tmp_path):
+    """modules/elasticity/FemModule.h:112-152 as the callback of BSRFormat<2>::assembleBilinear, both linear-system kinds."""
+    exe = build_unchanged_module(tmp_path, "elasticity_callback_unchanged")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.rstrip().endswith("bad=0"), r.stdout
+    print(r.stdout)
+
+
+@pytest.mark.parametrize("inc,nblocks", [("poisson_module_body.inc", 10), ("elasticity_callback_body.inc", 2)])
+def test_module_text_is_verbatim(inc, nblocks):
+    """Every block of tests/cpp/*_body.inc equals the cited lines of the reference (skipped where /root/reference is
     absent: the GPU box)."""
     ref_root = "/root/reference"
     if not os.path.isdir(ref_root):
         pytest.skip("the reference tree is not on this machine")
-    text = open(os.path.join(ROOT, "tests", "cpp", "poisson_module_body.inc"), encoding="utf-8").read().split("\n")
+    text = open(os.path.join(ROOT, "tests", "cpp", inc), encoding="utf-8").read().split("\n")
     blocks, cur = [], None
     for line in text:
         if line.startswith("// ---- "):
@@ -100,7 +112,7 @@ def test_module_text_is_verbatim():
             blocks.append(cur)
         elif cur is not None:
             cur[3].append(line)
-    assert len(blocks) == 10
+    assert len(blocks) == nblocks
     for name, a, b, lines in blocks:
         ref = open(os.path.join(ref_root, name), encoding="utf-8-sig").read().split("\n")[a - 1:b]
         assert lines[:len(ref)] == ref, f"{name}:{a}-{b} differs from the reference"
