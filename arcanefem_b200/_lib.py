@@ -24,7 +24,7 @@ class MeshView(C.Structure):
 
 class Options(C.Structure):
     _fields_ = [("block_size", C.c_int32), ("use_csr", C.c_int32), ("assembly_variant", C.c_int32), ("fan_mode", C.c_int32),
-                ("sparsity_build", C.c_int32), ("reserved", C.c_int32)]
+                ("sparsity_build", C.c_int32), ("pattern_layout", C.c_int32)]
 
 
 class OperatorDesc(C.Structure):

@@ -23,6 +23,7 @@ from . import _lib
 from ._lib import check
 
 ASM_DEFAULT, ASM_CELL_ATOMIC, ASM_CELL_ATOMIC_WARPAGG, ASM_NODE_GATHER, ASM_NODE_GATHER_SLOTS = 0, 1, 2, 3, 4
+PATTERN_DIAG_FIRST, PATTERN_DIAG_LAST = 0, 1
 OP_LAPLACE, OP_ELASTICITY, OP_HEAT = 0, 1, 2
 ELIMINATE_NONE, ELIMINATE_ROW, ELIMINATE_ROW_COLUMN = 0, 1, 2
 
@@ -272,6 +273,7 @@ class BSRFormat:
         self._nb_dof = int(nb_dof)
         self._h = C.c_void_p()
         self._mesh = None
+        self._use_csr = True
         self._keep = []
 
     def __del__(self):
@@ -282,7 +284,7 @@ class BSRFormat:
         except Exception:
             pass
 
-    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0, sparsity_build=0):
+    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0, sparsity_build=0, pattern_layout=0):
         if mesh is None:
             raise ValueError("BSRFormat(initialize): null mesh")  # ARCANE_CHECK_POINTER, BSRFormat.h:391
         if self._h.value:
@@ -305,8 +307,10 @@ class BSRFormat:
         opt.assembly_variant = int(assembly_variant)
         opt.fan_mode = int(fan_mode)  # b2f_fan_mode: 0 auto, 1 select walk, 2 lockstep walk
         opt.sparsity_build = int(sparsity_build)  # b2f_sparsity_build: 0 auto, 1 global sort, 2 row-wise from the node->cell lists
+        opt.pattern_layout = int(pattern_layout)  # b2f_pattern_layout: 0 diagonal first (sorted-edge build), 1 diagonal last (connectivity build, BSRFormat.h:479-578)
         check(self._lib.b2f_create(C.byref(mv), C.byref(opt), C.byref(self._h)))
         self._mesh = mesh
+        self._use_csr = bool(does_linear_system_use_csr)
 
     def computeSparsity(self):
         check(self._lib.b2f_compute_sparsity(self._h, _stream()))
@@ -331,10 +335,13 @@ class BSRFormat:
         check(self._lib.b2f_set_coords(self._h, C.c_void_p(coords.data_ptr())))
 
     def toLinearSystem(self, linear_system):
-        linear_system._fmt = self
-        if not linear_system.hasSetCSRValues():
-            raise ValueError("BSRFormat(toLinearSystem): Linear system was set to use CSR but is incompatible")
-        linear_system.setCSRValues(self.matrix().toCsr())
+        """femutils/BSRFormat.h:414-430: a CSR consumer gets the CSR view; any other linear system (the per-block branch,
+        BSRMatrix::toLinearSystem :261-280) is attached to the same device-resident values."""
+        linear_system._fmt = self  # attached first: Dirichlet / rhs entries work for either layout
+        if self._use_csr or self._nb_dof == 1:
+            if not linear_system.hasSetCSRValues():
+                raise ValueError("BSRFormat(toLinearSystem): Linear system was set to use CSR but is incompatible")
+            linear_system.setCSRValues(self.matrix().toCsr())
 
     def matrix(self):
         return BSRMatrix(self)

@@ -103,6 +103,10 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown assembly_variant %d", options->assembly_variant);
   if (options->sparsity_build < B2F_SPARSITY_AUTO || options->sparsity_build > B2F_SPARSITY_LISTS)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown sparsity_build %d", options->sparsity_build);
+  if (options->pattern_layout != B2F_PATTERN_DIAG_FIRST && options->pattern_layout != B2F_PATTERN_DIAG_LAST)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown pattern_layout %d", options->pattern_layout);
+  if (options->pattern_layout == B2F_PATTERN_DIAG_LAST && options->assembly_variant == B2F_ASM_NODE_GATHER_SLOTS)
+    return fail(B2F_ERR_NOT_IMPLEMENTED, "b2f_create: the first-generation slot-word kernel (kept for A/B measurements) only knows the diagonal-first layout");
   if (options->fan_mode < B2F_FAN_AUTO || options->fan_mode > B2F_FAN_LOCKSTEP)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown fan_mode %d", options->fan_mode);
   int ndev = 0;
@@ -116,6 +120,7 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
   h->nv = mesh->nodes_per_cell;
   h->per_block = options->use_csr == 0; // order_values_per_block = !does_linear_system_use_csr, BSRFormat.h:405
   h->variant = options->assembly_variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : options->assembly_variant;
+  h->diag_last = options->pattern_layout == B2F_PATTERN_DIAG_LAST ? 1 : 0;
   cudaGetDevice(&h->device);
   *out = h;
   return B2F_OK;

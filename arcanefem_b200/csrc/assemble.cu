@@ -32,6 +32,7 @@ void fill_assemble_args(const b2f_context_s* h, AssembleArgs* out)
     A.tile_extents[i] = h->tile_extents[i];
   A.counters = h->counters.as<unsigned long long>();
   A.accumulate = 0;
+  A.diag_last = h->diag_last;
   *out = A;
 }
 

@@ -152,7 +152,7 @@ namespace {
   template <int NVF>
   __global__ void __launch_bounds__(256) k_add_face_mass(long long nb_face, const int32_t* __restrict__ face_node, double h, const double* __restrict__ coords,
                                                          const uint8_t* __restrict__ own, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
-                                                         double* __restrict__ values, unsigned long long* __restrict__ counters)
+                                                         double* __restrict__ values, unsigned long long* __restrict__ counters, int diag_last)
   {
     const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= nb_face)
@@ -183,7 +183,7 @@ namespace {
       const int k = __ldg(row_index + n[a] + 1) - rb;
 #pragma unroll
       for (int b = 0; b < NVF; ++b) {
-        const int x = (a == b) ? 0 : find_slot(columns + rb, k, n[b]);
+        const int x = (a == b) ? diag_slot(k, diag_last) : find_slot(columns + rb, k, n[b], diag_last);
         if (x < 0)
           atomicAdd(counters, 1ull);
         else
@@ -232,6 +232,7 @@ namespace {
     const double* forced_value;
     double* rhs;
     long long nb_dof;
+    int diag_last;
   };
 
   // Row+column elimination, phase 1 (AlephDoFLinearSystem.cc:540-563): rhs[c] -= A[r,c] * g_r for every stored (r,c),
@@ -255,7 +256,7 @@ namespace {
           continue;
         const int32_t rb = S.row_index[br];
         const int k = S.row_index[br + 1] - rb;
-        const int x = (br == bc) ? 0 : find_slot(S.columns + rb, k, bc);
+        const int x = (br == bc) ? diag_slot(k, S.diag_last) : find_slot(S.columns + rb, k, bc, S.diag_last);
         if (x < 0)
           continue;
         acc = acc - S.values[value_index<BS, PER_BLOCK>(rb, k, x, ir, jc)] * S.elim_value[r];
@@ -304,8 +305,8 @@ namespace {
       }
       S.rhs[r] = S.elim_value[r];
     }
-    if (forced) { // the diagonal block is slot 0
-      double* d = S.values + value_index<BS, PER_BLOCK>(rb, k, 0, ir, ir);
+    if (forced) { // the diagonal block: slot 0, or k - 1 in a diagonal-last row
+      double* d = S.values + value_index<BS, PER_BLOCK>(rb, k, diag_slot(k, S.diag_last), ir, ir);
       *d = (S.forced_info[r] == 2) ? *d + S.forced_value[r] : S.forced_value[r];
     }
   }
@@ -399,10 +400,10 @@ int add_face_mass(b2f_context_s* h, int64_t nb_face, const int32_t* face_node, d
     return B2F_OK;
   if (h->mesh.dim == 2)
     k_add_face_mass<2><<<grid_for(nb_face, 256), 256, 0, s>>>(nb_face, face_node, coefficient, h->mesh.coords, h->mesh.node_is_own, h->row_index.as<int32_t>(),
-                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>());
+                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>(), h->diag_last);
   else
     k_add_face_mass<3><<<grid_for(nb_face, 256), 256, 0, s>>>(nb_face, face_node, coefficient, h->mesh.coords, h->mesh.node_is_own, h->row_index.as<int32_t>(),
-                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>());
+                                                             h->columns.as<int32_t>(), h->values.as<double>(), h->counters.as<unsigned long long>(), h->diag_last);
   B2F_CUDA(cudaGetLastError());
   return B2F_OK;
 }
@@ -438,6 +439,7 @@ int dirichlet_apply(b2f_context_s* h, cudaStream_t s)
   S.forced_value = h->forced_value.as<double>();
   S.rhs = h->rhs.as<double>();
   S.nb_dof = h->nb_dof;
+  S.diag_last = h->diag_last;
   if (S.nb_dof == 0)
     return B2F_OK;
   // Does any dof ask for row+column elimination?  (The flag arrays are caller-writable, so ask the device.)

@@ -205,7 +205,7 @@ namespace {
   __global__ void k_recv_index(const long long* __restrict__ meta_row, const long long* __restrict__ meta_k, const long long* __restrict__ row_off,
                                const long long* __restrict__ meta_col, long long nrows, const long long* __restrict__ sorted_gid, const int32_t* __restrict__ sorted_lid,
                                long long nb_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns, const uint8_t* __restrict__ is_ghost,
-                               long long* __restrict__ recv_index, unsigned long long* __restrict__ errors)
+                               long long* __restrict__ recv_index, unsigned long long* __restrict__ errors, int diag_last)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nrows)
@@ -231,7 +231,8 @@ namespace {
         const long long cp = lower_bound_i64(sorted_gid, nb_node, cin[x]);
         if (cp < nb_node && sorted_gid[cp] == cin[x]) {
           const int32_t c = sorted_lid[cp];
-          slot = (columns[rb] == c) ? 0 : find_slot(columns + rb, k, c);
+          const int ds = diag_slot(k, diag_last);
+          slot = (columns[rb + ds] == c) ? ds : find_slot(columns + rb, k, c, diag_last);
         }
         if (slot < 0)
           atomicAdd(errors, 1ull);
@@ -492,7 +493,7 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
       k_recv_index<BS, PB><<<grid_for(nrecv_rows, 128), 128, 0, stream>>>(mr_row.as<long long>(), mr_k.as<long long>(), mr_off.as<long long>(), mr_col.as<long long>(),
                                                                           nrecv_rows, gid_sorted.as<long long>(), lid_sorted.as<int32_t>(), nn, h->row_index.as<int32_t>(),
                                                                           h->columns.as<int32_t>(), d_ghost.as<uint8_t>(), P.recv_index.as<long long>(),
-                                                                          errs.as<unsigned long long>());
+                                                                          errs.as<unsigned long long>(), h->diag_last);
     B2F_CUDA(cudaGetLastError());
     return B2F_OK;
   });

@@ -72,6 +72,7 @@ struct b2f_context_s
   b2f_options opt{};
   int bs = 1, nv = 4, variant = B2F_ASM_NODE_GATHER;
   bool per_block = true;
+  int diag_last = 0; // b2f_pattern_layout: rows are stored neighbours first, diagonal last
   int device = 0;
 
   bool has_pattern = false;

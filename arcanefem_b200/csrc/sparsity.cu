@@ -98,11 +98,11 @@ namespace {
   }
 
   // K5: diagonal (BSRFormat.h:712-717) ...
-  __global__ void k_fill_diagonal(const int32_t* __restrict__ row_index, long long nb_node, int32_t* __restrict__ columns)
+  __global__ void k_fill_diagonal(const int32_t* __restrict__ row_index, long long nb_node, int32_t* __restrict__ columns, int diag_last)
   {
     const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (n < nb_node)
-      columns[row_index[n]] = (int32_t)n;
+      columns[diag_last ? row_index[n + 1] - 1 : row_index[n]] = (int32_t)n;
   }
 
   // ... then both directions of every unique edge (registerEdgeInColumns, BSRFormat.h:693-698,732-742).
@@ -180,13 +180,13 @@ namespace {
 
   // Sort the neighbour part of every row (entries 1..k-1; entry 0 is the diagonal) / every node->cell list.
   template <class T>
-  __global__ void __launch_bounds__(256) k_sort_segments(const int32_t* __restrict__ ptr, long long nb_seg, int skip, T* __restrict__ data)
+  __global__ void __launch_bounds__(256) k_sort_segments(const int32_t* __restrict__ ptr, long long nb_seg, int skip, T* __restrict__ data, int skip_back = 0)
   {
     const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31u;
     if (w >= nb_seg)
       return;
-    const int32_t b = ptr[w] + skip, e = ptr[w + 1];
+    const int32_t b = ptr[w] + skip, e = ptr[w + 1] - skip_back;
     warp_sort_segment<T>(data + b, e - b, lane);
   }
 
@@ -290,7 +290,7 @@ namespace {
   template <int NV>
   __global__ void __launch_bounds__(128) k_build_fan(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
                                                      const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, long long nb_node,
-                                                     int32_t* __restrict__ fan_count, uint32_t* __restrict__ stage, unsigned long long* __restrict__ counters)
+                                                     int32_t* __restrict__ fan_count, uint32_t* __restrict__ stage, unsigned long long* __restrict__ counters, int diag_last)
   {
     constexpr int NO = NV - 1; // other vertices of a cell
     const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -311,11 +311,12 @@ namespace {
     }
     uint32_t* out = stage + qb;
     int nout = 0, nstart = 0;
+    // plan slots: diagonal 0, neighbours 1 .. k-1 ascending, whatever the storage layout (diagonal-last rows hold neighbour x at x - 1)
     auto slot_of = [&](int32_t c) {
       int lo = 1, hi = k;
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (columns[rb + mid] < c)
+        if (columns[rb + mid - diag_last] < c)
           lo = mid + 1;
         else
           hi = mid;
@@ -527,7 +528,7 @@ namespace {
   template <int NV>
   __global__ void __launch_bounds__(256) k_pack_fan(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns,
                                                     const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list, const int32_t* __restrict__ fan_ptr,
-                                                    long long nb_node, const uint32_t* __restrict__ stage, uint32_t* __restrict__ fan_steps, uint32_t* __restrict__ fan_cell)
+                                                    long long nb_node, const uint32_t* __restrict__ stage, uint32_t* __restrict__ fan_steps, uint32_t* __restrict__ fan_cell, int diag_last)
   {
     constexpr int NO = NV - 1;
     const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -564,7 +565,7 @@ namespace {
             int lo = 1, hi = k;
             while (lo < hi) {
               const int mid = (lo + hi) >> 1;
-              if (columns[rb + mid] < c)
+              if (columns[rb + mid - diag_last] < c)
                 lo = mid + 1;
               else
                 hi = mid;
@@ -785,7 +786,7 @@ namespace {
   template <int NV, bool WRITE>
   __global__ void __launch_bounds__(RU_ROWS) k_row_unique(const int32_t* __restrict__ cell_node, const int32_t* __restrict__ nc_ptr, const uint32_t* __restrict__ nc_list,
                                                           long long nb_node, const int32_t* __restrict__ row_index, int32_t* __restrict__ deg,
-                                                          int32_t* __restrict__ columns, unsigned long long* __restrict__ counters)
+                                                          int32_t* __restrict__ columns, unsigned long long* __restrict__ counters, int diag_last)
   {
     __shared__ int32_t set[RU_CAP][RU_ROWS];
     const int t = threadIdx.x;
@@ -837,9 +838,9 @@ namespace {
     }
     else {
       const int32_t rb = row_index[row];
-      columns[rb] = (int32_t)row;
+      columns[rb + (diag_last ? cnt : 0)] = (int32_t)row;
       for (int i = 0; i < cnt; ++i)
-        columns[rb + 1 + i] = set[i][t];
+        columns[rb + 1 - diag_last + i] = set[i][t];
     }
   }
 } // namespace
@@ -859,9 +860,9 @@ static int pattern_from_lists(b2f_context_s* h, cudaStream_t stream, bool* fallb
   const uint32_t* ncl = h->nc_list.as<uint32_t>();
   if (nn > 0) {
     if (nv == 3)
-      k_row_unique<3, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters);
+      k_row_unique<3, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters, h->diag_last);
     else
-      k_row_unique<4, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters);
+      k_row_unique<4, false><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, nullptr, deg, nullptr, counters, h->diag_last);
     B2F_CUDA(cudaGetLastError());
   }
   B2F_CUDA(h->row_index.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
@@ -886,9 +887,11 @@ static int pattern_from_lists(b2f_context_s* h, cudaStream_t stream, bool* fallb
   B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
   if (nn > 0) {
     if (nv == 3)
-      k_row_unique<3, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters);
+      k_row_unique<3, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters,
+                                                                           h->diag_last);
     else
-      k_row_unique<4, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters);
+      k_row_unique<4, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters,
+                                                                           h->diag_last);
     B2F_CUDA(cudaGetLastError());
   }
   B2F_CUDA(h->nb_nz_per_row.alloc(sizeof(int32_t) * (size_t)nn));
@@ -960,12 +963,12 @@ static int pattern_by_sort(b2f_context_s* h, cudaStream_t stream)
   // --- K5: columns, then canonical order inside every row
   B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
   B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
-  int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724
-  k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(cursor, nn, 1);
-  k_fill_diagonal<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->columns.as<int32_t>());
+  int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724 (diagonal-last rows: the neighbours start at 0, :554-567)
+  k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(cursor, nn, 1 - h->diag_last);
+  k_fill_diagonal<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->columns.as<int32_t>(), h->diag_last);
   if (nkeys > 0)
     k_fill_neighbours<<<grid_for(nkeys, 256), 256, 0, stream>>>(sorted, nkeys, shift, h->row_index.as<int32_t>(), cursor, h->columns.as<int32_t>());
-  k_sort_segments<int32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, 1, h->columns.as<int32_t>());
+  k_sort_segments<int32_t><<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, 1 - h->diag_last, h->columns.as<int32_t>(), h->diag_last);
   B2F_CUDA(cudaGetLastError());
 
   // --- K6
@@ -1114,9 +1117,9 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
       stage = h->ws_keys_a.as<uint32_t>();
     }
     if (nv == 3)
-      k_build_fan<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters);
+      k_build_fan<3><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters, h->diag_last);
     else
-      k_build_fan<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters);
+      k_build_fan<4><<<grid_for(nn, 128), 128, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, nn, fan_count, stage, counters, h->diag_last);
     B2F_CUDA(cudaGetLastError());
     B2F_CUDA(h->fan_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
     long long nb_step = 0;
@@ -1128,10 +1131,10 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     B2F_CUDA(h->fan_cell.alloc(sizeof(uint32_t) * (size_t)(nb_step + 8)));
     if (nv == 3)
       k_pack_fan<3><<<grid_for(((nn + 31) / 32) * 32, 256), 256, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, h->fan_ptr.as<int32_t>(), nn, stage,
-                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>());
+                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>(), h->diag_last);
     else
       k_pack_fan<4><<<grid_for(((nn + 31) / 32) * 32, 256), 256, 0, stream>>>(h->mesh.cell_node, ri, co, ncp, ncl, h->fan_ptr.as<int32_t>(), nn, stage,
-                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>());
+                                                                            h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>(), h->diag_last);
     B2F_CUDA(cudaGetLastError());
     if (nv == 4 && nb_step > 0) {
       k_fan_pivot_hint<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());

@@ -101,6 +101,14 @@ typedef enum b2f_fan_mode { B2F_FAN_AUTO = 0, B2F_FAN_SELECT = 1, B2F_FAN_LOCKST
  * are built in a second pass), except for rows with more than 64 neighbours, which take SORT. */
 typedef enum b2f_sparsity_build { B2F_SPARSITY_AUTO = 0, B2F_SPARSITY_SORT = 1, B2F_SPARSITY_LISTS = 2 } b2f_sparsity_build;
 
+/* Order of the blocks inside a row.  DIAG_FIRST (default): diagonal, then the neighbours by ascending id - what the sorted-edge
+ * build of the reference gives when executed in key order (femutils/BSRFormat.h:602-744).  DIAG_LAST: the neighbours first, the
+ * diagonal last - the layout of the reference's connectivity ("atomic-free") sparsity, computeSparsityAtomicFree :479-578, which
+ * lists a node's neighbours in the order of Arcane's node-node / node-face connectivity and then appends the node itself.  That
+ * connectivity order is a property of Arcane's edge numbering and is not reproducible outside Arcane: the
+ * neighbours are listed by ascending id here; the per-row neighbour SET is the same as DIAG_FIRST's. */
+typedef enum b2f_pattern_layout { B2F_PATTERN_DIAG_FIRST = 0, B2F_PATTERN_DIAG_LAST = 1 } b2f_pattern_layout;
+
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
 typedef struct b2f_options {
   int32_t block_size; /* NB_DOF: 1, 2 or 3 */
@@ -108,7 +116,7 @@ typedef struct b2f_options {
   int32_t assembly_variant; /* b2f_assembly_variant; the reference's use_atomic_free=true maps to NODE_GATHER */
   int32_t fan_mode; /* b2f_fan_mode: walk of the node-gather kernel on tets (0 = chosen from the plan) */
   int32_t sparsity_build; /* b2f_sparsity_build */
-  int32_t reserved;
+  int32_t pattern_layout; /* b2f_pattern_layout */
 } b2f_options;
 
 typedef struct b2f_operator {

@@ -36,11 +36,13 @@ __device__ __forceinline__ long long value_index(long long rb, int k, int x, int
   return rb * (BS * BS) + (long long)i * (BS * k) + x * BS + j;
 }
 
-// Slot of column c in a row stored "diagonal first, then ascending" (k entries).  Returns -1 if absent.
+// Slot of the off-diagonal column c in a row of k entries stored "diagonal first, then ascending" (dl = 0) or "ascending,
+// diagonal last" (dl = 1, b2f_pattern_layout).  Returns -1 if absent.
 template <class ColPtr>
-__device__ __forceinline__ int find_slot(ColPtr cols, int k, int32_t c)
+__device__ __forceinline__ int find_slot(ColPtr cols, int k, int32_t c, int dl = 0)
 {
-  int lo = 1, hi = k;
+  int lo = 1 - dl, hi = k - dl;
+  const int end = hi;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
     if (cols[mid] < c)
@@ -48,8 +50,9 @@ __device__ __forceinline__ int find_slot(ColPtr cols, int k, int32_t c)
     else
       hi = mid;
   }
-  return (lo < k && cols[lo] == c) ? lo : -1;
+  return (lo < end && cols[lo] == c) ? lo : -1;
 }
+__device__ __forceinline__ int diag_slot(int k, int dl) { return dl ? k - 1 : 0; }
 
 template <int NV>
 __device__ __forceinline__ void load_cell_nodes(const int32_t* __restrict__ cell_node, long long cell, int32_t (&n)[NV])
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(256) k_cell_atomic(AssembleArgs A, Op op)
     for (int b = 0; b < NV; ++b) {
       int x = -1;
       if (own) {
-        x = (a == b) ? 0 : find_slot(A.columns + rb, k, n[b]);
+        x = (a == b) ? diag_slot(k, A.diag_last) : find_slot(A.columns + rb, k, n[b], A.diag_last);
         if (x < 0)
           atomicAdd(A.counters, 1ull);
       }
@@ -280,7 +283,7 @@ __device__ __forceinline__ void gather_rows(const AssembleArgs& A, const Op& op,
         const typename Op::Geom G = op.prepare(X, cell);
 #pragma unroll
         for (int b = 0; b < NV; ++b) {
-          const int x = (b == 0) ? 0 : find_slot(cols, k, n[b]);
+          const int x = (b == 0) ? diag_slot(k, A.diag_last) : find_slot(cols, k, n[b], A.diag_last);
           if (x < 0) {
             atomicAdd(A.counters, 1ull);
             continue;
@@ -947,16 +950,22 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   __syncthreads();
 
   if (nstep > 0) {
+    // The plan's slots are "diagonal 0, neighbours 1 .. k-1 ascending".  Diagonal-last rows (b2f_pattern_layout) store neighbour x
+    // at position x - 1 and the diagonal at k - 1: the row's base addresses are moved back by one slot, so every neighbour access
+    // of the walk is unchanged, and the diagonal is addressed as slot k.
+    const int dl = A.diag_last;
+    const int ds = dl ? k : 0;
+    const int acc_shift = dl * (PER_BLOCK ? BS2 : BS);
 #if B2F_FAN_ASM_SMEM
-    SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) };
-    SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) };
+    SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) - 8u * (uint32_t)acc_shift };
+    SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) - 4u * (uint32_t)dl };
     SmemU32 st{ (uint32_t)__cvta_generic_to_shared(steps_s + (qb - abeg_al)) };
     // the addresses become opaque here, after the barrier: the asm loads below depend on them and cannot be hoisted above
     // the wait, and the compiler keeps them in registers instead of re-deriving them
     asm volatile("" : "+r"(acc.a), "+r"(cols.a), "+r"(st.a)::"memory");
 #else
-    double* acc = acc_s + (size_t)(rb - vbeg) * BS2;
-    const int32_t* cols = cols_s + (rb - vbeg_al);
+    double* acc = acc_s + (size_t)(rb - vbeg) * BS2 - acc_shift;
+    const int32_t* cols = cols_s + (rb - vbeg_al) - dl;
     const uint32_t* st = steps_s + (qb - abeg_al);
 #endif
     const uint32_t* cl = A.fan_cell + qb;
@@ -965,7 +974,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     for (int x = 1; x < k; ++x)
       prefetch_l2(A.coords + 3ll * cols[x]);
     double diag[BS2];
-    load_block<BS, PER_BLOCK>(acc, k, 0, diag);
+    load_block<BS, PER_BLOCK>(acc, k, ds, diag);
     double measure = 0.0;
     if constexpr (LOCKSTEP) {
       static_assert(!LOCKSTEP || NV == 4, "the lockstep walk is for tetrahedra");
@@ -1232,7 +1241,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         sum += acc[x];
       diag[0] = -sum;
     }
-    store_block<BS, PER_BLOCK>(acc, k, 0, diag);
+    store_block<BS, PER_BLOCK>(acc, k, ds, diag);
     if constexpr (SRC)
       A.rhs[row * BS] += A.rhs_factor * measure;
   }

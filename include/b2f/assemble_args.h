@@ -33,6 +33,7 @@ struct AssembleArgs
   long long nb_tile = -1; // -1: every tile
   double* rhs = nullptr; // fused constant source (fan kernel): rhs[row * BS] += rhs_factor * (sum of 6*volume / 2*area of the incident cells)
   double rhs_factor = 0.0;
+  int diag_last = 0; // rows are stored neighbours first (ascending), diagonal last (b2f_pattern_layout)
 };
 
 enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };
