@@ -24,7 +24,7 @@ class MeshView(C.Structure):
 
 class Options(C.Structure):
     _fields_ = [("block_size", C.c_int32), ("use_csr", C.c_int32), ("assembly_variant", C.c_int32), ("fan_mode", C.c_int32),
-                ("sparsity_build", C.c_int32), ("pattern_layout", C.c_int32)]
+                ("sparsity_build", C.c_int32), ("pattern_layout", C.c_int32), ("reorder", C.c_int32), ("reserved", C.c_int32)]
 
 
 class OperatorDesc(C.Structure):
@@ -67,7 +67,7 @@ class IjView(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("nb_edge", C.c_int64), ("nb_col", C.c_int64), ("nb_nz", C.c_int64), ("columns_not_found", C.c_int64),
                 ("workspace_bytes", C.c_int64), ("resident_bytes", C.c_int64), ("gather_fallback_tiles", C.c_int64), ("fan_steps", C.c_int64),
-                ("sparsity_by_lists", C.c_int64), ("fan_lockstep", C.c_int64), ("fan_lockstep_bodies_milli", C.c_int64)]
+                ("sparsity_by_lists", C.c_int64), ("fan_lockstep", C.c_int64), ("fan_lockstep_bodies_milli", C.c_int64), ("reordered", C.c_int64)]
 
 
 _H = C.c_void_p  # b2f_handle

@@ -284,7 +284,7 @@ class BSRFormat:
         except Exception:
             pass
 
-    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0, sparsity_build=0, pattern_layout=0):
+    def initialize(self, mesh, does_linear_system_use_csr, use_atomic_free=False, assembly_variant=None, fan_mode=0, sparsity_build=0, pattern_layout=0, reorder=0):
         if mesh is None:
             raise ValueError("BSRFormat(initialize): null mesh")  # ARCANE_CHECK_POINTER, BSRFormat.h:391
         if self._h.value:
@@ -307,6 +307,7 @@ class BSRFormat:
         opt.assembly_variant = int(assembly_variant)
         opt.fan_mode = int(fan_mode)  # b2f_fan_mode: 0 auto, 1 select walk, 2 lockstep walk
         opt.sparsity_build = int(sparsity_build)  # b2f_sparsity_build: 0 auto, 1 global sort, 2 row-wise from the node->cell lists
+        opt.reorder = int(reorder)  # b2f_reorder: 1 = the library sorts the nodes along a Morton curve internally (views stay in the caller's numbering)
         opt.pattern_layout = int(pattern_layout)  # b2f_pattern_layout: 0 diagonal first (sorted-edge build), 1 diagonal last (connectivity build, BSRFormat.h:479-578)
         check(self._lib.b2f_create(C.byref(mv), C.byref(opt), C.byref(self._h)))
         self._mesh = mesh

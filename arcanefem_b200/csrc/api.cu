@@ -107,6 +107,8 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown pattern_layout %d", options->pattern_layout);
   if (options->pattern_layout == B2F_PATTERN_DIAG_LAST && options->assembly_variant == B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_NOT_IMPLEMENTED, "b2f_create: the first-generation slot-word kernel (kept for A/B measurements) only knows the diagonal-first layout");
+  if (options->reorder != B2F_REORDER_NONE && options->reorder != B2F_REORDER_MORTON)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown reorder %d", options->reorder);
   if (options->fan_mode < B2F_FAN_AUTO || options->fan_mode > B2F_FAN_LOCKSTEP)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown fan_mode %d", options->fan_mode);
   int ndev = 0;
@@ -133,7 +135,8 @@ int b2f_destroy(b2f_handle h)
   DevBuf* bufs[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
                      &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_dst, &h->ghost.recv_src,
-                     &h->ij_flag, &h->ij_off, &h->ij_ncols, &h->ij_rows, &h->ij_row_local, &h->ij_cols, &h->ij_values, &h->ij_rhs };
+                     &h->ij_flag, &h->ij_off, &h->ij_ncols, &h->ij_rows, &h->ij_row_local, &h->ij_cols, &h->ij_values, &h->ij_rhs,
+                     &h->perm_rows, &h->r_row_index, &h->r_columns, &h->r_coords };
   for (DevBuf* b : bufs)
     b->release();
   for (cudaEvent_t e : h->pipe_events)
@@ -220,6 +223,11 @@ int b2f_user_assemble_begin(b2f_handle h, int32_t nodes_per_cell, int32_t block_
   if (!h->mesh.coords)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_user_assemble_begin: mesh coordinates are null");
   B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, (cudaStream_t)stream));
+  if (h->reordered) { // a caller-compiled operator that runs on the fan kernel reads the internal coordinates too
+    const int rc = permute_coords(h, (cudaStream_t)stream);
+    if (rc != B2F_OK)
+      return rc;
+  }
   fill_assemble_args(h, static_cast<AssembleArgs*>(args_out));
   *variant_out = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
   *per_block_out = h->per_block ? 1 : 0;
@@ -352,6 +360,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   out->sparsity_by_lists = h->pattern_by_lists ? 1 : 0;
   out->fan_lockstep = h->fan_lockstep ? 1 : 0;
   out->fan_lockstep_bodies_milli = (int64_t)(h->fan_lockstep_bodies * 1000.0 + 0.5);
+  out->reordered = h->reordered ? 1 : 0;
   if (h->counters.p) {
     unsigned long long c[4] = { 0, 0, 0, 0 };
     B2F_CUDA(cudaMemcpy(c, h->counters.p, sizeof(c), cudaMemcpyDeviceToHost));
@@ -360,7 +369,8 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   }
   out->workspace_bytes = (int64_t)(h->ws_keys_a.bytes + h->ws_keys_b.bytes + h->ws_tmp.bytes + h->ws_i32a.bytes + h->ws_i64.bytes);
   const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
-                          &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage };
+                          &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage, &h->perm_rows, &h->r_row_index, &h->r_columns,
+                          &h->r_coords };
   for (const DevBuf* b : res)
     out->resident_bytes += (int64_t)b->bytes;
   return B2F_OK;
@@ -574,7 +584,7 @@ int b2f_assemble_host(b2f_handle h, const b2f_operator* op, const double* coords
   const size_t cbytes = sizeof(double) * 3 * (size_t)nn;
   B2F_CUDA(h->coords_stage.alloc(cbytes));
   const int variant = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
-  const bool pipelined = variant == B2F_ASM_NODE_GATHER && h->fan_ok && nn >= (1ll << 16);
+  const bool pipelined = variant == B2F_ASM_NODE_GATHER && h->fan_ok && nn >= (1ll << 16) && !h->reordered; // row chunks follow the caller's row order
   if (!pipelined) {
     B2F_CUDA(cudaMemcpyAsync(h->coords_stage.p, coords_host, cbytes, cudaMemcpyHostToDevice, s));
     const double* saved = h->mesh.coords;

@@ -33,6 +33,14 @@ void fill_assemble_args(const b2f_context_s* h, AssembleArgs* out)
   A.counters = h->counters.as<unsigned long long>();
   A.accumulate = 0;
   A.diag_last = h->diag_last;
+  // reorder mode: the fan kernel's launcher swaps the internal copies in (launch_assemble_layout); every other kernel keeps
+  // the caller's arrays above
+  if (h->reordered) {
+    A.r_perm = h->perm_rows.as<int32_t>();
+    A.r_row_index = h->r_row_index.as<int32_t>();
+    A.r_columns = h->r_columns.as<int32_t>();
+    A.r_coords = h->r_coords.as<double>();
+  }
   *out = A;
 }
 

@@ -26,6 +26,11 @@ inline int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stre
       A.rhs = h->rhs.as<double>();
       A.rhs_factor = *qdot / (Op::NV == 4 ? 24.0 : 6.0);
     }
+    if (h->reordered && variant == B2F_ASM_NODE_GATHER && h->fan_ok && uses_fan<Op>::value) {
+      const int rc = permute_coords(h, stream); // coords_internal[i] = coords[perm[i]]: the caller may have moved the nodes
+      if (rc != B2F_OK)
+        return rc;
+    }
     B2F_CUDA(launch_assemble<Op>(A, op, variant, h->per_block, h->nb_nz, stream));
     if (qdot != nullptr && !fused)
       return rhs_constant_source(h, *qdot, stream);

@@ -84,6 +84,10 @@ struct b2f_context_s
   b2f::DevBuf nc_ptr, nc_list, nc_slots; // node -> cell lists and the column-slot plan of the gather kernel
   bool slots_ok = false;
   b2f::DevBuf fan_ptr, fan_steps, fan_cell; // fan-walk plan of the default gather kernel (one word per step, cell id per step)
+  // b2f_reorder: the plan above is stored in the library's own node order; internal -> caller row, the internal copies of
+  // row_index / columns (column ids in the internal numbering) and of the coordinates (refreshed by every assembly)
+  bool reordered = false;
+  b2f::DevBuf perm_rows, r_row_index, r_columns, r_coords;
   bool fan_ok = false;
   bool fan_lockstep = false; // step words converted to the lockstep form (sparsity.cu k_fan_lockstep)
   double fan_lockstep_bodies = 0.0; // step bodies a warp would execute per warp step in the lockstep form (1 = rows in step)
@@ -112,6 +116,9 @@ struct b2f_context_s
 namespace b2f {
 // sparsity.cu
 int build_pattern(b2f_context_s* h, cudaStream_t stream);
+// sparsity.cu
+int reorder_plan(b2f_context_s* h, cudaStream_t stream);
+int permute_coords(b2f_context_s* h, cudaStream_t stream);
 // assemble.cu
 struct AssembleArgs;
 void fill_assemble_args(const b2f_context_s* h, AssembleArgs* A); // pointers, plan and counters of the handle (accumulate = 0, whole matrix)

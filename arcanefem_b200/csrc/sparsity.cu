@@ -14,6 +14,9 @@
 //   * the reference fills neighbour slots in atomic-arrival order, which is non-deterministic on a GPU; here every
 //     row is then sorted (warp rank sort), giving the canonical order "diagonal, then ascending ids";
 //   * all sizes are 64-bit internally; Int32 overflow of a per-rank count is reported, not wrapped.
+#include <algorithm>
+#include <cstring>
+#include <utility>
 #include <cub/cub.cuh>
 #include "internal.h"
 
@@ -1173,6 +1176,14 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0);
   }
 
+  // b2f_reorder: store the plan in a space-filling order of the nodes (single-rank node gather only)
+  h->reordered = false;
+  if (h->opt.reorder == B2F_REORDER_MORTON && h->fan_ok && h->mesh.cell_is_own == nullptr && h->mesh.coords != nullptr) {
+    rc = reorder_plan(h, stream);
+    if (rc != B2F_OK)
+      return rc;
+  }
+
   // BSRMatrix::initialize fills the values with 0 (femutils/BSRFormat.h:136); done last because the plan build borrows the array
   B2F_CUDA(cudaMemsetAsync(h->values.p, 0, sizeof(double) * (size_t)h->nb_nz, stream));
 
@@ -1194,6 +1205,250 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   h->ws_i32a.release();
   h->ws_keys_a.release();
   h->has_pattern = true;
+  return B2F_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// b2f_reorder (b2f.h): node locality supplied by the library.  The pattern and the walk plan are built in the caller's
+// numbering as always; then the rows are sorted along a Morton curve of the node coordinates and the plan is stored in that
+// order: internal row i is the caller's row perm[i], its column ids are translated to internal ids, its step words and
+// cell ids move with it unchanged (slots are row-local, so the walk of a row - hence every value - is bit for bit the one
+// of the unpermuted plan).  The caller's row_index / columns stay as they are: they are the views, and the destination map
+// of the kernel's write-out.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+  __device__ __forceinline__ unsigned long long order_bits(double x)
+  {
+    unsigned long long u = (unsigned long long)__double_as_longlong(x);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull); // monotone map of doubles to unsigned integers
+  }
+  __host__ __device__ inline double unorder_bits(unsigned long long u)
+  {
+    u = (u >> 63) ? (u & 0x7fffffffffffffffull) : ~u;
+    double x;
+    memcpy(&x, &u, sizeof(x));
+    return x;
+  }
+  // box[0..2] = min, box[3..5] = max (order_bits encoding; box initialised to ~0 / 0)
+  __global__ void __launch_bounds__(256) k_bbox(const double* __restrict__ coords, long long nn, unsigned long long* __restrict__ box)
+  {
+    unsigned long long lo[3] = { ~0ull, ~0ull, ~0ull }, hi[3] = { 0ull, 0ull, 0ull };
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nn; i += (long long)gridDim.x * blockDim.x)
+      for (int d = 0; d < 3; ++d) {
+        const unsigned long long u = order_bits(coords[3 * i + d]);
+        lo[d] = u < lo[d] ? u : lo[d];
+        hi[d] = u > hi[d] ? u : hi[d];
+      }
+    for (int d = 0; d < 3; ++d) {
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long a = __shfl_xor_sync(0xffffffffu, lo[d], o), b = __shfl_xor_sync(0xffffffffu, hi[d], o);
+        lo[d] = a < lo[d] ? a : lo[d];
+        hi[d] = b > hi[d] ? b : hi[d];
+      }
+      if ((threadIdx.x & 31) == 0) {
+        atomicMin(box + d, lo[d]);
+        atomicMax(box + 3 + d, hi[d]);
+      }
+    }
+  }
+  __device__ __forceinline__ unsigned long long spread3(unsigned long long v) // 21 bits -> every third bit
+  {
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+  }
+  __global__ void __launch_bounds__(256) k_morton_keys(const double* __restrict__ coords, long long nn, double x0, double y0, double z0, double sx, double sy, double sz,
+                                                       unsigned long long* __restrict__ keys, int32_t* __restrict__ ids)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nn)
+      return;
+    const double q = 2097151.0; // 2^21 - 1
+    const unsigned long long a = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i] - x0) * sx));
+    const unsigned long long b = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 1] - y0) * sy));
+    const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 2] - z0) * sz));
+    keys[i] = spread3(a) | (spread3(b) << 1) | (spread3(c) << 2);
+    ids[i] = (int32_t)i;
+  }
+  __global__ void __launch_bounds__(256) k_invert_perm(const int32_t* __restrict__ perm, long long nn, int32_t* __restrict__ newid)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nn)
+      newid[perm[i]] = (int32_t)i;
+  }
+  __global__ void __launch_bounds__(256) k_perm_lengths(const int32_t* __restrict__ perm, long long nn, const int32_t* __restrict__ row_index, const int32_t* __restrict__ fan_ptr,
+                                                        int32_t* __restrict__ len_row, int32_t* __restrict__ len_fan)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nn)
+      return;
+    const int32_t r = perm[i];
+    len_row[i] = row_index[r + 1] - row_index[r];
+    len_fan[i] = fan_ptr[r + 1] - fan_ptr[r];
+  }
+  // one warp per internal row: columns (translated), step words (pivot hint cleared: it is a property of the 32 rows a warp
+  // walks together and is recomputed for the new grouping), cell ids
+  __global__ void __launch_bounds__(256) k_perm_rows(const int32_t* __restrict__ perm, const int32_t* __restrict__ newid, long long nn, const int32_t* __restrict__ row_index,
+                                                     const int32_t* __restrict__ columns, const int32_t* __restrict__ fan_ptr, const uint32_t* __restrict__ fan_steps,
+                                                     const uint32_t* __restrict__ fan_cell, const int32_t* __restrict__ r_row_index, int32_t* __restrict__ r_columns,
+                                                     const int32_t* __restrict__ r_fan_ptr, uint32_t* __restrict__ r_fan_steps, uint32_t* __restrict__ r_fan_cell)
+  {
+    const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= nn)
+      return;
+    const int32_t r = perm[i];
+    const int32_t cb = row_index[r], k = row_index[r + 1] - cb, db = r_row_index[i];
+    for (int q = lane; q < k; q += 32)
+      r_columns[db + q] = newid[columns[cb + q]];
+    const int32_t fb = fan_ptr[r], nf = fan_ptr[r + 1] - fb, gb = r_fan_ptr[i];
+    for (int q = lane; q < nf; q += 32) {
+      const uint32_t w = fan_steps[fb + q];
+      r_fan_steps[gb + q] = (w & 0x80000000u) ? w : (w & ~4096u);
+      r_fan_cell[gb + q] = fan_cell[fb + q];
+    }
+  }
+  __global__ void __launch_bounds__(256) k_permute_coords(const int32_t* __restrict__ perm, long long nn, const double* __restrict__ coords, double* __restrict__ out)
+  {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; // one thread per scalar: coalesced stores
+    if (q >= 3 * nn)
+      return;
+    const long long i = q / 3;
+    out[q] = __ldg(coords + 3ll * perm[i] + (q - 3 * i));
+  }
+} // namespace
+
+int permute_coords(b2f_context_s* h, cudaStream_t stream)
+{
+  const long long nn = h->mesh.nb_node;
+  k_permute_coords<<<grid_for(3 * nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, h->mesh.coords, h->r_coords.as<double>());
+  B2F_CUDA(cudaGetLastError());
+  return B2F_OK;
+}
+
+int reorder_plan(b2f_context_s* h, cudaStream_t stream)
+{
+  const long long nn = h->mesh.nb_node;
+  unsigned long long* counters = h->counters.as<unsigned long long>();
+  // 1. bounding box
+  DevBuf box_d;
+  B2F_CUDA(box_d.alloc(sizeof(unsigned long long) * 6));
+  unsigned long long box[6] = { ~0ull, ~0ull, ~0ull, 0ull, 0ull, 0ull };
+  B2F_CUDA(cudaMemcpyAsync(box_d.p, box, sizeof(box), cudaMemcpyHostToDevice, stream));
+  k_bbox<<<(unsigned)std::min<long long>(1184, (nn + 255) / 256), 256, 0, stream>>>(h->mesh.coords, nn, box_d.as<unsigned long long>());
+  B2F_CUDA(cudaGetLastError());
+  B2F_CUDA(cudaMemcpyAsync(box, box_d.p, sizeof(box), cudaMemcpyDeviceToHost, stream));
+  B2F_CUDA(cudaStreamSynchronize(stream));
+  box_d.release();
+  double lo[3], sc[3];
+  for (int d = 0; d < 3; ++d) {
+    lo[d] = unorder_bits(box[d]);
+    const double ext = unorder_bits(box[3 + d]) - lo[d];
+    sc[d] = ext > 0.0 ? 2097151.0 / ext : 0.0;
+  }
+  // 2. Morton keys, stable radix sort -> perm (internal -> caller), newid (caller -> internal)
+  DevBuf keys_a, keys_b, ids_a, newid;
+  B2F_CUDA(keys_a.alloc(sizeof(unsigned long long) * (size_t)nn));
+  B2F_CUDA(keys_b.alloc(sizeof(unsigned long long) * (size_t)nn));
+  B2F_CUDA(ids_a.alloc(sizeof(int32_t) * (size_t)nn));
+  B2F_CUDA(newid.alloc(sizeof(int32_t) * (size_t)nn));
+  B2F_CUDA(h->perm_rows.alloc(sizeof(int32_t) * (size_t)nn));
+  auto cleanup = [&]() {
+    keys_a.release();
+    keys_b.release();
+    ids_a.release();
+    newid.release();
+  };
+  k_morton_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], keys_a.as<unsigned long long>(), ids_a.as<int32_t>());
+  {
+    size_t tb = 0;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(),
+                                                    h->perm_rows.as<int32_t>(), nn, 0, 63, stream);
+    if (e == cudaSuccess)
+      e = h->ws_tmp.alloc(tb);
+    if (e == cudaSuccess)
+      e = cub::DeviceRadixSort::SortPairs(h->ws_tmp.p, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(), h->perm_rows.as<int32_t>(), nn,
+                                          0, 63, stream);
+    if (e != cudaSuccess) {
+      cleanup();
+      return fail_cuda(e, "reorder_plan: radix sort of the Morton keys");
+    }
+  }
+  k_invert_perm<<<grid_for(nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, newid.as<int32_t>());
+  // 3. internal offsets
+  DevBuf len_row, len_fan, new_fan_ptr, new_steps, new_cell;
+  cudaError_t e = len_row.alloc(sizeof(int32_t) * (size_t)(nn + 1));
+  if (e == cudaSuccess)
+    e = len_fan.alloc(sizeof(int32_t) * (size_t)(nn + 1));
+  if (e == cudaSuccess)
+    e = h->r_row_index.alloc(sizeof(int32_t) * (size_t)(nn + 1));
+  if (e == cudaSuccess)
+    e = new_fan_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1));
+  if (e == cudaSuccess)
+    e = h->r_columns.alloc(sizeof(int32_t) * (size_t)(h->nb_col + 8));
+  if (e == cudaSuccess)
+    e = new_steps.alloc(sizeof(uint32_t) * (size_t)(h->nb_fan_step + 8));
+  if (e == cudaSuccess)
+    e = new_cell.alloc(sizeof(uint32_t) * (size_t)(h->nb_fan_step + 8));
+  if (e == cudaSuccess)
+    e = h->r_coords.alloc(sizeof(double) * 3 * (size_t)nn);
+  auto cleanup2 = [&]() {
+    cleanup();
+    len_row.release();
+    len_fan.release();
+    new_fan_ptr.release();
+    new_steps.release();
+    new_cell.release();
+  };
+  if (e != cudaSuccess) {
+    cleanup2();
+    return fail_cuda(e, "reorder_plan: allocation");
+  }
+  k_perm_lengths<<<grid_for(nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, h->row_index.as<int32_t>(), h->fan_ptr.as<int32_t>(), len_row.as<int32_t>(),
+                                                        len_fan.as<int32_t>());
+  long long t1 = 0, t2 = 0;
+  int rc = scan_counts(h, len_row.as<int32_t>(), nn, h->r_row_index.as<int32_t>(), &t1, stream);
+  if (rc == B2F_OK)
+    rc = scan_counts(h, len_fan.as<int32_t>(), nn, new_fan_ptr.as<int32_t>(), &t2, stream);
+  if (rc == B2F_OK && (t1 != h->nb_col || t2 != h->nb_fan_step))
+    rc = fail(B2F_ERR_STATE, "reorder_plan: permuted sizes %lld / %lld differ from %lld / %lld", t1, t2, (long long)h->nb_col, (long long)h->nb_fan_step);
+  if (rc != B2F_OK) {
+    cleanup2();
+    return rc;
+  }
+  // 4. rows into the internal order
+  k_perm_rows<<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), newid.as<int32_t>(), nn, h->row_index.as<int32_t>(), h->columns.as<int32_t>(),
+                                                          h->fan_ptr.as<int32_t>(), h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>(), h->r_row_index.as<int32_t>(),
+                                                          h->r_columns.as<int32_t>(), new_fan_ptr.as<int32_t>(), new_steps.as<uint32_t>(), new_cell.as<uint32_t>());
+  e = cudaGetLastError();
+  if (e == cudaSuccess)
+    e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess) {
+    cleanup2();
+    return fail_cuda(e, "reorder_plan: row permutation");
+  }
+  // the plan of the handle is now the internal one
+  std::swap(h->fan_ptr, new_fan_ptr);
+  std::swap(h->fan_steps, new_steps);
+  std::swap(h->fan_cell, new_cell);
+  cleanup2();
+  if (h->nv == 4 && h->nb_fan_step > 0) {
+    k_fan_pivot_hint<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
+    B2F_CUDA(cudaGetLastError());
+  }
+  {
+    int* ext = reinterpret_cast<int*>(counters + 4);
+    B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 6, stream));
+    k_tile_extents<<<grid_for((nn + 31) / 32, 128), 128, 0, stream>>>(h->r_row_index.as<int32_t>(), h->fan_ptr.as<int32_t>(), nn, ext);
+    B2F_CUDA(cudaGetLastError());
+    B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 6, cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+  }
+  h->reordered = true;
   return B2F_OK;
 }
 

@@ -233,9 +233,10 @@ __device__ __forceinline__ double row_measure(const AssembleArgs& A, long long r
   return sum;
 }
 
+// row_map (SMEM == false only): the rows handled are row_map[row0 .. row0 + nrows) instead of row0 .. row0 + nrows (reorder mode).
 template <class Op, bool PER_BLOCK, bool SMEM>
 __device__ __forceinline__ void gather_rows(const AssembleArgs& A, const Op& op, long long row0, int nrows, int32_t vbeg, int32_t vend, int32_t abeg, int32_t aend,
-                                            double* acc_s, int32_t* cols_s, uint32_t* adj_s)
+                                            double* acc_s, int32_t* cols_s, uint32_t* adj_s, const int32_t* row_map = nullptr)
 {
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   const int t = threadIdx.x;
@@ -257,7 +258,7 @@ __device__ __forceinline__ void gather_rows(const AssembleArgs& A, const Op& op,
   }
 
   if (t < nrows) {
-    const long long row = row0 + t;
+    const long long row = (!SMEM && row_map != nullptr) ? (long long)__ldg(row_map + row0 + t) : row0 + t;
     const int32_t rb = __ldg(A.row_index + row);
     const int k = __ldg(A.row_index + row + 1) - rb;
     const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
@@ -890,10 +891,26 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   if (!fits) { // oversized tile (very long rows): search-based path on global memory
     if (t == 0)
       atomicAdd(A.counters + 1, 1ull);
-    gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, __ldg(A.nc_ptr + row0), __ldg(A.nc_ptr + row0 + nrows), nullptr, nullptr, nullptr);
-    if constexpr (SRC) {
-      if (t < nrows && (A.node_is_own == nullptr || A.node_is_own[row0 + t] != 0))
-        A.rhs[(row0 + t) * BS] += A.rhs_factor * row_measure<NV>(A, row0 + t);
+    if (A.row_perm == nullptr) {
+      gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, __ldg(A.nc_ptr + row0), __ldg(A.nc_ptr + row0 + nrows), nullptr, nullptr, nullptr);
+      if constexpr (SRC) {
+        if (t < nrows && (A.node_is_own == nullptr || A.node_is_own[row0 + t] != 0))
+          A.rhs[(row0 + t) * BS] += A.rhs_factor * row_measure<NV>(A, row0 + t);
+      }
+    }
+    else { // reorder mode: the same rows in the caller's numbering, on the caller's arrays
+      AssembleArgs C = A;
+      C.row_index = A.out_row_index;
+      C.columns = A.caller_columns;
+      C.coords = A.caller_coords;
+      gather_rows<Op, PER_BLOCK, false>(C, op, row0, nrows, 0, 0, 0, 0, nullptr, nullptr, nullptr, A.row_perm);
+      if constexpr (SRC) {
+        if (t < nrows) {
+          const long long r = __ldg(A.row_perm + row0 + t);
+          if (A.node_is_own == nullptr || A.node_is_own[r] != 0)
+            A.rhs[r * BS] += A.rhs_factor * row_measure<NV>(C, r);
+        }
+      }
     }
     continue;
   }
@@ -909,23 +926,38 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       tma_load_1d(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
   }
   const int nval = (vend - vbeg) * BS2;
+  // per-row setup overlaps the bulk copies
+  const long long row = row0 + t; // internal row in the reorder mode
+  const bool permuted = A.row_perm != nullptr;
+  long long out_row = row; // the caller's row: ownership, right-hand side, destination of the values
+  int32_t rb = 0, qb = 0;
+  int k = 0, nstep = 0;
+  long long out_base = 0; // first value of the row in the caller's value array (reorder mode)
+  double X0[3] = { 0.0, 0.0, 0.0 };
+  if (t < nrows) {
+    rb = __ldg(A.row_index + row);
+    k = __ldg(A.row_index + row + 1) - rb;
+    if (permuted) {
+      out_row = __ldg(A.row_perm + row);
+      out_base = (long long)__ldg(A.out_row_index + out_row) * BS2;
+    }
+  }
   if (A.accumulate && !POST) {
-    for (int q = t; q < nval; q += C::ROWS)
-      acc_s[q] = A.values[(long long)vbeg * BS2 + q];
+    if (!permuted) {
+      for (int q = t; q < nval; q += C::ROWS)
+        acc_s[q] = A.values[(long long)vbeg * BS2 + q];
+    }
+    else if (t < nrows) {
+      for (int q = 0; q < k * BS2; ++q)
+        acc_s[(size_t)(rb - vbeg) * BS2 + q] = A.values[out_base + q];
+    }
   }
   else {
     for (int q = t; q < nval; q += C::ROWS)
       acc_s[q] = 0.0;
   }
-  // per-row setup overlaps the bulk copies
-  const long long row = row0 + t;
-  int32_t rb = 0, qb = 0;
-  int k = 0, nstep = 0;
-  double X0[3] = { 0.0, 0.0, 0.0 };
   if (t < nrows) {
-    rb = __ldg(A.row_index + row);
-    k = __ldg(A.row_index + row + 1) - rb;
-    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[row] != 0);
+    const bool own = (A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0);
     qb = __ldg(A.fan_ptr + row);
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
     load_xyz(A.coords, (int32_t)row, X0);
@@ -1243,10 +1275,30 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     }
     store_block<BS, PER_BLOCK>(acc, k, ds, diag);
     if constexpr (SRC)
-      A.rhs[row * BS] += A.rhs_factor * measure;
+      A.rhs[out_row * BS] += A.rhs_factor * measure;
   }
 
   __syncthreads();
+  if (permuted) {
+    // reorder mode: the tile's rows are not neighbours in the caller's value array; a half-warp per row copies the row's
+    // k * BS2 values (contiguous at both ends) to where the caller's row_index puts them
+    const bool add_old_p = POST && A.accumulate;
+    const int lane = t & 31, half = lane >> 4, hl = lane & 15;
+    for (int j = 0; j < 32; j += 2) {
+      const int src_lane = j + half;
+      const int kj = __shfl_sync(0xffffffffu, k, src_lane);
+      const int32_t rbj = __shfl_sync(0xffffffffu, rb, src_lane);
+      const long long dst = __shfl_sync(0xffffffffu, out_base, src_lane);
+      const bool live = ((t & ~31) + src_lane) < nrows;
+      if (live) {
+        const double* src = acc_s + (size_t)(rbj - vbeg) * BS2;
+        for (int q = hl; q < kj * BS2; q += 16)
+          A.values[dst + q] = src[q] + (add_old_p ? A.values[dst + q] : 0.0);
+      }
+    }
+    __syncthreads();
+    continue;
+  }
   const long long base = (long long)vbeg * BS2;
   const int head = (int)(base & 1); // values is 16-byte aligned at element 0
   const bool add_old = POST && A.accumulate;
@@ -1334,6 +1386,16 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
       grid = A.nb_tile;
     if (grid > 0) {
       long long ctas = grid;
+      AssembleArgs F = A; // the fan kernel's view: in the reorder mode the internal copies take the place of the caller's arrays
+      if (A.r_perm != nullptr) {
+        F.row_perm = A.r_perm;
+        F.out_row_index = A.row_index;
+        F.caller_columns = A.columns;
+        F.caller_coords = A.coords;
+        F.row_index = A.r_row_index;
+        F.columns = A.r_columns;
+        F.coords = A.r_coords;
+      }
 #if B2F_FAN_PERSIST
       // one CTA per resident slot (B2F_FAN_PERSIST = waves of such CTAs; 1 = exactly the resident set)
       static int sm_count = 0;
@@ -1350,7 +1412,7 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
       if (resident < ctas)
         ctas = resident;
 #endif
-      kern<<<(unsigned)ctas, C::ROWS, smem, stream>>>(A, op, acc_blocks, step_cap, grid);
+      kern<<<(unsigned)ctas, C::ROWS, smem, stream>>>(F, op, acc_blocks, step_cap, grid);
     }
     return cudaGetLastError();
   }

@@ -34,6 +34,19 @@ struct AssembleArgs
   double* rhs = nullptr; // fused constant source (fan kernel): rhs[row * BS] += rhs_factor * (sum of 6*volume / 2*area of the incident cells)
   double rhs_factor = 0.0;
   int diag_last = 0; // rows are stored neighbours first (ascending), diagonal last (b2f_pattern_layout)
+  // Reorder mode of the fan kernel (b2f_options.reorder): the kernel walks tiles of INTERNAL rows (a space-filling order of the
+  // nodes); row_index / columns / coords / fan_* above are then the internal copies (rows permuted, column ids and coordinates in
+  // the internal numbering) and the values are written to the caller's layout through row_perm / out_row_index.
+  // filled from the handle (null without reordering); every kernel but the fan kernel ignores them:
+  const int32_t* r_perm = nullptr; // internal row -> caller row
+  const int32_t* r_row_index = nullptr; // internal copies: rows permuted, column ids and coordinates in the internal numbering
+  const int32_t* r_columns = nullptr;
+  const double* r_coords = nullptr;
+  // set by the fan kernel's launcher, which swaps the internal copies into row_index / columns / coords:
+  const int32_t* row_perm = nullptr; // internal row -> caller row; null = rows are walked in the caller's order
+  const int32_t* out_row_index = nullptr; // caller row_index: where a row's values go
+  const int32_t* caller_columns = nullptr; // caller-numbered columns / coordinates for the tiles that take the global fallback path
+  const double* caller_coords = nullptr;
 };
 
 enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };

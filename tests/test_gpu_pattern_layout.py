@@ -30,13 +30,22 @@ def _setup(mesh_name, bs, use_csr, variant, sparsity_build=0):
     return fem, bsr, dim, cells, coords
 
 
-def _rotation(ri):
-    """index map canonical (diagonal first) -> diagonal-last storage, per block."""
+def _maps(ri):
+    """(to_storage, to_canonical): storage_array == canonical_array[to_storage], canonical_array == storage_array[to_canonical].
+    Canonical = diagonal first; storage = diagonal last: canonical slot 0 lives at k - 1, canonical slot x >= 1 at x - 1."""
     k = np.diff(ri)
     start = np.repeat(ri[:-1], k)
     pos = np.arange(ri[-1]) - start
     kk = np.repeat(k, k)
-    return start + (pos + kk - 1) % kk  # canonical slot 0 (diagonal) lives at k - 1, slot x >= 1 at x - 1
+    return start + (pos + 1) % kk, start + (pos + kk - 1) % kk
+
+
+def _rotation(ri):
+    return _maps(ri)[0]
+
+
+def _to_canonical(ri):
+    return _maps(ri)[1]
 
 
 @pytest.mark.parametrize("sparsity_build", [0, 1])
@@ -79,12 +88,12 @@ def test_values_match_the_oracle_after_rotating_the_rows(mesh_name, bs, kind, va
     assert st["columns_not_found"] == 0 and st["gather_fallback_tiles"] == 0
     got = block_rows(_np(bsr.matrix().values()), ri, bs, not use_csr)  # blocks in storage order
     canon = np.empty_like(got)
-    canon[:] = got[_rotation(ri)]
+    canon[:] = got[_to_canonical(ri)]
     assert_values_close(canon.reshape(-1), ref, ri, bs, what=f"{mesh_name} bs={bs} {kind} variant {variant} diag-last")
     # accumulate mode doubles
     bsr.assembleBilinear(op, accumulate=True)
     torch.cuda.synchronize()
-    twice = block_rows(_np(bsr.matrix().values()), ri, bs, not use_csr)[_rotation(ri)]
+    twice = block_rows(_np(bsr.matrix().values()), ri, bs, not use_csr)[_to_canonical(ri)]
     assert_values_close(twice.reshape(-1), 2.0 * ref, ri, bs, what="accumulate")
 
 
