@@ -107,7 +107,7 @@ int b2f_create(const b2f_mesh_view* mesh, const b2f_options* options, b2f_handle
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown pattern_layout %d", options->pattern_layout);
   if (options->pattern_layout == B2F_PATTERN_DIAG_LAST && options->assembly_variant == B2F_ASM_NODE_GATHER_SLOTS)
     return fail(B2F_ERR_NOT_IMPLEMENTED, "b2f_create: the first-generation slot-word kernel (kept for A/B measurements) only knows the diagonal-first layout");
-  if (options->reorder != B2F_REORDER_NONE && options->reorder != B2F_REORDER_MORTON)
+  if (options->reorder < B2F_REORDER_NONE || options->reorder > B2F_REORDER_PENCIL)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown reorder %d", options->reorder);
   if (options->fan_mode < B2F_FAN_AUTO || options->fan_mode > B2F_FAN_LOCKSTEP)
     return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_create: unknown fan_mode %d", options->fan_mode);
@@ -136,7 +136,7 @@ int b2f_destroy(b2f_handle h)
                      &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->ws_keys_a, &h->ws_keys_b, &h->ws_tmp, &h->ws_i32a, &h->ws_i64,
                      &h->coords_stage, &h->ghost.send_index, &h->ghost.recv_index, &h->ghost.send_vals, &h->ghost.recv_vals, &h->ghost.recv_dst, &h->ghost.recv_src,
                      &h->ij_flag, &h->ij_off, &h->ij_ncols, &h->ij_rows, &h->ij_row_local, &h->ij_cols, &h->ij_values, &h->ij_rhs,
-                     &h->perm_rows, &h->r_row_index, &h->r_columns, &h->r_coords };
+                     &h->perm_rows, &h->r_row_index, &h->r_columns, &h->r_coords, &h->r_slot_map };
   for (DevBuf* b : bufs)
     b->release();
   for (cudaEvent_t e : h->pipe_events)
@@ -370,7 +370,7 @@ int b2f_get_stats(b2f_handle h, b2f_stats* out)
   out->workspace_bytes = (int64_t)(h->ws_keys_a.bytes + h->ws_keys_b.bytes + h->ws_tmp.bytes + h->ws_i32a.bytes + h->ws_i64.bytes);
   const DevBuf* res[] = { &h->row_index, &h->columns, &h->nb_nz_per_row, &h->values, &h->nc_ptr, &h->nc_list, &h->nc_slots, &h->fan_ptr, &h->fan_steps, &h->fan_cell, &h->csr_rows, &h->csr_nbcol, &h->csr_cols, &h->rhs,
                           &h->forced_info, &h->forced_value, &h->elim_info, &h->elim_value, &h->counters, &h->coords_stage, &h->perm_rows, &h->r_row_index, &h->r_columns,
-                          &h->r_coords };
+                          &h->r_coords, &h->r_slot_map };
   for (const DevBuf* b : res)
     out->resident_bytes += (int64_t)b->bytes;
   return B2F_OK;

@@ -40,6 +40,7 @@ void fill_assemble_args(const b2f_context_s* h, AssembleArgs* out)
     A.r_row_index = h->r_row_index.as<int32_t>();
     A.r_columns = h->r_columns.as<int32_t>();
     A.r_coords = h->r_coords.as<double>();
+    A.r_slot_map = h->r_slot_map.as<uint16_t>();
   }
   *out = A;
 }

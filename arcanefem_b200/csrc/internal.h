@@ -87,7 +87,8 @@ struct b2f_context_s
   // b2f_reorder: the plan above is stored in the library's own node order; internal -> caller row, the internal copies of
   // row_index / columns (column ids in the internal numbering) and of the coordinates (refreshed by every assembly)
   bool reordered = false;
-  b2f::DevBuf perm_rows, r_row_index, r_columns, r_coords;
+  b2f::DevBuf perm_rows, r_row_index, r_columns, r_coords, r_slot_map;
+  bool inner = false; // the shadow context reorder_plan builds the internal pattern + plan in: no value array, no system state
   bool fan_ok = false;
   bool fan_lockstep = false; // step words converted to the lockstep form (sparsity.cu k_fan_lockstep)
   double fan_lockstep_bodies = 0.0; // step bodies a warp would execute per warp step in the lockstep form (1 = rows in step)

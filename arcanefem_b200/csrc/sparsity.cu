@@ -15,6 +15,7 @@
 //     row is then sorted (warp rank sort), giving the canonical order "diagonal, then ascending ids";
 //   * all sizes are 64-bit internally; Int32 overflow of a per-rank count is reported, not wrapped.
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <utility>
 #include <cub/cub.cuh>
@@ -887,7 +888,8 @@ static int pattern_from_lists(b2f_context_s* h, cudaStream_t stream, bool* fallb
   h->nb_nz = nb_nz;
   h->nb_edge = (nb_col - nn) / 2;
   B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
-  B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
+  if (!h->inner)
+    B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
   if (nn > 0) {
     if (nv == 3)
       k_row_unique<3, true><<<grid_for(nn, RU_ROWS), RU_ROWS, 0, stream>>>(h->mesh.cell_node, ncp, ncl, nn, h->row_index.as<int32_t>(), nullptr, h->columns.as<int32_t>(), counters,
@@ -965,7 +967,8 @@ static int pattern_by_sort(b2f_context_s* h, cudaStream_t stream)
 
   // --- K5: columns, then canonical order inside every row
   B2F_CUDA(h->columns.alloc(sizeof(int32_t) * (size_t)(nb_col + 8))); // +8: bulk copies round the tile end up to 16 bytes
-  B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
+  if (!h->inner)
+    B2F_CUDA(h->values.alloc(sizeof(double) * (size_t)nb_nz));
   int32_t* cursor = deg; // reuse: offsets.fill(1), BSRFormat.h:724 (diagonal-last rows: the neighbours start at 0, :554-567)
   k_fill_i32<<<grid_for(nn, 256), 256, 0, stream>>>(cursor, nn, 1 - h->diag_last);
   k_fill_diagonal<<<grid_for(nn, 256), 256, 0, stream>>>(h->row_index.as<int32_t>(), nn, h->columns.as<int32_t>(), h->diag_last);
@@ -1088,6 +1091,8 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
   const long long nb_adj = h->nb_pair;
 
   // --- plan of the gather kernel: fan walk (default) or the column-slot words of the first-generation kernel
+  // (b2f_reorder: the plan is built by reorder_plan on the internally renumbered connectivity instead)
+  const bool want_reorder = !h->inner && h->opt.reorder != B2F_REORDER_NONE && h->variant == B2F_ASM_NODE_GATHER && h->mesh.cell_is_own == nullptr && h->mesh.coords != nullptr && nn > 0;
   const int32_t* tile_ptr = h->nc_ptr.as<int32_t>();
   B2F_CUDA(cudaMemsetAsync(counters + 3, 0, sizeof(unsigned long long), stream));
   h->fan_ok = false;
@@ -1102,7 +1107,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
                                                               h->nc_list.as<uint32_t>(), nn, h->nc_slots.as<uint32_t>(), counters);
     B2F_CUDA(cudaGetLastError());
   }
-  else if (h->variant == B2F_ASM_NODE_GATHER) {
+  else if (h->variant == B2F_ASM_NODE_GATHER && !want_reorder) {
     B2F_CUDA(h->ws_i32a.alloc(sizeof(int32_t) * (size_t)(nn + 1)));
     int32_t* fan_count = h->ws_i32a.as<int32_t>();
     const int32_t* ri = h->row_index.as<int32_t>();
@@ -1173,15 +1178,24 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 6, cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaStreamSynchronize(stream));
     h->slots_ok = (h->variant == B2F_ASM_NODE_GATHER_SLOTS) && (long_rows == 0);
-    h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0);
+    h->fan_ok = (h->variant == B2F_ASM_NODE_GATHER) && (long_rows == 0) && !want_reorder;
   }
 
   // b2f_reorder: store the plan in a space-filling order of the nodes (single-rank node gather only)
   h->reordered = false;
-  if (h->opt.reorder == B2F_REORDER_MORTON && h->fan_ok && h->mesh.cell_is_own == nullptr && h->mesh.coords != nullptr) {
-    rc = reorder_plan(h, stream);
+  if (want_reorder) {
+    rc = reorder_plan(h, stream); // sets fan_ok / reordered when every row fits the walk plan; otherwise the search-based kernel runs
     if (rc != B2F_OK)
       return rc;
+  }
+  if (h->inner) { // shadow context of reorder_plan: pattern + plan only
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    h->ws_i64.release();
+    h->ws_tmp.release();
+    h->ws_i32a.release();
+    h->ws_keys_a.release();
+    h->has_pattern = true;
+    return B2F_OK;
   }
 
   // BSRMatrix::initialize fills the values with 0 (femutils/BSRFormat.h:136); done last because the plan build borrows the array
@@ -1261,17 +1275,27 @@ namespace {
     v = (v | v << 2) & 0x1249249249249249ull;
     return v;
   }
-  __global__ void __launch_bounds__(256) k_morton_keys(const double* __restrict__ coords, long long nn, double x0, double y0, double z0, double sx, double sy, double sz,
-                                                       unsigned long long* __restrict__ keys, int32_t* __restrict__ ids)
+  // mode 1 (MORTON): 21 bits per axis interleaved.  mode 2 (PENCIL): bins of one mean node spacing in z and y (offset by half a
+  // bin, so the jittered planes of a structured mesh stay together), x resolved to 21 bits inside a bin: key = (bin z, bin y, x).
+  __global__ void __launch_bounds__(256) k_order_keys(const double* __restrict__ coords, long long nn, int mode, double x0, double y0, double z0, double sx, double sy, double sz,
+                                                      double inv_h, unsigned long long* __restrict__ keys, int32_t* __restrict__ ids)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nn)
       return;
     const double q = 2097151.0; // 2^21 - 1
-    const unsigned long long a = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i] - x0) * sx));
-    const unsigned long long b = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 1] - y0) * sy));
-    const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 2] - z0) * sz));
-    keys[i] = spread3(a) | (spread3(b) << 1) | (spread3(c) << 2);
+    const double x = coords[3 * i] - x0, y = coords[3 * i + 1] - y0, z = coords[3 * i + 2] - z0;
+    const unsigned long long a = (unsigned long long)fmin(q, fmax(0.0, x * sx));
+    if (mode == 2) {
+      const unsigned long long by = (unsigned long long)fmin(q, fmax(0.0, floor(y * inv_h + 0.5)));
+      const unsigned long long bz = (unsigned long long)fmin(q, fmax(0.0, floor(z * inv_h + 0.5)));
+      keys[i] = (bz << 42) | (by << 21) | a;
+    }
+    else {
+      const unsigned long long b = (unsigned long long)fmin(q, fmax(0.0, y * sy));
+      const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, z * sz));
+      keys[i] = spread3(a) | (spread3(b) << 1) | (spread3(c) << 2);
+    }
     ids[i] = (int32_t)i;
   }
   __global__ void __launch_bounds__(256) k_invert_perm(const int32_t* __restrict__ perm, long long nn, int32_t* __restrict__ newid)
@@ -1280,36 +1304,35 @@ namespace {
     if (i < nn)
       newid[perm[i]] = (int32_t)i;
   }
-  __global__ void __launch_bounds__(256) k_perm_lengths(const int32_t* __restrict__ perm, long long nn, const int32_t* __restrict__ row_index, const int32_t* __restrict__ fan_ptr,
-                                                        int32_t* __restrict__ len_row, int32_t* __restrict__ len_fan)
+  __global__ void __launch_bounds__(256) k_renumber_cells(const int32_t* __restrict__ cell_node, long long n, const int32_t* __restrict__ newid, int32_t* __restrict__ out)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nn)
-      return;
-    const int32_t r = perm[i];
-    len_row[i] = row_index[r + 1] - row_index[r];
-    len_fan[i] = fan_ptr[r + 1] - fan_ptr[r];
+    if (i < n)
+      out[i] = newid[cell_node[i]];
   }
-  // one warp per internal row: columns (translated), step words (pivot hint cleared: it is a property of the 32 rows a warp
-  // walks together and is recomputed for the new grouping), cell ids
-  __global__ void __launch_bounds__(256) k_perm_rows(const int32_t* __restrict__ perm, const int32_t* __restrict__ newid, long long nn, const int32_t* __restrict__ row_index,
-                                                     const int32_t* __restrict__ columns, const int32_t* __restrict__ fan_ptr, const uint32_t* __restrict__ fan_steps,
-                                                     const uint32_t* __restrict__ fan_cell, const int32_t* __restrict__ r_row_index, int32_t* __restrict__ r_columns,
-                                                     const int32_t* __restrict__ r_fan_ptr, uint32_t* __restrict__ r_fan_steps, uint32_t* __restrict__ r_fan_cell)
+  // One warp per internal row i (caller row r = perm[i]): block x of the internal row is column perm[r_columns[x]] of the
+  // caller's row; its slot there is found by a scan of the caller's row (rows are short; both rows hold the same set).
+  __global__ void __launch_bounds__(256) k_slot_map(const int32_t* __restrict__ perm, long long nn, const int32_t* __restrict__ r_row_index, const int32_t* __restrict__ r_columns,
+                                                    const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns, uint16_t* __restrict__ slot_map,
+                                                    unsigned long long* __restrict__ unmatched)
   {
     const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (i >= nn)
       return;
     const int32_t r = perm[i];
-    const int32_t cb = row_index[r], k = row_index[r + 1] - cb, db = r_row_index[i];
-    for (int q = lane; q < k; q += 32)
-      r_columns[db + q] = newid[columns[cb + q]];
-    const int32_t fb = fan_ptr[r], nf = fan_ptr[r + 1] - fb, gb = r_fan_ptr[i];
-    for (int q = lane; q < nf; q += 32) {
-      const uint32_t w = fan_steps[fb + q];
-      r_fan_steps[gb + q] = (w & 0x80000000u) ? w : (w & ~4096u);
-      r_fan_cell[gb + q] = fan_cell[fb + q];
+    const int32_t ib = r_row_index[i], k = r_row_index[i + 1] - ib, cb = row_index[r], kc = row_index[r + 1] - cb;
+    for (int x = lane; x < k; x += 32) {
+      const int32_t c = perm[r_columns[ib + x]];
+      int found = -1;
+      for (int y = 0; y < kc; ++y)
+        if (columns[cb + y] == c) {
+          found = y;
+          break;
+        }
+      if (found < 0 || k != kc)
+        atomicAdd(unmatched, 1ull);
+      slot_map[ib + x] = (uint16_t)(found < 0 ? 0 : found);
     }
   }
   __global__ void __launch_bounds__(256) k_permute_coords(const int32_t* __restrict__ perm, long long nn, const double* __restrict__ coords, double* __restrict__ out)
@@ -1344,12 +1367,20 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
   B2F_CUDA(cudaMemcpyAsync(box, box_d.p, sizeof(box), cudaMemcpyDeviceToHost, stream));
   B2F_CUDA(cudaStreamSynchronize(stream));
   box_d.release();
-  double lo[3], sc[3];
+  double lo[3], sc[3], measure = 1.0;
+  int axes = 0;
   for (int d = 0; d < 3; ++d) {
     lo[d] = unorder_bits(box[d]);
     const double ext = unorder_bits(box[3 + d]) - lo[d];
     sc[d] = ext > 0.0 ? 2097151.0 / ext : 0.0;
+    if (ext > 0.0) {
+      measure *= ext;
+      ++axes;
+    }
   }
+  // mean node spacing of the bounding box (PENCIL bins)
+  const double spacing = axes > 0 ? pow(measure / (double)nn, 1.0 / axes) : 1.0;
+  const double inv_h = spacing > 0.0 ? 1.0 / spacing : 0.0;
   // 2. Morton keys, stable radix sort -> perm (internal -> caller), newid (caller -> internal)
   DevBuf keys_a, keys_b, ids_a, newid;
   B2F_CUDA(keys_a.alloc(sizeof(unsigned long long) * (size_t)nn));
@@ -1363,7 +1394,8 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
     ids_a.release();
     newid.release();
   };
-  k_morton_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], keys_a.as<unsigned long long>(), ids_a.as<int32_t>());
+  k_order_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, h->opt.reorder, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], inv_h, keys_a.as<unsigned long long>(),
+                                                      ids_a.as<int32_t>());
   {
     size_t tb = 0;
     cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(),
@@ -1379,75 +1411,79 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
     }
   }
   k_invert_perm<<<grid_for(nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, newid.as<int32_t>());
-  // 3. internal offsets
-  DevBuf len_row, len_fan, new_fan_ptr, new_steps, new_cell;
-  cudaError_t e = len_row.alloc(sizeof(int32_t) * (size_t)(nn + 1));
-  if (e == cudaSuccess)
-    e = len_fan.alloc(sizeof(int32_t) * (size_t)(nn + 1));
-  if (e == cudaSuccess)
-    e = h->r_row_index.alloc(sizeof(int32_t) * (size_t)(nn + 1));
-  if (e == cudaSuccess)
-    e = new_fan_ptr.alloc(sizeof(int32_t) * (size_t)(nn + 1));
-  if (e == cudaSuccess)
-    e = h->r_columns.alloc(sizeof(int32_t) * (size_t)(h->nb_col + 8));
-  if (e == cudaSuccess)
-    e = new_steps.alloc(sizeof(uint32_t) * (size_t)(h->nb_fan_step + 8));
-  if (e == cudaSuccess)
-    e = new_cell.alloc(sizeof(uint32_t) * (size_t)(h->nb_fan_step + 8));
-  if (e == cudaSuccess)
-    e = h->r_coords.alloc(sizeof(double) * 3 * (size_t)nn);
-  auto cleanup2 = [&]() {
-    cleanup();
-    len_row.release();
-    len_fan.release();
-    new_fan_ptr.release();
-    new_steps.release();
-    new_cell.release();
-  };
+  // 3. the connectivity in the internal numbering, and pattern + node->cell lists + walk plan built from it by the ordinary
+  //    build in a shadow context (no value array, no system state): the walks are then canonical in the INTERNAL column order,
+  //    so the rows a warp walks together (neighbours in space) meet "the same" neighbour at the same step
+  const long long nc = h->mesh.nb_cell;
+  DevBuf r_cells;
+  cudaError_t e = r_cells.alloc(sizeof(int32_t) * (size_t)(nc * h->nv));
   if (e != cudaSuccess) {
-    cleanup2();
-    return fail_cuda(e, "reorder_plan: allocation");
+    cleanup();
+    return fail_cuda(e, "reorder_plan: allocation of the renumbered connectivity");
   }
-  k_perm_lengths<<<grid_for(nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, h->row_index.as<int32_t>(), h->fan_ptr.as<int32_t>(), len_row.as<int32_t>(),
-                                                        len_fan.as<int32_t>());
-  long long t1 = 0, t2 = 0;
-  int rc = scan_counts(h, len_row.as<int32_t>(), nn, h->r_row_index.as<int32_t>(), &t1, stream);
-  if (rc == B2F_OK)
-    rc = scan_counts(h, len_fan.as<int32_t>(), nn, new_fan_ptr.as<int32_t>(), &t2, stream);
-  if (rc == B2F_OK && (t1 != h->nb_col || t2 != h->nb_fan_step))
-    rc = fail(B2F_ERR_STATE, "reorder_plan: permuted sizes %lld / %lld differ from %lld / %lld", t1, t2, (long long)h->nb_col, (long long)h->nb_fan_step);
+  k_renumber_cells<<<grid_for(nc * h->nv, 256), 256, 0, stream>>>(h->mesh.cell_node, nc * h->nv, newid.as<int32_t>(), r_cells.as<int32_t>());
+  b2f_context_s in;
+  in.inner = true;
+  in.mesh = h->mesh;
+  in.mesh.cell_node = r_cells.as<int32_t>();
+  in.mesh.coords = nullptr;
+  in.mesh.node_is_own = nullptr;
+  in.opt = h->opt;
+  in.opt.reorder = B2F_REORDER_NONE;
+  in.bs = h->bs;
+  in.nv = h->nv;
+  in.variant = h->variant;
+  in.per_block = h->per_block;
+  in.diag_last = h->diag_last;
+  in.device = h->device;
+  int rc = build_pattern(&in, stream);
+  DevBuf* in_all[] = { &in.row_index, &in.columns, &in.nb_nz_per_row, &in.values, &in.nc_ptr, &in.nc_list, &in.nc_slots, &in.fan_ptr, &in.fan_steps, &in.fan_cell,
+                       &in.counters, &in.ws_keys_a, &in.ws_keys_b, &in.ws_tmp, &in.ws_i32a, &in.ws_i64 };
+  auto drop_inner = [&]() {
+    for (DevBuf* b : in_all)
+      b->release();
+    r_cells.release();
+    cleanup();
+  };
   if (rc != B2F_OK) {
-    cleanup2();
+    drop_inner();
     return rc;
   }
-  // 4. rows into the internal order
-  k_perm_rows<<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), newid.as<int32_t>(), nn, h->row_index.as<int32_t>(), h->columns.as<int32_t>(),
-                                                          h->fan_ptr.as<int32_t>(), h->fan_steps.as<uint32_t>(), h->fan_cell.as<uint32_t>(), h->r_row_index.as<int32_t>(),
-                                                          h->r_columns.as<int32_t>(), new_fan_ptr.as<int32_t>(), new_steps.as<uint32_t>(), new_cell.as<uint32_t>());
-  e = cudaGetLastError();
+  if (!in.fan_ok || in.nb_col != h->nb_col) { // a row too long for the walk plan: the search-based kernel runs, on the caller's arrays
+    drop_inner();
+    h->perm_rows.release();
+    return B2F_OK;
+  }
+  // 4. the internal arrays move into the handle; slot map internal block -> slot in the caller's row
+  std::swap(h->r_row_index, in.row_index);
+  std::swap(h->r_columns, in.columns);
+  std::swap(h->fan_ptr, in.fan_ptr);
+  std::swap(h->fan_steps, in.fan_steps);
+  std::swap(h->fan_cell, in.fan_cell);
+  h->nb_fan_step = in.nb_fan_step;
+  for (int q = 0; q < 6; ++q)
+    h->tile_extents[q] = in.tile_extents[q];
+  e = h->r_slot_map.alloc(sizeof(uint16_t) * (size_t)(h->nb_col + 8));
+  if (e == cudaSuccess)
+    e = h->r_coords.alloc(sizeof(double) * 3 * (size_t)nn);
+  if (e == cudaSuccess) {
+    B2F_CUDA(cudaMemsetAsync(counters + 3, 0, sizeof(unsigned long long), stream));
+    k_slot_map<<<grid_for(nn * 32, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, h->r_row_index.as<int32_t>(), h->r_columns.as<int32_t>(), h->row_index.as<int32_t>(),
+                                                           h->columns.as<int32_t>(), h->r_slot_map.as<uint16_t>(), counters + 3);
+    e = cudaGetLastError();
+  }
+  unsigned long long unmatched = 0;
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(&unmatched, counters + 3, sizeof(unmatched), cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess)
     e = cudaStreamSynchronize(stream);
-  if (e != cudaSuccess) {
-    cleanup2();
-    return fail_cuda(e, "reorder_plan: row permutation");
-  }
-  // the plan of the handle is now the internal one
-  std::swap(h->fan_ptr, new_fan_ptr);
-  std::swap(h->fan_steps, new_steps);
-  std::swap(h->fan_cell, new_cell);
-  cleanup2();
-  if (h->nv == 4 && h->nb_fan_step > 0) {
-    k_fan_pivot_hint<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
-    B2F_CUDA(cudaGetLastError());
-  }
-  {
-    int* ext = reinterpret_cast<int*>(counters + 4);
-    B2F_CUDA(cudaMemsetAsync(ext, 0, sizeof(int) * 6, stream));
-    k_tile_extents<<<grid_for((nn + 31) / 32, 128), 128, 0, stream>>>(h->r_row_index.as<int32_t>(), h->fan_ptr.as<int32_t>(), nn, ext);
-    B2F_CUDA(cudaGetLastError());
-    B2F_CUDA(cudaMemcpyAsync(h->tile_extents, ext, sizeof(int) * 6, cudaMemcpyDeviceToHost, stream));
-    B2F_CUDA(cudaStreamSynchronize(stream));
-  }
+  drop_inner();
+  if (e != cudaSuccess)
+    return fail_cuda(e, "reorder_plan: slot map");
+  if (unmatched != 0)
+    return fail(B2F_ERR_STATE, "reorder_plan: %llu blocks of the internal pattern have no counterpart in the caller's pattern", unmatched);
+  h->fan_ok = true;
+  h->fan_lockstep = false;
   h->reordered = true;
   return B2F_OK;
 }

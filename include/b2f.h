@@ -113,12 +113,18 @@ typedef enum b2f_pattern_layout { B2F_PATTERN_DIAG_FIRST = 0, B2F_PATTERN_DIAG_L
  * their neighbours: it is fast when consecutive node ids are close in space (any mesh generator's numbering, an RCM or a
  * space-filling order) and several times slower when they are not (a random renumbering: 6.8 ms instead of 0.95 ms on the
  * 50 M-tet cube).  The reference's one-thread-per-cell kernels have no such precondition (femutils/BSRFormat.h:807-836), so the
- * library can supply the locality itself.  MORTON: b2f_compute_sparsity sorts the nodes along a Morton curve of their
- * coordinates and stores its plan (tiles, column ids, walk words) in that INTERNAL order; every assembly permutes the
- * coordinates into it (one streaming pass) and the kernel writes each row's values where the CALLER's row_index puts them.
- * Pattern, values, right-hand side and every view stay in the caller's numbering, bit for bit the same as without reordering.
+ * library can supply the locality itself: b2f_compute_sparsity sorts the nodes along a space-filling order of their
+ * coordinates, renumbers the connectivity INTERNALLY and builds the kernel's plan (tiles, column ids, walk words) in that
+ * numbering; every assembly permutes the coordinates into it (one streaming pass) and the kernel writes each row's values
+ * where the CALLER's row_index and column order put them.  Pattern, values, right-hand side and every view stay in the
+ * caller's numbering (values agree with the unreordered kernel to rounding: the rows are walked in another order).
  * Applies to the node-gather variant on a single rank (ignored with cell_is_own and for the other variants). */
-typedef enum b2f_reorder { B2F_REORDER_NONE = 0, B2F_REORDER_MORTON = 1 } b2f_reorder;
+typedef enum b2f_reorder {
+  B2F_REORDER_NONE = 0,
+  B2F_REORDER_MORTON = 1, /* Morton (Z) curve of the coordinates: compact 3D tiles */
+  B2F_REORDER_PENCIL = 2 /* bins of one mean node spacing in y and z, nodes sorted by x inside a bin: a tile is a run along x, like the
+                          * lexicographic numbering of a structured mesh, so the lanes of a warp gather neighbouring coordinates */
+} b2f_reorder;
 
 /* Mirrors BSRFormat<NB_DOF>::initialize(mesh, does_linear_system_use_csr, use_atomic_free), BSRFormat.h:389. */
 typedef struct b2f_options {

@@ -17,6 +17,7 @@
 //                   value is written exactly once and no zero-fill pass is needed.
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <type_traits>
 #include <utility>
 #include <cuda_runtime.h>
@@ -947,9 +948,15 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       for (int q = t; q < nval; q += C::ROWS)
         acc_s[q] = A.values[(long long)vbeg * BS2 + q];
     }
-    else if (t < nrows) {
-      for (int q = 0; q < k * BS2; ++q)
-        acc_s[(size_t)(rb - vbeg) * BS2 + q] = A.values[out_base + q];
+    else if (t < nrows) { // block x of the internal row is block slot_map[x] of the caller's row
+      for (int x = 0; x < k; ++x) {
+        const int xs = (int)__ldg(A.slot_map + rb + x);
+#pragma unroll
+        for (int i = 0; i < BS; ++i)
+#pragma unroll
+          for (int j = 0; j < BS; ++j)
+            acc_s[(size_t)(rb - vbeg) * BS2 + value_index<BS, PER_BLOCK>(0, k, x, i, j)] = A.values[out_base + value_index<BS, PER_BLOCK>(0, k, xs, i, j)];
+      }
     }
   }
   else {
@@ -1292,8 +1299,16 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       const bool live = ((t & ~31) + src_lane) < nrows;
       if (live) {
         const double* src = acc_s + (size_t)(rbj - vbeg) * BS2;
-        for (int q = hl; q < kj * BS2; q += 16)
-          A.values[dst + q] = src[q] + (add_old_p ? A.values[dst + q] : 0.0);
+        for (int x = hl; x < kj; x += 16) { // block x of the internal row is block slot_map[x] of the caller's row
+          const int xs = (int)__ldg(A.slot_map + rbj + x);
+#pragma unroll
+          for (int i = 0; i < BS; ++i)
+#pragma unroll
+            for (int jj = 0; jj < BS; ++jj) {
+              const long long d = dst + value_index<BS, PER_BLOCK>(0, kj, xs, i, jj);
+              A.values[d] = src[value_index<BS, PER_BLOCK>(0, kj, x, i, jj)] + (add_old_p ? A.values[d] : 0.0);
+            }
+        }
       }
     }
     __syncthreads();
@@ -1374,6 +1389,11 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     const int tb = A.tile_extents[2 * lvl], ta = A.tile_extents[2 * lvl + 1];
     int acc_blocks = tb < C::ROWS * C::MAX_BLOCKS_PER_ROW ? tb : C::ROWS * C::MAX_BLOCKS_PER_ROW;
     int step_cap = ta < C::ROWS * C::MAX_ADJ_PER_ROW ? ta : C::ROWS * C::MAX_ADJ_PER_ROW;
+    if (const char* cap = getenv("B2F_FAN_TILE_CAP_BLOCKS")) { // test hook: a small tile capacity sends ordinary tiles down the global fallback path
+      const int c = atoi(cap);
+      if (c > 0 && c < acc_blocks)
+        acc_blocks = c;
+    }
     acc_blocks = (acc_blocks + 3) & ~3;
     step_cap = (step_cap + 3) & ~3;
     const size_t smem = C::smem_bytes(acc_blocks, step_cap);
@@ -1395,6 +1415,7 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
         F.row_index = A.r_row_index;
         F.columns = A.r_columns;
         F.coords = A.r_coords;
+        F.slot_map = A.r_slot_map;
       }
 #if B2F_FAN_PERSIST
       // one CTA per resident slot (B2F_FAN_PERSIST = waves of such CTAs; 1 = exactly the resident set)

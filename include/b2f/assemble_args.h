@@ -42,11 +42,13 @@ struct AssembleArgs
   const int32_t* r_row_index = nullptr; // internal copies: rows permuted, column ids and coordinates in the internal numbering
   const int32_t* r_columns = nullptr;
   const double* r_coords = nullptr;
+  const uint16_t* r_slot_map = nullptr; // per internal block: its slot in the caller's row
   // set by the fan kernel's launcher, which swaps the internal copies into row_index / columns / coords:
   const int32_t* row_perm = nullptr; // internal row -> caller row; null = rows are walked in the caller's order
   const int32_t* out_row_index = nullptr; // caller row_index: where a row's values go
   const int32_t* caller_columns = nullptr; // caller-numbered columns / coordinates for the tiles that take the global fallback path
   const double* caller_coords = nullptr;
+  const uint16_t* slot_map = nullptr;
 };
 
 enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };

@@ -88,6 +88,7 @@ def main():
     print(json.dumps({"delaunay_points": args.points, "cells": int(cells.shape[0]), "generation_s": round(time.time() - t0, 1)}), flush=True)
     measure("delaunay, random node numbering", cells, coords, 0, args.steps, args.warmup)
     measure("delaunay, random node numbering, reorder=MORTON", cells, coords, 1, args.steps, args.warmup)
+    measure("delaunay, random node numbering, reorder=PENCIL", cells, coords, 2, args.steps, args.warmup)
     mc, mx = morton_renumber(cells, coords)
     measure("delaunay, nodes numbered along a Morton curve by the caller", mc, mx, 0, args.steps, args.warmup)
     del cells, coords, mc, mx
@@ -95,8 +96,9 @@ def main():
         cells, coords = gen.cube_kuhn(args.cube, shuffle_cells=42, shuffle_nodes=7)
         measure(f"Kuhn cube {args.cube}^3, random cell order + random node numbering", cells, coords, 0, args.steps, args.warmup)
         measure(f"Kuhn cube {args.cube}^3, random cell order + random node numbering, reorder=MORTON", cells, coords, 1, args.steps, args.warmup)
+        measure(f"Kuhn cube {args.cube}^3, random cell order + random node numbering, reorder=PENCIL", cells, coords, 2, args.steps, args.warmup)
         cells, coords = gen.cube_kuhn(args.cube)
-        measure(f"Kuhn cube {args.cube}^3, lexicographic numbering (headline mesh), reorder=MORTON", cells, coords, 1, args.steps, args.warmup)
+        measure(f"Kuhn cube {args.cube}^3, lexicographic numbering (headline mesh), reorder=PENCIL", cells, coords, 2, args.steps, args.warmup)
 
 
 if __name__ == "__main__":
