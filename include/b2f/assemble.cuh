@@ -1291,6 +1291,12 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // k * BS2 values (contiguous at both ends) to where the caller's row_index puts them
     const bool add_old_p = POST && A.accumulate;
     const int lane = t & 31, half = lane >> 4, hl = lane & 15;
+    // the tile's slot map goes through shared memory (one coalesced pass; the column ids are dead after the walk, their
+    // staging area is reused): a dependent global load per block inside the copy loop cost more than the whole walk
+    uint16_t* map_s = reinterpret_cast<uint16_t*>(cols_s);
+    for (int q = t; q < vend - vbeg; q += C::ROWS)
+      map_s[q] = __ldg(A.slot_map + vbeg + q);
+    __syncthreads();
     for (int j = 0; j < 32; j += 2) {
       const int src_lane = j + half;
       const int kj = __shfl_sync(0xffffffffu, k, src_lane);
@@ -1300,7 +1306,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       if (live) {
         const double* src = acc_s + (size_t)(rbj - vbeg) * BS2;
         for (int x = hl; x < kj; x += 16) { // block x of the internal row is block slot_map[x] of the caller's row
-          const int xs = (int)__ldg(A.slot_map + rbj + x);
+          const int xs = (int)map_s[rbj - vbeg + x];
 #pragma unroll
           for (int i = 0; i < BS; ++i)
 #pragma unroll
