@@ -1275,28 +1275,36 @@ namespace {
     v = (v | v << 2) & 0x1249249249249249ull;
     return v;
   }
-  // mode 1 (MORTON): 21 bits per axis interleaved.  mode 2 (PENCIL): bins of one mean node spacing in z and y (offset by half a
-  // bin, so the jittered planes of a structured mesh stay together), x resolved to 21 bits inside a bin: key = (bin z, bin y, x).
-  __global__ void __launch_bounds__(256) k_order_keys(const double* __restrict__ coords, long long nn, int mode, double x0, double y0, double z0, double sx, double sy, double sz,
-                                                      double inv_h, unsigned long long* __restrict__ keys, int32_t* __restrict__ ids)
+  // MORTON: 21 bits per axis interleaved
+  __global__ void __launch_bounds__(256) k_morton_keys(const double* __restrict__ coords, long long nn, double x0, double y0, double z0, double sx, double sy, double sz,
+                                                       unsigned long long* __restrict__ keys, int32_t* __restrict__ ids)
   {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nn)
       return;
     const double q = 2097151.0; // 2^21 - 1
-    const double x = coords[3 * i] - x0, y = coords[3 * i + 1] - y0, z = coords[3 * i + 2] - z0;
-    const unsigned long long a = (unsigned long long)fmin(q, fmax(0.0, x * sx));
-    if (mode == 2) {
-      const unsigned long long by = (unsigned long long)fmin(q, fmax(0.0, floor(y * inv_h + 0.5)));
-      const unsigned long long bz = (unsigned long long)fmin(q, fmax(0.0, floor(z * inv_h + 0.5)));
-      keys[i] = (bz << 42) | (by << 21) | a;
-    }
-    else {
-      const unsigned long long b = (unsigned long long)fmin(q, fmax(0.0, y * sy));
-      const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, z * sz));
-      keys[i] = spread3(a) | (spread3(b) << 1) | (spread3(c) << 2);
-    }
+    const unsigned long long a = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i] - x0) * sx));
+    const unsigned long long b = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 1] - y0) * sy));
+    const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, (coords[3 * i + 2] - z0) * sz));
+    keys[i] = spread3(a) | (spread3(b) << 1) | (spread3(c) << 2);
     ids[i] = (int32_t)i;
+  }
+  // PENCIL, one pass of three: key = (group of the node's current rank, coordinate `axis` resolved to 40 bits).  ids_in = the
+  // order of the previous pass (null: identity); group = rank / group_size.  Equal-COUNT groups: slabs of nn^(2/3) nodes by z,
+  // lines of nn^(1/3) nodes by y inside a slab, then x inside a line - on a structured lattice (jittered by less than half a
+  // spacing) exactly its planes and lines, on an unstructured mesh pencils that follow the node density.
+  __global__ void __launch_bounds__(256) k_pencil_keys(const double* __restrict__ coords, long long nn, const int32_t* __restrict__ ids_in, long long group_size, int axis,
+                                                       double lo, double scale40, unsigned long long* __restrict__ keys, int32_t* __restrict__ ids_out)
+  {
+    const long long rank = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (rank >= nn)
+      return;
+    const int32_t node = ids_in ? ids_in[rank] : (int32_t)rank;
+    const unsigned long long group = (unsigned long long)(rank / group_size);
+    const double q = 1099511627775.0; // 2^40 - 1
+    const unsigned long long c = (unsigned long long)fmin(q, fmax(0.0, (coords[3ll * node + axis] - lo) * scale40));
+    keys[rank] = (group << 40) | c;
+    ids_out[rank] = node;
   }
   __global__ void __launch_bounds__(256) k_invert_perm(const int32_t* __restrict__ perm, long long nn, int32_t* __restrict__ newid)
   {
@@ -1367,20 +1375,12 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
   B2F_CUDA(cudaMemcpyAsync(box, box_d.p, sizeof(box), cudaMemcpyDeviceToHost, stream));
   B2F_CUDA(cudaStreamSynchronize(stream));
   box_d.release();
-  double lo[3], sc[3], measure = 1.0;
-  int axes = 0;
+  double lo[3], sc[3], ext[3];
   for (int d = 0; d < 3; ++d) {
     lo[d] = unorder_bits(box[d]);
-    const double ext = unorder_bits(box[3 + d]) - lo[d];
-    sc[d] = ext > 0.0 ? 2097151.0 / ext : 0.0;
-    if (ext > 0.0) {
-      measure *= ext;
-      ++axes;
-    }
+    ext[d] = unorder_bits(box[3 + d]) - lo[d];
+    sc[d] = ext[d] > 0.0 ? 2097151.0 / ext[d] : 0.0;
   }
-  // mean node spacing of the bounding box (PENCIL bins)
-  const double spacing = axes > 0 ? pow(measure / (double)nn, 1.0 / axes) : 1.0;
-  const double inv_h = spacing > 0.0 ? 1.0 / spacing : 0.0;
   // 2. Morton keys, stable radix sort -> perm (internal -> caller), newid (caller -> internal)
   DevBuf keys_a, keys_b, ids_a, newid;
   B2F_CUDA(keys_a.alloc(sizeof(unsigned long long) * (size_t)nn));
@@ -1394,21 +1394,52 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
     ids_a.release();
     newid.release();
   };
-  k_order_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, h->opt.reorder, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], inv_h, keys_a.as<unsigned long long>(),
-                                                      ids_a.as<int32_t>());
-  {
+  auto sort_pass = [&](int bits) -> cudaError_t { // (keys_a, ids_a) -> (keys_b, perm_rows), stable
     size_t tb = 0;
     cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(),
-                                                    h->perm_rows.as<int32_t>(), nn, 0, 63, stream);
+                                                    h->perm_rows.as<int32_t>(), nn, 0, bits, stream);
     if (e == cudaSuccess)
       e = h->ws_tmp.alloc(tb);
     if (e == cudaSuccess)
-      e = cub::DeviceRadixSort::SortPairs(h->ws_tmp.p, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(), h->perm_rows.as<int32_t>(), nn,
-                                          0, 63, stream);
-    if (e != cudaSuccess) {
-      cleanup();
-      return fail_cuda(e, "reorder_plan: radix sort of the Morton keys");
+      e = cub::DeviceRadixSort::SortPairs(h->ws_tmp.p, tb, keys_a.as<unsigned long long>(), keys_b.as<unsigned long long>(), ids_a.as<int32_t>(), h->perm_rows.as<int32_t>(), nn, 0,
+                                          bits, stream);
+    return e;
+  };
+  cudaError_t es = cudaSuccess;
+  if (h->opt.reorder == B2F_REORDER_PENCIL) {
+    // axes that have an extent, slowest first (z, y, x); group sizes nn^((a-1)/a) ... so that every level holds equal counts
+    int axes[3], na = 0;
+    for (int d = 2; d >= 0; --d)
+      if (ext[d] > 0.0)
+        axes[na++] = d;
+    const long long line = std::max<long long>(1, llround(pow((double)nn, na > 0 ? 1.0 / na : 1.0)));
+    const int32_t* prev = nullptr;
+    for (int lvl = 0; lvl < na && es == cudaSuccess; ++lvl) {
+      // pass 0 sorts everything along the slowest axis; pass 1 sorts inside groups of line^(na-1) consecutive ranks (slabs),
+      // pass 2 inside groups of `line` ranks (lines)
+      long long group = nn;
+      if (lvl > 0) {
+        group = 1;
+        for (int q = lvl; q < na; ++q)
+          group *= line;
+      }
+      const int d = axes[lvl];
+      k_pencil_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, prev, group, d, lo[d], 1099511627775.0 / ext[d], keys_a.as<unsigned long long>(), ids_a.as<int32_t>());
+      es = sort_pass(64);
+      prev = h->perm_rows.as<int32_t>(); // read by the next pass's key kernel before its sort rewrites it
     }
+    if (na == 0) { // all nodes coincide: identity
+      k_pencil_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, nullptr, nn, 0, 0.0, 0.0, keys_a.as<unsigned long long>(), ids_a.as<int32_t>());
+      es = sort_pass(64);
+    }
+  }
+  else {
+    k_morton_keys<<<grid_for(nn, 256), 256, 0, stream>>>(h->mesh.coords, nn, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], keys_a.as<unsigned long long>(), ids_a.as<int32_t>());
+    es = sort_pass(63);
+  }
+  if (es != cudaSuccess) {
+    cleanup();
+    return fail_cuda(es, "reorder_plan: radix sort of the order keys");
   }
   k_invert_perm<<<grid_for(nn, 256), 256, 0, stream>>>(h->perm_rows.as<int32_t>(), nn, newid.as<int32_t>());
   // 3. the connectivity in the internal numbering, and pattern + node->cell lists + walk plan built from it by the ordinary
