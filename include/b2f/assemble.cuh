@@ -373,6 +373,24 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_glob
                "l"(__cvta_generic_to_global(src_global)), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// Cache hints of the fan kernel's streams (B2F_FAN_STREAM): 1 = the slab write-out uses streaming stores (st.global.cs), 2 = also the
+// bulk copies of columns and step words carry an L2 evict_first policy - both are touched once per launch, while the gathered
+// coordinates are re-read ~14 times from L2 (hit rate 54 %, profiles/r02_fan_ncu.txt).
+#ifndef B2F_FAN_STREAM
+#define B2F_FAN_STREAM 0
+#endif
+__device__ __forceinline__ void tma_load_1d_stream(void* dst_smem, const void* src_global, uint32_t bytes, unsigned long long* bar)
+{
+#if B2F_FAN_STREAM >= 2
+  unsigned long long policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(dst_smem)),
+               "l"(__cvta_generic_to_global(src_global)), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+               : "memory");
+#else
+  tma_load_1d(dst_smem, src_global, bytes, bar);
+#endif
+}
 #ifndef B2F_FAN_PREFETCH
 #define B2F_FAN_PREFETCH 0
 #endif
@@ -857,7 +875,8 @@ struct FanCfg : SlotsCfg<Op>
 // run (which set receives the entering vertex, which of the other two leaves): no selects and no register moves, at the
 // price of one multi-way branch per step.  Rows of a warp that sit in different variants are serialised.  Opt-in
 // (B2F_FAN_LOCKSTEP, plan converted by k_fan_lockstep in sparsity.cu): on B200 it measured slower than the select walk.
-template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC, bool LOCKSTEP>
+// PERM: the reorder mode (b2f_options.reorder) as its own instantiation, so that the default kernel carries none of its state.
+template <class Op, bool PER_BLOCK, bool DIAG_BY_ROW_SUM, bool SRC, bool LOCKSTEP, bool PERM = false>
 __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / FanCfg<Op>::ROWS) k_node_fan(AssembleArgs A, Op op, int acc_blocks, int step_cap, long long nb_tiles)
 {
   using C = FanCfg<Op>;
@@ -879,8 +898,15 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   if (t == 0)
     mbar_init(bar, 1);
   __syncthreads();
+#if B2F_FAN_PERSIST
   uint32_t phase = 0;
   for (long long tile = blockIdx.x; tile < nb_tiles; tile += gridDim.x) {
+#else
+  constexpr uint32_t phase = 0;
+  const long long tile = blockIdx.x;
+  (void)nb_tiles;
+  do { // one tile per CTA; `continue` leaves
+#endif
   const long long row0 = (tile + A.first_tile) * C::ROWS;
   const long long left = A.nb_node - row0;
   const int nrows = left < C::ROWS ? (int)left : C::ROWS;
@@ -892,7 +918,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   if (!fits) { // oversized tile (very long rows): search-based path on global memory
     if (t == 0)
       atomicAdd(A.counters + 1, 1ull);
-    if (A.row_perm == nullptr) {
+    if constexpr (!PERM) {
       gather_rows<Op, PER_BLOCK, false>(A, op, row0, nrows, vbeg, vend, __ldg(A.nc_ptr + row0), __ldg(A.nc_ptr + row0 + nrows), nullptr, nullptr, nullptr);
       if constexpr (SRC) {
         if (t < nrows && (A.node_is_own == nullptr || A.node_is_own[row0 + t] != 0))
@@ -922,14 +948,14 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     mbar_expect_tx(bar, (uint32_t)(ncols_cp + nstep_cp) * 4u);
     if (ncols_cp > 0)
-      tma_load_1d(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
+      tma_load_1d_stream(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
     if (nstep_cp > 0)
-      tma_load_1d(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
+      tma_load_1d_stream(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
   }
   const int nval = (vend - vbeg) * BS2;
   // per-row setup overlaps the bulk copies
   const long long row = row0 + t; // internal row in the reorder mode
-  const bool permuted = A.row_perm != nullptr;
+  constexpr bool permuted = PERM;
   long long out_row = row; // the caller's row: ownership, right-hand side, destination of the values
   int32_t rb = 0, qb = 0;
   int k = 0, nstep = 0;
@@ -985,7 +1011,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   }
 #endif
   mbar_wait(bar, phase);
+#if B2F_FAN_PERSIST
   phase ^= 1u;
+#endif
   __syncthreads();
 
   if (nstep > 0) {
@@ -993,8 +1021,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // at position x - 1 and the diagonal at k - 1: the row's base addresses are moved back by one slot, so every neighbour access
     // of the walk is unchanged, and the diagonal is addressed as slot k.
     const int dl = A.diag_last;
-    const int ds = dl ? k : 0;
     const int acc_shift = dl * (PER_BLOCK ? BS2 : BS);
+#define B2F_DIAG_SLOT (A.diag_last ? k : 0) /* re-read from the parameter bank where it is used: no register lives across the walk */
 #if B2F_FAN_ASM_SMEM
     SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) - 8u * (uint32_t)acc_shift };
     SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) - 4u * (uint32_t)dl };
@@ -1013,7 +1041,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     for (int x = 1; x < k; ++x)
       prefetch_l2(A.coords + 3ll * cols[x]);
     double diag[BS2];
-    load_block<BS, PER_BLOCK>(acc, k, ds, diag);
+    load_block<BS, PER_BLOCK>(acc, k, B2F_DIAG_SLOT, diag);
     double measure = 0.0;
     if constexpr (LOCKSTEP) {
       static_assert(!LOCKSTEP || NV == 4, "the lockstep walk is for tetrahedra");
@@ -1280,15 +1308,14 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         sum += acc[x];
       diag[0] = -sum;
     }
-    store_block<BS, PER_BLOCK>(acc, k, ds, diag);
+    store_block<BS, PER_BLOCK>(acc, k, B2F_DIAG_SLOT, diag);
+#undef B2F_DIAG_SLOT
     if constexpr (SRC)
       A.rhs[out_row * BS] += A.rhs_factor * measure;
   }
 
   __syncthreads();
-  if (permuted) {
-    // reorder mode: the tile's rows are not neighbours in the caller's value array; a half-warp per row copies the row's
-    // k * BS2 values (contiguous at both ends) to where the caller's row_index puts them
+  if constexpr (PERM) {
     // reorder mode: one thread per row writes the row's blocks where the caller's row_index and column order put them
     // (block x of the internal row is block slot_map[x] of the caller's row).  A warp's stores are strided by the row length -
     // uncoalesced, but 3 instructions per block; the cooperative half-warp copy that coalesces them costs ~8x the instructions
@@ -1330,14 +1357,23 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     }
   }
   else {
-    for (int q = t; q < nvec; q += C::ROWS)
+    for (int q = t; q < nvec; q += C::ROWS) {
+#if B2F_FAN_STREAM >= 1
+      __stcs(dst + q, make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]));
+#else
       dst[q] = make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]);
+#endif
+    }
   }
   const int tail = head + 2 * nvec;
   if (t == 0 && tail < nval)
     A.values[base + tail] = acc_s[tail] + (add_old ? A.values[base + tail] : 0.0);
+#if B2F_FAN_PERSIST
   __syncthreads(); // the next tile of a persistent CTA clears the accumulators and overwrites the staging areas
   } // tiles of this CTA
+#else
+  } while (0);
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -1382,6 +1418,9 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
                                  : (ls ? k_node_fan<Op, PER_BLOCK, false, true, LS> : k_node_fan<Op, PER_BLOCK, false, true, false>))
                       : (row_sum ? (ls ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false, LS> : k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false, false>)
                                  : (ls ? k_node_fan<Op, PER_BLOCK, false, false, LS> : k_node_fan<Op, PER_BLOCK, false, false, false>));
+    if (A.r_perm != nullptr) // reorder mode: the select walk only (the plan is never converted to the lockstep form there)
+      kern = A.rhs ? (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, true, false, true> : k_node_fan<Op, PER_BLOCK, false, true, false, true>)
+                   : (row_sum ? k_node_fan<Op, PER_BLOCK, CAN_ROW_SUM, false, false, true> : k_node_fan<Op, PER_BLOCK, false, false, false, true>);
     if (B2F_FAN_CARVEOUT >= 0) {
       cudaError_t ec = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, B2F_FAN_CARVEOUT);
       if (ec != cudaSuccess)
