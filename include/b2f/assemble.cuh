@@ -581,6 +581,17 @@ __global__ void __launch_bounds__(SlotsCfg<Op>::ROWS) k_node_gather_slots(Assemb
 // ---------------------------------------------------------------------------------------------------
 constexpr unsigned FAN_START = 0x80000000u;
 
+// Operators whose row-0 entries are "zero-row-sum stiffness + m off the diagonal, + 2 m on it" with a per-cell mass term
+// m = op.mass(G) (heat: lambda * stiffness + mass / dt) declare `static constexpr bool ROW_SUM_MASS = true`: over the cells around
+// a row, diag = -(sum of the row's off-diagonal entries) + (NV + 1) * (sum of m) - one add per step instead of the diagonal's
+// dot product (BS = 1, overwrite mode).
+template <class Op, class = void>
+struct row_sum_mass : std::false_type
+{};
+template <class Op>
+struct row_sum_mass<Op, std::enable_if_t<Op::ROW_SUM_MASS>> : std::true_type
+{};
+
 // Operator entry points of the fan kernel, selected by arity (only the matching one is instantiated).
 template <class Op>
 __device__ __forceinline__ auto tet_finish(const Op& op, const TetGeom& T, double cell, bool odd) -> decltype(op.finish(T, cell, odd))
@@ -768,6 +779,8 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       for (int e = 0; e < BS2; ++e)
         diag[e] += out[e];
     }
+    else if constexpr (row_sum_mass<Op>::value)
+      diag[0] += op.mass(G); // the diagonal register carries the sum of the mass terms until the end of the row
     // one vertex leaves: its accumulator is flushed (plain store: it was loaded on entry).  C becomes N (renaming by
     // the caller); the vertex that stays becomes / remains O.  New m: (eC x eN) = g2 if N stays, (eC x eO) = -g1 if O stays.
     double leave[BS2];
@@ -835,6 +848,8 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       for (int e = 0; e < BS2; ++e)
         diag[e] += out[e];
     }
+    else if constexpr (row_sum_mass<Op>::value)
+      diag[0] += op.mass(G);
     store_block<BS, PER_BLOCK>(acc, k, sN, accN);
   }
 }
@@ -1121,6 +1136,8 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
           for (int q = 0; q < BS2; ++q)
             diag[q] += out[q];
         }
+        else if constexpr (DIAG_BY_ROW_SUM && row_sum_mass<Op>::value)
+          diag[0] += op.mass(G);
         if constexpr (LY) {
           store_block<BS, PER_BLOCK>(acc, k, sl[Y], av[Y]);
 #pragma unroll
@@ -1306,7 +1323,10 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       double sum = 0.0;
       for (int x = 1; x < k; ++x)
         sum += acc[x];
-      diag[0] = -sum;
+      if constexpr (row_sum_mass<Op>::value)
+        diag[0] = fma((double)(NV + 1), diag[0], -sum);
+      else
+        diag[0] = -sum;
     }
     store_block<BS, PER_BLOCK>(acc, k, B2F_DIAG_SLOT, diag);
 #undef B2F_DIAG_SLOT
@@ -1410,7 +1430,7 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
   if constexpr (uses_fan<Op>::value)
   if (variant == VARIANT_NODE_GATHER && A.fan_ok) {
     using C = FanCfg<Op>;
-    constexpr bool CAN_ROW_SUM = Op::ROW_SUM_ZERO && Op::BS == 1;
+    constexpr bool CAN_ROW_SUM = (Op::ROW_SUM_ZERO || row_sum_mass<Op>::value) && Op::BS == 1;
     const bool row_sum = CAN_ROW_SUM && !A.accumulate;
     constexpr bool LS = Op::NV == 4; // the lockstep walk exists for tets
     const bool ls = LS && A.fan_lockstep;

@@ -295,6 +295,7 @@ struct HeatTri
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true; // per-cell conductivity
   static constexpr bool LINEAR_POST = false;
+  static constexpr bool ROW_SUM_MASS = true; // row 0 = zero-row-sum stiffness + m (off the diagonal) / + 2 m (on it): see assemble.cuh
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
@@ -303,6 +304,7 @@ struct HeatTri
     double ks; // lambda * 0.25 / area
     double m; // area / 12 / dt
   };
+  __device__ __forceinline__ double mass(const Geom& G) const { return G.m; }
   __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
   __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const { return prepare_oriented(X, cell_value(cell), false); }
   // odd: X lists the cell's vertices in an odd permutation of the cell's own order (the signed area flips back)
@@ -330,6 +332,7 @@ struct HeatTet
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true;
   static constexpr bool LINEAR_POST = false;
+  static constexpr bool ROW_SUM_MASS = true;
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
@@ -337,6 +340,7 @@ struct HeatTet
     TetGeom t;
     double ks, m;
   };
+  __device__ __forceinline__ double mass(const Geom& G) const { return G.m; }
   __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const { return finish(tet_geometry(X), cell_value(cell), false); }
   __device__ __forceinline__ Geom finish(const TetGeom& T, double lam, bool) const
