@@ -64,6 +64,12 @@ class IjView(C.Structure):
                 ("cols", C.c_void_p), ("values", C.c_void_p), ("rhs", C.c_void_p)]
 
 
+class IjBuffers(C.Structure):
+    """b2f_ij_buffers: caller-owned outputs of b2f_ij_own_rows_no_alloc."""
+    _fields_ = [("capacity_rows", C.c_int64), ("capacity_values", C.c_int64), ("ncols", C.c_void_p), ("rows", C.c_void_p), ("row_local", C.c_void_p),
+                ("cols", C.c_void_p), ("values", C.c_void_p), ("rhs", C.c_void_p), ("totals_out", C.c_void_p)]
+
+
 class Stats(C.Structure):
     _fields_ = [("nb_edge", C.c_int64), ("nb_col", C.c_int64), ("nb_nz", C.c_int64), ("columns_not_found", C.c_int64),
                 ("workspace_bytes", C.c_int64), ("resident_bytes", C.c_int64), ("gather_fallback_tiles", C.c_int64), ("fan_steps", C.c_int64),
@@ -116,6 +122,8 @@ PROTOTYPES = {
     "b2f_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "b2f_nccl_comm_init": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _P(C.c_void_p)]),
     "b2f_nccl_comm_destroy": (C.c_int, [C.c_void_p]),
+    "b2f_ij_own_rows_no_alloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                           _P(IjBuffers), _S]),
 }
 
 _lib = None

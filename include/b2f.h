@@ -358,6 +358,44 @@ int b2f_nccl_unique_id(void* id128_out_host);
 int b2f_nccl_comm_init(const void* id128_host, int32_t rank, int32_t world, void** comm_out);
 int b2f_nccl_comm_destroy(void* comm);
 
+/*
+ * Allocation-free own-row extraction.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as b2f_to_hypre_ij (own rows of a CSR matrix in local order, global row / column ids, bit-identical
+ * values), but handle-free: the caller passes every input and every output as device pointers, and the two scan arrays
+ * the extraction needs (row slot and value offset per row, plus per-tile sums) live in a file-scope
+ * `static __device__` array of the library instead of the handle's workspace.  The entry point calls no cudaMalloc,
+ * cudaFree or allocating library routine and does not synchronise.
+ *   limit   : nb_row <= B2F_NO_ALLOC_MAX_ROWS scalar rows (the array is 8 MiB + 12 KiB, resident on every GPU that loads
+ *             the library until the process exits); larger sizes are refused with B2F_ERR_INVALID_ARGUMENT.
+ *   device  : the calling thread's current device (cudaSetDevice); all pointers must belong to it.  The address of the
+ *             array is looked up once per device on the first call there - a call with nb_row = 0 does only that, for
+ *             callers that want the set-up outside a capture.
+ *   sharing : every call on a device uses the same array.  Nothing in it needs clearing (each call writes every word
+ *             it later reads), but two calls that overlap on the GPU (different streams, no ordering) race; calls on
+ *             one stream, or ordered by events, are safe.
+ *   inputs  : row_ptr [nb_row] (or nb_row + 1) first entry of each row; row_ncols [nb_row] row lengths, NULL = row_ptr[r+1]-row_ptr[r];
+ *             cols / values the CSR arrays; rhs, node_is_own (per block row: row r belongs to node r / block_size) and
+ *             dof_number (global numbering; NULL keeps local ids) may be NULL.
+ *   outputs : arrays of the capacities given; rows or entries beyond a capacity are dropped, never written.
+ *             totals_out (device, 2 x int64: own rows, their entries) lets the caller check them against the capacities.
+ */
+#define B2F_NO_ALLOC_MAX_ROWS (1 << 20)
+typedef struct b2f_ij_buffers {
+  int64_t capacity_rows; /* length of ncols, rows, row_local, rhs */
+  int64_t capacity_values; /* length of cols, values */
+  int32_t* ncols;
+  int32_t* rows;
+  int32_t* row_local;
+  int32_t* cols;
+  double* values;
+  double* rhs; /* may be NULL */
+  int64_t* totals_out; /* [2] */
+} b2f_ij_buffers;
+int b2f_ij_own_rows_no_alloc(const int32_t* row_ptr, const int32_t* row_ncols, const int32_t* cols, const double* values, const double* rhs,
+                             const uint8_t* node_is_own, const int32_t* dof_number, int64_t nb_row, int32_t block_size, const b2f_ij_buffers* out,
+                             b2f_stream stream);
+
 #ifdef __cplusplus
 }
 #endif
