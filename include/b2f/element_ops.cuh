@@ -49,6 +49,12 @@ namespace b2f {
 // of three DFMAs where two Newton steps (B2F_RCP_CUBIC == 0) need four.  No range checks and no slow path like the
 // compiler's division has (cells with a measure outside the normal range are degenerate anyway).
 // tools/experiments/rcp_probe.cu measures both forms against 1.0 / x.
+// Heat rows: diagonal from the row itself (off-diagonal sum + mass sum) instead of computing it per step.  Parity-exact to
+// 1e-12 but measured slower on B200 (heat3d 1.58 vs 1.51 ms, heat2d 1.50 vs 1.39 ms: the mass term per step costs more
+// than the diagonal it removes), so it is off; -DB2F_HEAT_ROW_SUM=1 builds it for A/B runs.
+#ifndef B2F_HEAT_ROW_SUM
+#define B2F_HEAT_ROW_SUM 0
+#endif
 #ifndef B2F_RCP_CUBIC
 #define B2F_RCP_CUBIC 1
 #endif
@@ -295,7 +301,7 @@ struct HeatTri
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true; // per-cell conductivity
   static constexpr bool LINEAR_POST = false;
-  static constexpr bool ROW_SUM_MASS = true; // row 0 = zero-row-sum stiffness + m (off the diagonal) / + 2 m (on it): see assemble.cuh
+  static constexpr bool ROW_SUM_MASS = B2F_HEAT_ROW_SUM != 0; // row 0 = zero-row-sum stiffness + m (off the diagonal) / + 2 m (on it): see assemble.cuh
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
@@ -332,7 +338,7 @@ struct HeatTet
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
   static constexpr bool NEEDS_CELL = true;
   static constexpr bool LINEAR_POST = false;
-  static constexpr bool ROW_SUM_MASS = true;
+  static constexpr bool ROW_SUM_MASS = B2F_HEAT_ROW_SUM != 0;
   double lambda, inv_dt;
   const double* cell_lambda;
   struct Geom
