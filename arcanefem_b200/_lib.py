@@ -119,6 +119,7 @@ PROTOTYPES = {
     "b2f_ghost_plan": (C.c_int, [_H, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, _S]),
     "b2f_ghost_exchange": (C.c_int, [_H, C.c_void_p, _S]),
     "b2f_assemble_exchange": (C.c_int, [_H, _P(OperatorDesc), C.c_void_p, _S]),
+    "b2f_assemble_exchange_host": (C.c_int, [_H, _P(OperatorDesc), C.c_void_p, C.c_void_p, C.c_void_p, _S]),
     "b2f_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "b2f_nccl_comm_init": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _P(C.c_void_p)]),
     "b2f_nccl_comm_destroy": (C.c_int, [C.c_void_p]),

@@ -748,4 +748,149 @@ int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm,
   return ghost_add(h, s);
 }
 
+// Multi-rank twin of b2f_assemble_host: the chunk pipeline of that entry point with the ghost-row exchange of
+// b2f_assemble_exchange inside it.  Chunks are assembled in row order as their coordinates land; as soon as the chunk that
+// holds the last sent row is done the exchange starts on the handle's communication stream; chunks whose rows neither travel
+// nor receive partial sums go back to the host at once, the others after the received sums have been added.
+int b2f_assemble_exchange_host(b2f_handle h, const b2f_operator* op, void* nccl_comm, const double* coords_host, double* values_host, b2f_stream stream)
+{
+  B2F_CHECK_HANDLE(h);
+  B2F_NEED_PATTERN(h);
+  B2F_ON_DEVICE(h);
+  if (!op || !coords_host)
+    return fail(B2F_ERR_INVALID_ARGUMENT, "b2f_assemble_exchange_host: null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  const GhostPlan& P = h->ghost;
+  if (!P.ready)
+    return fail(B2F_ERR_STATE, "b2f_assemble_exchange_host: b2f_ghost_plan has not been called");
+  const long long nn = h->mesh.nb_node;
+  const size_t cbytes = sizeof(double) * 3 * (size_t)nn;
+  B2F_CUDA(h->coords_stage.alloc(cbytes));
+  const int variant = h->variant == B2F_ASM_DEFAULT ? B2F_ASM_NODE_GATHER : h->variant;
+  const bool pipelined = variant == B2F_ASM_NODE_GATHER && h->fan_ok && nn >= (1ll << 16) && !h->reordered && !op->accumulate;
+  const double* saved = h->mesh.coords;
+  if (!pipelined) {
+    B2F_CUDA(cudaMemcpyAsync(h->coords_stage.p, coords_host, cbytes, cudaMemcpyHostToDevice, s));
+    h->mesh.coords = h->coords_stage.as<double>();
+    int rc = b2f_assemble_exchange(h, op, nccl_comm, stream);
+    h->mesh.coords = saved;
+    if (rc != B2F_OK)
+      return rc;
+    if (values_host)
+      B2F_CUDA(cudaMemcpyAsync(values_host, h->values.p, sizeof(double) * (size_t)h->nb_nz, cudaMemcpyDeviceToHost, s));
+    B2F_CUDA(cudaStreamSynchronize(s));
+    return B2F_OK;
+  }
+  if (h->chunk_row.empty()) {
+    int rc = pipeline_plan(h, B2F_HOST_PIPELINE_CHUNKS, s);
+    if (rc != B2F_OK)
+      return rc;
+  }
+  const int nc = (int)h->chunk_row.size() - 1;
+  if (!h->pipe_h2d)
+    B2F_CUDA(cudaStreamCreateWithFlags(&h->pipe_h2d, cudaStreamNonBlocking));
+  if (!h->pipe_d2h)
+    B2F_CUDA(cudaStreamCreateWithFlags(&h->pipe_d2h, cudaStreamNonBlocking));
+  while ((int)h->pipe_events.size() < 2 * nc + 1) {
+    cudaEvent_t e;
+    B2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->pipe_events.push_back(e);
+  }
+  if (!h->comm_stream) {
+    int least = 0, greatest = 0;
+    B2F_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B2F_CUDA(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, greatest));
+    for (cudaEvent_t& e : h->comm_events)
+      B2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  B2F_CUDA(cudaEventRecord(h->pipe_events[2 * nc], s));
+  B2F_CUDA(cudaStreamWaitEvent(h->pipe_h2d, h->pipe_events[2 * nc], 0));
+  B2F_CUDA(cudaStreamWaitEvent(h->pipe_d2h, h->pipe_events[2 * nc], 0));
+  B2F_CUDA(cudaMemsetAsync(h->counters.p, 0, sizeof(unsigned long long) * 2, s));
+  h->mesh.coords = h->coords_stage.as<double>();
+  // a chunk waits for the exchange when its rows travel (they are zeroed by the pack) or receive partial sums
+  auto deferred = [&](int c) {
+    const bool sends = P.total_send > 0 && h->chunk_row[c] < P.send_row_hi && h->chunk_row[c + 1] > P.send_row_lo;
+    const bool receives = P.total_recv > 0 && h->chunk_value_off[c] <= P.recv_val_hi && h->chunk_value_off[c + 1] > P.recv_val_lo;
+    return sends || receives;
+  };
+  auto read_back = [&](int c) -> cudaError_t {
+    const int64_t v0 = h->chunk_value_off[c], v1 = h->chunk_value_off[c + 1];
+    return v1 > v0 ? cudaMemcpyAsync(values_host + v0, h->values.as<double>() + v0, sizeof(double) * (size_t)(v1 - v0), cudaMemcpyDeviceToHost, h->pipe_d2h) : cudaSuccess;
+  };
+  int rc = B2F_OK;
+  cudaError_t ce = cudaSuccess;
+  bool exchange_started = false;
+  auto start_exchange = [&]() {
+    ce = cudaEventRecord(h->comm_events[0], s);
+    if (ce == cudaSuccess)
+      ce = cudaStreamWaitEvent(h->comm_stream, h->comm_events[0], 0);
+    if (ce == cudaSuccess)
+      rc = ghost_send_recv(h, nccl_comm, h->comm_stream);
+    exchange_started = true;
+  };
+  if (P.total_send == 0)
+    start_exchange(); // a rank that only receives posts its receives at once
+  long long pos = 0;
+  for (int c = 0; c < nc && rc == B2F_OK && ce == cudaSuccess; ++c) {
+    const long long need = (c == nc - 1) ? nn : std::min<long long>(nn, h->chunk_node_hi[c] + 1);
+    if (need > pos) {
+      ce = cudaMemcpyAsync(h->coords_stage.as<double>() + 3 * pos, coords_host + 3 * pos, sizeof(double) * 3 * (size_t)(need - pos), cudaMemcpyHostToDevice, h->pipe_h2d);
+      if (ce == cudaSuccess)
+        ce = cudaEventRecord(h->pipe_events[2 * c], h->pipe_h2d);
+      if (ce == cudaSuccess)
+        ce = cudaStreamWaitEvent(s, h->pipe_events[2 * c], 0);
+      pos = need;
+      if (ce != cudaSuccess)
+        break;
+    }
+    h->range_first_row = h->chunk_row[c];
+    h->range_rows = h->chunk_row[c + 1] - h->chunk_row[c];
+    h->range_keep_counters = true;
+    rc = assemble(h, op, s);
+    if (rc != B2F_OK)
+      break;
+    if (!exchange_started && h->chunk_row[c + 1] >= P.send_row_hi)
+      start_exchange();
+    if (rc == B2F_OK && ce == cudaSuccess && values_host && !deferred(c)) {
+      ce = cudaEventRecord(h->pipe_events[2 * c + 1], s);
+      if (ce == cudaSuccess)
+        ce = cudaStreamWaitEvent(h->pipe_d2h, h->pipe_events[2 * c + 1], 0);
+      if (ce == cudaSuccess)
+        ce = read_back(c);
+    }
+  }
+  h->range_rows = -1;
+  h->range_first_row = 0;
+  h->range_keep_counters = false;
+  h->mesh.coords = saved;
+  // the caller's stream always rejoins the communication stream, also on an error path
+  if (exchange_started) {
+    cudaError_t e1 = cudaEventRecord(h->comm_events[1], h->comm_stream);
+    if (e1 == cudaSuccess)
+      e1 = cudaStreamWaitEvent(s, h->comm_events[1], 0);
+    if (ce == cudaSuccess)
+      ce = e1;
+  }
+  if (rc == B2F_OK && ce == cudaSuccess)
+    rc = ghost_add(h, s);
+  if (rc == B2F_OK && ce == cudaSuccess && values_host) {
+    ce = cudaEventRecord(h->pipe_events[2 * nc], s);
+    if (ce == cudaSuccess)
+      ce = cudaStreamWaitEvent(h->pipe_d2h, h->pipe_events[2 * nc], 0);
+    for (int c = 0; c < nc && ce == cudaSuccess; ++c)
+      if (deferred(c))
+        ce = read_back(c);
+  }
+  cudaError_t e1 = cudaStreamSynchronize(h->pipe_h2d), e2 = cudaStreamSynchronize(h->comm_stream), e3 = cudaStreamSynchronize(s), e4 = cudaStreamSynchronize(h->pipe_d2h);
+  if (rc != B2F_OK)
+    return rc;
+  B2F_CUDA(ce);
+  B2F_CUDA(e1);
+  B2F_CUDA(e2);
+  B2F_CUDA(e3);
+  B2F_CUDA(e4);
+  return B2F_OK;
+}
+
 } // extern "C"

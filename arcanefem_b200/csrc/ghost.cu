@@ -513,7 +513,16 @@ int ghost_plan(b2f_context_s* h, void* comm_v, int rank, int world, const int32_
     B2F_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, kin, kout, iota.as<long long>(), P.recv_src.as<long long>(), P.total_recv, 0, 64, stream));
     B2F_CUDA(h->ws_tmp.alloc(tb));
     B2F_CUDA(cub::DeviceRadixSort::SortPairs(h->ws_tmp.p, tb, kin, kout, iota.as<long long>(), P.recv_src.as<long long>(), P.total_recv, 0, 64, stream));
+    long long ends[2] = { 0, -1 };
+    B2F_CUDA(cudaMemcpyAsync(&ends[0], P.recv_dst.as<long long>(), sizeof(long long), cudaMemcpyDeviceToHost, stream));
+    B2F_CUDA(cudaMemcpyAsync(&ends[1], P.recv_dst.as<long long>() + (P.total_recv - 1), sizeof(long long), cudaMemcpyDeviceToHost, stream));
     B2F_CUDA(cudaStreamSynchronize(stream)); // iota is released at the end of this scope
+    P.recv_val_lo = ends[0];
+    P.recv_val_hi = ends[1];
+  }
+  else {
+    P.recv_val_lo = 0;
+    P.recv_val_hi = -1;
   }
   unsigned long long nerr = 0;
   B2F_CUDA(cudaMemcpyAsync(&nerr, errs.p, sizeof(nerr), cudaMemcpyDeviceToHost, stream));

@@ -62,6 +62,7 @@ struct GhostPlan
   DevBuf recv_dst, recv_src; // recv_index in a stable sorted order + the position of each entry in recv_vals (fixed summation order)
   int64_t total_send = 0, total_recv = 0; // scalars
   int64_t send_row_lo = 0, send_row_hi = 0; // span of the local rows that are sent (ghost rows an assembled cell touches)
+  int64_t recv_val_lo = 0, recv_val_hi = -1; // span (inclusive) of the value indices that receive partial sums
 };
 
 } // namespace b2f

@@ -230,6 +230,15 @@ class GhostExchange:
         d = op.desc(False)
         check(self._lib.b2f_assemble_exchange(self._bsr._h, C.byref(d), self._comm, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
+    def assemble_and_run_host(self, op, coords_host, values_host=None):
+        """Host-buffer entry point of the multi-GPU step (b2f_assemble_exchange_host): pinned coordinates in, values out,
+        pipelined over row chunks with the exchange inside.  Synchronises before returning."""
+        import torch
+        d = op.desc(False)
+        vp = C.c_void_p(values_host.data_ptr()) if values_host is not None else None
+        check(self._lib.b2f_assemble_exchange_host(self._bsr._h, C.byref(d), self._comm, C.c_void_p(coords_host.data_ptr()), vp,
+                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
     def close(self):
         if self._comm and self._owns_comm:
             self._lib.b2f_nccl_comm_destroy(self._comm)

@@ -519,6 +519,8 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
         def e2e_step(read_back=True):
             if exchange is None and ls is None:
                 bsr.assembleBilinearHost(op, coords_host, values_host if read_back else None)  # C ABI b2f_assemble_host; synchronises before returning
+            elif exchange is not None and ls is None and not args.no_overlap:
+                exchange.assemble_and_run_host(op, coords_host, values_host if read_back else None)  # C ABI b2f_assemble_exchange_host
             else:
                 coords_dev.copy_(coords_host, non_blocking=True)
                 step()
@@ -548,6 +550,8 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
         out["e2e"] = {"value": round(own_nnz / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(coords_host.numel() * 8), "d2h_bytes_per_step": int(values_host.numel() * 8),
                       "ms_per_step": round(e2e_s * 1e3, 3),
                       "api": "b2f_assemble_host (pinned host coordinates in, values out, pipelined over row chunks)" if exchange is None and ls is None else
+                             "b2f_assemble_exchange_host (pinned host coordinates in, values out, row chunks with the ghost-row exchange inside), per rank, max over ranks"
+                             if exchange is not None and ls is None and not args.no_overlap else
                              "pinned coordinates H2D + the timed step + values D2H, per rank, max over ranks"}
         # the reference's own data flow keeps the matrix on the device for the Hypre solve (BASELINE.json north_star): same call
         # with the read-back skipped, coordinates in from pinned host memory, one 8-byte checksum of the values out (reported

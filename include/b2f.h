@@ -353,6 +353,13 @@ int b2f_ghost_exchange(b2f_handle h, void* nccl_comm, b2f_stream stream);
  * one launch, the additions happen in the same order).  Falls back to the sequence when the operator accumulates, the
  * default gather kernel is not in use, or the sent rows span more than a quarter of the local numbering. */
 int b2f_assemble_exchange(b2f_handle h, const b2f_operator* op, void* nccl_comm, b2f_stream stream);
+/* Host-buffer entry point of the multi-GPU step (b2f_assemble_host + b2f_assemble_exchange in one pipeline; what bench.py times as
+ * `e2e` at N > 1): coordinates go up as a growing prefix, row chunks are assembled as they land, the ghost rows travel as soon as
+ * the last of them is assembled, and every chunk's values go back to the host while the next chunk is assembled - chunks whose
+ * rows travel or receive partial sums after the sums have been added.  Same values as b2f_assemble_exchange followed by a copy.
+ * Pinned host memory recommended; values_host may be NULL.  Synchronises before returning.  Falls back to copy / step / copy
+ * when the default gather kernel is not in use, the operator accumulates, or the mesh has fewer than 65536 nodes. */
+int b2f_assemble_exchange_host(b2f_handle h, const b2f_operator* op, void* nccl_comm, const double* coords_host, double* values_host, b2f_stream stream);
 /* NCCL bootstrap helpers so a host without its own NCCL binding can create the communicator. */
 int b2f_nccl_unique_id(void* id128_out_host);
 int b2f_nccl_comm_init(const void* id128_host, int32_t rank, int32_t world, void** comm_out);

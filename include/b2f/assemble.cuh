@@ -606,6 +606,30 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
   return op.prepare_oriented(X, cell, odd);
 }
 
+// 1: the per-row loads of the prologue are issued with the tile extents (one DRAM round trip instead of three)
+#ifndef B2F_FAN_EARLY_ROW
+#define B2F_FAN_EARLY_ROW 0
+#endif
+#ifndef B2F_FAN_ADDR_AHEAD
+#define B2F_FAN_ADDR_AHEAD 0
+#endif
+#ifndef B2F_FAN_AHEAD2
+#define B2F_FAN_AHEAD2 0
+#endif
+// experiment: cache prefetch (no destination register) of the vertex that enters two steps ahead; 1 = L1, 2 = L2
+#ifndef B2F_FAN_PF2
+#define B2F_FAN_PF2 0
+#endif
+__device__ __forceinline__ void prefetch_ahead(const double* p)
+{
+#if B2F_FAN_PF2 == 1
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 2));
+#elif B2F_FAN_PF2 == 2
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 2));
+#endif
+}
 #ifndef B2F_FAN_ASM_SMEM
 #define B2F_FAN_ASM_SMEM 1
 #endif
@@ -925,6 +949,23 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   const long long row0 = (tile + A.first_tile) * C::ROWS;
   const long long left = A.nb_node - row0;
   const int nrows = left < C::ROWS ? (int)left : C::ROWS;
+#if B2F_FAN_EARLY_ROW
+  // every per-row load that depends on the row id alone is issued here, together with the tile extents: one DRAM round trip in
+  // front of the walk instead of three (extents -> walk length -> row extents and coordinates)
+  const long long row = row0 + t; // internal row in the reorder mode
+  int32_t e_rb = 0, e_rbn = 0, e_qb = 0, e_qbn = 0;
+  double X0[3] = { 0.0, 0.0, 0.0 };
+  uint8_t e_own = 1;
+  if (t < nrows) {
+    e_rb = __ldg(A.row_index + row);
+    e_rbn = __ldg(A.row_index + row + 1);
+    e_qb = __ldg(A.fan_ptr + row);
+    e_qbn = __ldg(A.fan_ptr + row + 1);
+    load_xyz(A.coords, (int32_t)row, X0);
+    if (!PERM && A.node_is_own != nullptr)
+      e_own = A.node_is_own[row];
+  }
+#endif
   const int32_t vbeg = __ldg(A.row_index + row0), vend = __ldg(A.row_index + row0 + nrows);
   const int32_t abeg = __ldg(A.fan_ptr + row0), aend = __ldg(A.fan_ptr + row0 + nrows);
   const int32_t vbeg_al = vbeg & ~3, abeg_al = abeg & ~3; // 16-byte aligned sources
@@ -969,16 +1010,25 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   }
   const int nval = (vend - vbeg) * BS2;
   // per-row setup overlaps the bulk copies
+#if !B2F_FAN_EARLY_ROW
   const long long row = row0 + t; // internal row in the reorder mode
+#endif
   constexpr bool permuted = PERM;
   long long out_row = row; // the caller's row: ownership, right-hand side, destination of the values
   int32_t rb = 0, qb = 0;
   int k = 0, nstep = 0;
   long long out_base = 0; // first value of the row in the caller's value array (reorder mode)
+#if !B2F_FAN_EARLY_ROW
   double X0[3] = { 0.0, 0.0, 0.0 };
+#endif
   if (t < nrows) {
+#if B2F_FAN_EARLY_ROW
+    rb = e_rb;
+    k = e_rbn - rb;
+#else
     rb = __ldg(A.row_index + row);
     k = __ldg(A.row_index + row + 1) - rb;
+#endif
     if (permuted) {
       out_row = __ldg(A.row_perm + row);
       out_base = (long long)__ldg(A.out_row_index + out_row) * BS2;
@@ -1005,10 +1055,16 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       acc_s[q] = 0.0;
   }
   if (t < nrows) {
+#if B2F_FAN_EARLY_ROW
+    const bool own = PERM ? ((A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0)) : (e_own != 0);
+    qb = e_qb;
+    nstep = own ? (e_qbn - qb) : 0;
+#else
     const bool own = (A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0);
     qb = __ldg(A.fan_ptr + row);
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
     load_xyz(A.coords, (int32_t)row, X0);
+#endif
   }
 #if B2F_FAN_TILE_AHEAD > 0
   // Streaming data of the tile that will start when this one retires (about one wave of CTAs ahead) is pulled into L2
@@ -1222,9 +1278,24 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
+#if B2F_FAN_AHEAD2
+    // experiment: coordinates prefetched TWO steps ahead, two register sets alternating with the two halves of the loop
+    double Xn[3], XnB[3];
+    uint32_t w = st[0], wB = nstep > 1 ? st[1] : 0u;
+    load_xyz(A.coords, cols[w & 1023u], Xn);
+    if (nstep > 1)
+      load_xyz(A.coords, cols[wB & 1023u], XnB);
+#else
     double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
     uint32_t w = st[0];
     load_xyz(A.coords, cols[w & 1023u], Xn);
+#if B2F_FAN_ADDR_AHEAD
+    // the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
+    // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago
+    uint32_t w1 = nstep > 1 ? st[1] : 0u, w2 = nstep > 2 ? st[2] : 0u;
+    int32_t cn = nstep > 1 ? cols[w1 & 1023u] : 0;
+#endif
+#endif
     int p = 0;
     bool newest_is_Q = false;
     // The prefetched coordinates are consumed (edge vector) BEFORE the next prefetch is issued into the same registers:
@@ -1268,22 +1339,70 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       // step p: P enters (Q is the newest)
       uint32_t wc = w;
       enter(eP);
+#if B2F_FAN_AHEAD2
+      if (p + 2 < nstep) {
+        w = st[p + 2];
+        load_xyz(A.coords, cols[w & 1023u], Xn);
+      }
+#else
+#if B2F_FAN_ADDR_AHEAD
+      if (p + 1 < nstep)
+        load_xyz(A.coords, cn, Xn);
+      if (p + 2 < nstep)
+        cn = cols[w2 & 1023u];
+      w = w1;
+      w1 = w2;
+      if (p + 3 < nstep)
+        w2 = st[p + 3];
+#else
       if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
+#endif
+#if B2F_FAN_PF2
+      if (p + 2 < nstep)
+        prefetch_ahead(A.coords + 3ll * cols[st[p + 2] & 1023u]);
+#endif
+#endif
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
         break;
       // step p: Q enters (P is the newest)
+#if B2F_FAN_AHEAD2
+      wc = wB;
+#pragma unroll
+      for (int d = 0; d < 3; ++d)
+        eQ[d] = (NV == 4) ? XnB[d] - X0[d] : XnB[d];
+      if (p + 2 < nstep) {
+        wB = st[p + 2];
+        load_xyz(A.coords, cols[wB & 1023u], XnB);
+      }
+#else
       wc = w;
       enter(eQ);
+#if B2F_FAN_ADDR_AHEAD
+      if (p + 1 < nstep)
+        load_xyz(A.coords, cn, Xn);
+      if (p + 2 < nstep)
+        cn = cols[w2 & 1023u];
+      w = w1;
+      w1 = w2;
+      if (p + 3 < nstep)
+        w2 = st[p + 3];
+#else
       if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
         load_xyz(A.coords, cols[w & 1023u], Xn);
       }
+#endif
+#if B2F_FAN_PF2
+      if (p + 2 < nstep)
+        prefetch_ahead(A.coords + 3ll * cols[st[p + 2] & 1023u]);
+#endif
+#endif
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;

@@ -59,7 +59,8 @@ def _worker(rank, world, port, case, q):
         okw = op_params(kind)
         op = fem.Operator.laplace() if bs == 1 else fem.Operator.elasticity(21.0e5, 0.28)
         bsr = fem.BSRFormat(bs)
-        bsr.initialize(Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"]), use_csr, assembly_variant=variant)
+        mesh_obj = Mesh.from_numpy(3, cells, coords, cell_is_own=part["cell_is_own"])
+        bsr.initialize(mesh_obj, use_csr, assembly_variant=variant)
         bsr.computeSparsity()
         assert bsr.stats()["sparsity_by_lists"] == 1, "the exchange mode builds its pattern from the node->cell lists too"
         ex = mg.GhostExchange(bsr, rank, world, part["node_owner"], part["node_gid"])
@@ -80,6 +81,22 @@ def _worker(rank, world, port, case, q):
             assert torch.equal(mat.values(), sequential), "the exchange is not bitwise repeatable"
         else:
             torch.testing.assert_close(mat.values(), sequential, rtol=1e-12, atol=1e-14)
+        if case.get("host_entry"):
+            # b2f_assemble_exchange_host: pinned coordinates in, values out, row chunks with the exchange inside (pipelined from
+            # 65536 local nodes on): the host copy and the device matrix must equal the device path bit for bit
+            coords_host = torch.as_tensor(coords).pin_memory()
+            values_host = torch.full((mat.nbNz(),), float("nan"), dtype=torch.float64).pin_memory()
+            bsr.setCoords(torch.zeros_like(mesh_obj.coords))  # the entry point must take its coordinates from the host array
+            for _ in range(2):
+                ex.assemble_and_run_host(op, coords_host, values_host)
+            bsr.setCoords(mesh_obj.coords)
+            if variant == 3:
+                assert torch.equal(values_host, sequential.cpu()), "b2f_assemble_exchange_host: host values differ from the device path"
+                assert torch.equal(mat.values(), sequential), "b2f_assemble_exchange_host: device values differ from the device path"
+            else:
+                torch.testing.assert_close(values_host, sequential.cpu(), rtol=1e-12, atol=1e-14)
+            ex.assemble_and_run_host(op, coords_host, None)  # no read-back
+            assert torch.equal(mat.values(), sequential) or variant != 3
         ri, co, vals = mat.rowIndexWithEnd().cpu().numpy(), mat.columns().cpu().numpy(), mat.values().cpu().numpy()
         gri, gco = orc.build_pattern(gcells, gcoords.shape[0])
         gvals, _ = orc.assemble(gcells, gcoords, gri, gco, bs=bs, per_block=True, **okw)
@@ -149,3 +166,11 @@ def test_block_sizes_and_layouts_through_the_exchange(world, bs, use_csr):
         pytest.skip("BS = 1: both layouts coincide")
     case = dict(n_hex=8, variant=3, bs=bs, use_csr=use_csr, decomposition="slab" if world == 2 else "block")
     _run(world, case)
+
+
+@pytest.mark.parametrize("world,n_hex,decomposition", [(2, 6, "slab"), (2, 44, "slab"), (4, 64, "block")])
+def test_host_entry_point_with_the_exchange_inside(world, n_hex, decomposition):
+    """b2f_assemble_exchange_host.  n_hex = 6: the copy / step / copy fallback.  44: 45^3 = 91 k nodes per rank, the chunk
+    pipeline; slabs keep the travelling rows in the first chunk and the receiving rows in the last.  64 in 2 x 2 blocks: 70 k
+    nodes per rank with ghost and receiving rows spread over the whole numbering (most chunks wait for the exchange)."""
+    _run(world, dict(n_hex=n_hex, variant=3, bs=1, use_csr=True, decomposition=decomposition, host_entry=True))

@@ -3,11 +3,11 @@
 # N-rank parity tests first, then the strong line (one 406^3 cube over NP ranks, the weak run nested) and the reference arm.
 TAG=${1:-r02}; NP=${2:-8}
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_multirank.py -x -q ${SCALE_K:+-k "$SCALE_K"} > gpurun_out/pytest_multirank_${TAG}_${NP}gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_multirank_${TAG}_${NP}gpu.log
+timeout ${SCALE_PYTEST_TIMEOUT:-900} python -m pytest tests/test_gpu_multirank.py -x -q ${SCALE_K:+-k "$SCALE_K"} > gpurun_out/pytest_multirank_${TAG}_${NP}gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_multirank_${TAG}_${NP}gpu.log
 tail -4 gpurun_out/pytest_multirank_${TAG}_${NP}gpu.log
 for n in ${SCALE_NS:-2 4 8}; do
   [ $n -le $NP ] || continue
-  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29520 + n)) bench.py --gpus $n --steps 10 --warmup 3 \
+  timeout ${SCALE_BENCH_TIMEOUT:-900} python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29520 + n)) bench.py --gpus $n --steps 10 --warmup 3 \
     > gpurun_out/scale_${TAG}_${n}gpu.json 2> gpurun_out/scale_${TAG}_${n}gpu.err; echo "bench N=$n rc=$?"; tail -2 gpurun_out/scale_${TAG}_${n}gpu.err
   python -c "
 import json
