@@ -72,12 +72,54 @@ __device__ __forceinline__ void load_cell_nodes(const int32_t* __restrict__ cell
   }
 }
 
+#ifndef B2F_FAN_SOA
+#define B2F_FAN_SOA 0
+#endif
 __device__ __forceinline__ void load_xyz(const double* __restrict__ coords, int32_t node, double (&x)[3])
 {
   const double* p = coords + 3ll * node;
   x[0] = __ldg(p);
   x[1] = __ldg(p + 1);
   x[2] = __ldg(p + 2);
+}
+
+// xyz[first .. first + count) of the interleaved array -> x / y / z arrays of `stride` doubles.  256 nodes per CTA: 768 doubles are
+// read coalesced into shared memory and leave it with a pitch of 3 (odd: no bank conflicts).
+__global__ void __launch_bounds__(256) k_coords_to_soa(const double* __restrict__ xyz, long long first, long long count, long long stride, double* __restrict__ soa)
+{
+  __shared__ double tile[768];
+  const long long n0 = (long long)blockIdx.x * 256;
+  const int n = count - n0 < 256 ? (int)(count - n0) : 256;
+  const double* src = xyz + 3 * (first + n0);
+  for (int q = threadIdx.x; q < 3 * n; q += 256)
+    tile[q] = __ldg(src + q);
+  __syncthreads();
+  if ((int)threadIdx.x < n) {
+    double* dst = soa + first + n0 + threadIdx.x;
+    dst[0] = tile[3 * threadIdx.x];
+    dst[stride] = tile[3 * threadIdx.x + 1];
+    dst[2 * stride] = tile[3 * threadIdx.x + 2];
+  }
+}
+
+// Coordinate source of the fan kernel: the caller's interleaved array (stride 0) or the library's own copy with x, y and z in
+// three arrays of `stride` doubles (B2F_FAN_SOA).  A warp that gathers 32 neighbouring nodes touches 6-7 cache lines per 8-byte
+// load in the interleaved array (24-byte pitch) and 2 in the split one; the L1 data pipe is the unit this kernel loads most.
+struct FanCoords
+{
+  const double* p;
+  long long stride;
+};
+__device__ __forceinline__ void load_xyz(const FanCoords& c, int32_t node, double (&x)[3])
+{
+#if B2F_FAN_SOA
+  const double* q = c.p + node;
+  x[0] = __ldg(q);
+  x[1] = __ldg(q + c.stride);
+  x[2] = __ldg(q + 2 * c.stride);
+#else
+  load_xyz(c.p, node, x);
+#endif
 }
 
 // Even permutation bringing local vertex a to position 0: tets m[k] = n[a ^ k] (double transpositions),
@@ -391,6 +433,20 @@ __device__ __forceinline__ void tma_load_1d_stream(void* dst_smem, const void* s
   tma_load_1d(dst_smem, src_global, bytes, bar);
 #endif
 }
+// 1: the finished slab of a tile leaves shared memory as ONE bulk copy of the async proxy (cp.async.bulk.global.shared::cta) instead of
+// LDS + STG.128 of every thread: the write-out then costs no wavefronts of the L1 data pipe (the unit this kernel loads most)
+#ifndef B2F_FAN_BULK_STORE
+#define B2F_FAN_BULK_STORE 1
+#endif
+__device__ __forceinline__ void tma_store_1d(void* dst_global, const void* src_smem, uint32_t bytes)
+{
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(__cvta_generic_to_global(dst_global)), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read()
+{
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
 #ifndef B2F_FAN_PREFETCH
 #define B2F_FAN_PREFETCH 0
 #endif
@@ -608,28 +664,11 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 
 // 1: the per-row loads of the prologue are issued with the tile extents (one DRAM round trip instead of three)
 #ifndef B2F_FAN_EARLY_ROW
-#define B2F_FAN_EARLY_ROW 0
+#define B2F_FAN_EARLY_ROW 1
 #endif
 #ifndef B2F_FAN_ADDR_AHEAD
-#define B2F_FAN_ADDR_AHEAD 0
+#define B2F_FAN_ADDR_AHEAD 1
 #endif
-#ifndef B2F_FAN_AHEAD2
-#define B2F_FAN_AHEAD2 0
-#endif
-// experiment: cache prefetch (no destination register) of the vertex that enters two steps ahead; 1 = L1, 2 = L2
-#ifndef B2F_FAN_PF2
-#define B2F_FAN_PF2 0
-#endif
-__device__ __forceinline__ void prefetch_ahead(const double* p)
-{
-#if B2F_FAN_PF2 == 1
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 2));
-#elif B2F_FAN_PF2 == 2
-  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-  asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 2));
-#endif
-}
 #ifndef B2F_FAN_ASM_SMEM
 #define B2F_FAN_ASM_SMEM 1
 #endif
@@ -717,7 +756,7 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
 template <class Op, bool PER_BLOCK, bool SKIP_DIAG, bool SRC, class AccT, class ColsT>
-__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
+__device__ __forceinline__ void fan_step(const Op& op, const FanCoords& coords, const double (&X0)[3], AccT acc, ColsT cols,
                                          int k, uint32_t wc, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure)
@@ -924,10 +963,21 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   // the outer products from zero, the diagonal block is minus the sum of the row's other blocks (gradients of a cell sum
   // to zero), the map runs once per stored block after the walk, and accumulate mode adds the old values at the store.
   constexpr bool POST = Op::LINEAR_POST;
+#if B2F_FAN_SOA
+  const FanCoords FC{ A.coords_soa, A.soa_stride };
+#else
+  const FanCoords FC{ A.coords, 0 };
+#endif
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
+#if B2F_FAN_BULK_STORE
+  double* const acc_base = reinterpret_cast<double*>(b2f_smem + 16);
+  double* acc_s = acc_base; // moved back by one element for tiles whose first value sits at an odd index (below)
+  int32_t* cols_s = reinterpret_cast<int32_t*>(acc_base + (size_t)acc_blocks * BS2);
+#else
   double* acc_s = reinterpret_cast<double*>(b2f_smem + 16);
   int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)acc_blocks * BS2);
+#endif
   uint32_t* steps_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
 
   const int t = threadIdx.x;
@@ -961,7 +1011,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     e_rbn = __ldg(A.row_index + row + 1);
     e_qb = __ldg(A.fan_ptr + row);
     e_qbn = __ldg(A.fan_ptr + row + 1);
-    load_xyz(A.coords, (int32_t)row, X0);
+    load_xyz(FC, (int32_t)row, X0);
     if (!PERM && A.node_is_own != nullptr)
       e_own = A.node_is_own[row];
   }
@@ -1009,6 +1059,11 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       tma_load_1d_stream(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
   }
   const int nval = (vend - vbeg) * BS2;
+#if B2F_FAN_BULK_STORE
+  // the slab takes the 16-byte phase of its destination (values is 16-byte aligned at element 0; bytes 8..15 of the dynamic
+  // shared memory are spare): element i of the slab and value vbeg * BS2 + i then sit at the same offset modulo 16
+  acc_s = acc_base - (int)(((long long)vbeg * BS2) & 1);
+#endif
   // per-row setup overlaps the bulk copies
 #if !B2F_FAN_EARLY_ROW
   const long long row = row0 + t; // internal row in the reorder mode
@@ -1063,7 +1118,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     const bool own = (A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0);
     qb = __ldg(A.fan_ptr + row);
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
-    load_xyz(A.coords, (int32_t)row, X0);
+    load_xyz(FC, (int32_t)row, X0);
 #endif
   }
 #if B2F_FAN_TILE_AHEAD > 0
@@ -1121,7 +1176,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       int sl[3] = { 0, 0, 0 };
       double Xn[3];
       uint32_t w = st[0], wc = 0;
-      load_xyz(A.coords, cols[w & 1023u], Xn);
+      load_xyz(FC, cols[w & 1023u], Xn);
       double cv = 0.0, cvn = 0.0;
       uint32_t cidn = 0;
       if constexpr (Op::NEEDS_CELL) {
@@ -1141,7 +1196,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         for (int d = 0; d < 3; ++d)
           e[F][d] = Xn[d] - X0[d];
         if (more)
-          load_xyz(A.coords, cols[w & 1023u], Xn);
+          load_xyz(FC, cols[w & 1023u], Xn);
         sl[F] = (int)(wc & 1023u);
         load_block<BS, PER_BLOCK>(acc, k, sl[F], av[F]);
         const bool odd = (wc >> 13) & 1u;
@@ -1231,9 +1286,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
           sl[1] = (int)(wc & 1023u);
           sl[2] = (int)((wc >> 10) & 1023u);
           double XB[3];
-          load_xyz(A.coords, cols[sl[2]], XB);
+          load_xyz(FC, cols[sl[2]], XB);
           if (more)
-            load_xyz(A.coords, cols[w & 1023u], Xn);
+            load_xyz(FC, cols[w & 1023u], Xn);
           load_block<BS, PER_BLOCK>(acc, k, sl[1], av[1]);
           load_block<BS, PER_BLOCK>(acc, k, sl[2], av[2]);
 #pragma unroll
@@ -1278,24 +1333,20 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // two register sets P, Q alternate between "newest window vertex" and "entering vertex"; slot 0 (the diagonal) = empty
     double eP[3], eQ[3], eO[3], m[3], accP[BS2], accQ[BS2], accO[BS2];
     int sP = 0, sQ = 0, sO = 0;
-#if B2F_FAN_AHEAD2
-    // experiment: coordinates prefetched TWO steps ahead, two register sets alternating with the two halves of the loop
-    double Xn[3], XnB[3];
-    uint32_t w = st[0], wB = nstep > 1 ? st[1] : 0u;
-    load_xyz(A.coords, cols[w & 1023u], Xn);
-    if (nstep > 1)
-      load_xyz(A.coords, cols[wB & 1023u], XnB);
-#else
     double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
     uint32_t w = st[0];
-    load_xyz(A.coords, cols[w & 1023u], Xn);
-#if B2F_FAN_ADDR_AHEAD
-    // the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
-    // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago
-    uint32_t w1 = nstep > 1 ? st[1] : 0u, w2 = nstep > 2 ? st[2] : 0u;
-    int32_t cn = nstep > 1 ? cols[w1 & 1023u] : 0;
-#endif
-#endif
+    load_xyz(FC, cols[w & 1023u], Xn);
+    // AA: the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
+    // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago.  Two
+    // registers; the instantiations that have none to spare (reorder mode, fused source term, per-cell data) keep the short chain.
+    constexpr bool AA = B2F_FAN_ADDR_AHEAD && !PERM && !SRC && !Op::NEEDS_CELL;
+    uint32_t w1 = 0u, w2 = 0u;
+    int32_t cn = 0;
+    if constexpr (AA) {
+      w1 = nstep > 1 ? st[1] : 0u;
+      w2 = nstep > 2 ? st[2] : 0u;
+      cn = nstep > 1 ? cols[w1 & 1023u] : 0;
+    }
     int p = 0;
     bool newest_is_Q = false;
     // The prefetched coordinates are consumed (edge vector) BEFORE the next prefetch is issued into the same registers:
@@ -1339,71 +1390,43 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       // step p: P enters (Q is the newest)
       uint32_t wc = w;
       enter(eP);
-#if B2F_FAN_AHEAD2
-      if (p + 2 < nstep) {
-        w = st[p + 2];
-        load_xyz(A.coords, cols[w & 1023u], Xn);
+      if constexpr (AA) {
+        if (p + 1 < nstep)
+          load_xyz(FC, cn, Xn);
+        if (p + 2 < nstep)
+          cn = cols[w2 & 1023u];
+        w = w1;
+        w1 = w2;
+        if (p + 3 < nstep)
+          w2 = st[p + 3];
       }
-#else
-#if B2F_FAN_ADDR_AHEAD
-      if (p + 1 < nstep)
-        load_xyz(A.coords, cn, Xn);
-      if (p + 2 < nstep)
-        cn = cols[w2 & 1023u];
-      w = w1;
-      w1 = w2;
-      if (p + 3 < nstep)
-        w2 = st[p + 3];
-#else
-      if (p + 1 < nstep) {
+      else if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
+        load_xyz(FC, cols[w & 1023u], Xn);
       }
-#endif
-#if B2F_FAN_PF2
-      if (p + 2 < nstep)
-        prefetch_ahead(A.coords + 3ll * cols[st[p + 2] & 1023u]);
-#endif
-#endif
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, FC, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
         break;
       // step p: Q enters (P is the newest)
-#if B2F_FAN_AHEAD2
-      wc = wB;
-#pragma unroll
-      for (int d = 0; d < 3; ++d)
-        eQ[d] = (NV == 4) ? XnB[d] - X0[d] : XnB[d];
-      if (p + 2 < nstep) {
-        wB = st[p + 2];
-        load_xyz(A.coords, cols[wB & 1023u], XnB);
-      }
-#else
       wc = w;
       enter(eQ);
-#if B2F_FAN_ADDR_AHEAD
-      if (p + 1 < nstep)
-        load_xyz(A.coords, cn, Xn);
-      if (p + 2 < nstep)
-        cn = cols[w2 & 1023u];
-      w = w1;
-      w1 = w2;
-      if (p + 3 < nstep)
-        w2 = st[p + 3];
-#else
-      if (p + 1 < nstep) {
-        B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
+      if constexpr (AA) {
+        if (p + 1 < nstep)
+          load_xyz(FC, cn, Xn);
+        if (p + 2 < nstep)
+          cn = cols[w2 & 1023u];
+        w = w1;
+        w1 = w2;
+        if (p + 3 < nstep)
+          w2 = st[p + 3];
       }
-#endif
-#if B2F_FAN_PF2
-      if (p + 2 < nstep)
-        prefetch_ahead(A.coords + 3ll * cols[st[p + 2] & 1023u]);
-#endif
-#endif
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
+      else if (p + 1 < nstep) {
+        B2F_NEXT_WORD(p)
+        load_xyz(FC, cols[w & 1023u], Xn);
+      }
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, FC, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
@@ -1495,7 +1518,18 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       dst[q] = make_double2(o.x + acc_s[head + 2 * q], o.y + acc_s[head + 2 * q + 1]);
     }
   }
+#if B2F_FAN_BULK_STORE
   else {
+    // generic-proxy writes of the walk (collected by the __syncthreads above) -> async-proxy read of the bulk copy
+    if (t == 0 && nvec > 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      tma_store_1d(dst, acc_s + head, (uint32_t)nvec * 16u);
+    }
+  }
+  if (false) {
+#else
+  else {
+#endif
     for (int q = t; q < nvec; q += C::ROWS) {
 #if B2F_FAN_STREAM >= 1
       __stcs(dst + q, make_double2(acc_s[head + 2 * q], acc_s[head + 2 * q + 1]));
@@ -1507,6 +1541,10 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   const int tail = head + 2 * nvec;
   if (t == 0 && tail < nval)
     A.values[base + tail] = acc_s[tail] + (add_old ? A.values[base + tail] : 0.0);
+#if B2F_FAN_BULK_STORE
+  if (t == 0 && !add_old && nvec > 0)
+    tma_store_wait_read(); // the slab must stay in place until the copy has read it (the CTA's shared memory is released at exit)
+#endif
 #if B2F_FAN_PERSIST
   __syncthreads(); // the next tile of a persistent CTA clears the accumulators and overwrites the staging areas
   } // tiles of this CTA
@@ -1597,6 +1635,23 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
         F.coords = A.r_coords;
         F.slot_map = A.r_slot_map;
       }
+#if B2F_FAN_SOA == 2
+      // EXPERIMENT (tools/build_variant.sh -DB2F_FAN_SOA=2): the split copy is made here, before every launch, into a buffer
+      // owned by the launcher - the product form takes it from the handle (AssembleArgs::coords_soa)
+      if (F.coords_soa == nullptr) {
+        static double* soa = nullptr;
+        static long long cap = 0;
+        if (cap < F.nb_node) {
+          cudaFree(soa);
+          if (cudaMalloc(&soa, sizeof(double) * 3 * (size_t)F.nb_node) != cudaSuccess)
+            return cudaErrorMemoryAllocation;
+          cap = F.nb_node;
+        }
+        k_coords_to_soa<<<(unsigned)((F.nb_node + 255) / 256), 256, 0, stream>>>(F.coords, 0, F.nb_node, F.nb_node, soa);
+        F.coords_soa = soa;
+        F.soa_stride = F.nb_node;
+      }
+#endif
 #if B2F_FAN_PERSIST
       // one CTA per resident slot (B2F_FAN_PERSIST = waves of such CTAs; 1 = exactly the resident set)
       static int sm_count = 0;
