@@ -12,6 +12,12 @@ inline int run(b2f_context_s* h, const Op& op, int accumulate, cudaStream_t stre
     AssembleArgs A;
     fill_assemble_args(h, &A);
     A.accumulate = accumulate;
+    // first-visit marks of the plan: usable when the slab starts from zero (overwrite mode) and every cell around an own row is
+    // assembled (in the cell_is_own exchange mode a slot that only ghost cells touch is never stored: the slab is cleared instead)
+#ifndef B2F_FAN_FIRST
+#define B2F_FAN_FIRST 1 /* 0: ignore the marks (A/B builds) */
+#endif
+    A.fan_first_mask = (B2F_FAN_FIRST && h->fan_first && !h->fan_lockstep && !accumulate && h->mesh.cell_is_own == nullptr) ? 8192u : 0u;
     int variant = h->variant;
     if (variant == B2F_ASM_DEFAULT)
       variant = B2F_ASM_NODE_GATHER;

@@ -104,6 +104,7 @@ struct b2f_context_s
   b2f::DevBuf coords_stage; // b2f_assemble_host
   // b2f_assemble_host pipeline: row chunks, the highest node id each chunk reads, value offsets at the chunk boundaries
   int64_t range_first_row = 0, range_rows = -1; // >= 0 while a chunk of the pipeline is being launched
+  bool fan_first = false; // the step words carry the first-visit marks (k_fan_first_flags)
   bool range_keep_counters = false; // a later range of the same assembly: the counters are not cleared again
   cudaStream_t comm_stream = nullptr; // b2f_assemble_exchange: ghost rows travel here while the other rows are assembled
   cudaEvent_t comm_events[2] = { nullptr, nullptr };

@@ -764,6 +764,44 @@ __global__ void __launch_bounds__(128) k_fan_pivot_hint(const int32_t* __restric
   }
 }
 
+// First visits.  A step that brings a vertex into the window loads its accumulator from the tile's shared-memory slab; the first
+// time a slot is loaded in its row the value is the initial zero.  The plan marks those loads (bit 13 of an emit word, bits 20 / 21
+// of a START word for its two slots), so the kernel starts the register from zero instead, and - every slot of a walked row
+// being stored at least once - does not have to clear the slab first: two passes less through the L1 data pipe, the unit the
+// fan kernel loads most.  One thread per row, 1024-slot bitmap in local memory.
+__global__ void __launch_bounds__(128) k_fan_first_flags(const int32_t* __restrict__ fan_ptr, long long nb_node, uint32_t* __restrict__ steps)
+{
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= nb_node)
+    return;
+  const int32_t qb = fan_ptr[row];
+  const int n = fan_ptr[row + 1] - qb;
+  uint32_t seen[32];
+  for (int i = 0; i < 32; ++i)
+    seen[i] = 0u;
+  auto first = [&](uint32_t slot) {
+    const uint32_t bit = 1u << (slot & 31u);
+    const bool f = (seen[slot >> 5] & bit) == 0u;
+    seen[slot >> 5] |= bit;
+    return f;
+  };
+  for (int p = 0; p < n; ++p) {
+    uint32_t w = steps[qb + p];
+    const uint32_t before = w;
+    if (w & 0x80000000u) {
+      if (first(w & 1023u))
+        w |= 1u << 20;
+      const uint32_t so = (w >> 10) & 1023u; // 0 for triangles (slot 0 is the diagonal, never a window vertex)
+      if (so != 0u && first(so))
+        w |= 1u << 21;
+    }
+    else if (first(w & 1023u))
+      w |= 1u << 13;
+    if (w != before)
+      steps[qb + p] = w;
+  }
+}
+
 namespace {
   // Cells with a node id outside [0, nb_node): counted before anything indexes with them.
   __global__ void __launch_bounds__(256) k_validate_cells(const int32_t* __restrict__ cell_node, long long n_entries, long long nb_node, unsigned long long* __restrict__ counters)
@@ -1148,6 +1186,12 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
       k_fan_pivot_hint<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
       B2F_CUDA(cudaGetLastError());
     }
+    h->fan_first = false;
+    if (nb_step > 0 && h->opt.fan_mode != B2F_FAN_LOCKSTEP) {
+      k_fan_first_flags<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
+      B2F_CUDA(cudaGetLastError());
+      h->fan_first = true;
+    }
     tile_ptr = h->fan_ptr.as<int32_t>();
     // lockstep form of the step words, on request only (B2F_FAN_LOCKSTEP): measured slower than the select walk even
     // where the rows of a warp walk in step (N=203 Kuhn cube: 1.07 bodies per warp step, 1.08 ms against 0.98 ms) -
@@ -1492,6 +1536,7 @@ int reorder_plan(b2f_context_s* h, cudaStream_t stream)
   std::swap(h->fan_steps, in.fan_steps);
   std::swap(h->fan_cell, in.fan_cell);
   h->nb_fan_step = in.nb_fan_step;
+  h->fan_first = in.fan_first;
   for (int q = 0; q < 6; ++q)
     h->tile_extents[q] = in.tile_extents[q];
   e = h->r_slot_map.alloc(sizeof(uint16_t) * (size_t)(h->nb_col + 8));

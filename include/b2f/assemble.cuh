@@ -72,54 +72,12 @@ __device__ __forceinline__ void load_cell_nodes(const int32_t* __restrict__ cell
   }
 }
 
-#ifndef B2F_FAN_SOA
-#define B2F_FAN_SOA 0
-#endif
 __device__ __forceinline__ void load_xyz(const double* __restrict__ coords, int32_t node, double (&x)[3])
 {
   const double* p = coords + 3ll * node;
   x[0] = __ldg(p);
   x[1] = __ldg(p + 1);
   x[2] = __ldg(p + 2);
-}
-
-// xyz[first .. first + count) of the interleaved array -> x / y / z arrays of `stride` doubles.  256 nodes per CTA: 768 doubles are
-// read coalesced into shared memory and leave it with a pitch of 3 (odd: no bank conflicts).
-__global__ void __launch_bounds__(256) k_coords_to_soa(const double* __restrict__ xyz, long long first, long long count, long long stride, double* __restrict__ soa)
-{
-  __shared__ double tile[768];
-  const long long n0 = (long long)blockIdx.x * 256;
-  const int n = count - n0 < 256 ? (int)(count - n0) : 256;
-  const double* src = xyz + 3 * (first + n0);
-  for (int q = threadIdx.x; q < 3 * n; q += 256)
-    tile[q] = __ldg(src + q);
-  __syncthreads();
-  if ((int)threadIdx.x < n) {
-    double* dst = soa + first + n0 + threadIdx.x;
-    dst[0] = tile[3 * threadIdx.x];
-    dst[stride] = tile[3 * threadIdx.x + 1];
-    dst[2 * stride] = tile[3 * threadIdx.x + 2];
-  }
-}
-
-// Coordinate source of the fan kernel: the caller's interleaved array (stride 0) or the library's own copy with x, y and z in
-// three arrays of `stride` doubles (B2F_FAN_SOA).  A warp that gathers 32 neighbouring nodes touches 6-7 cache lines per 8-byte
-// load in the interleaved array (24-byte pitch) and 2 in the split one; the L1 data pipe is the unit this kernel loads most.
-struct FanCoords
-{
-  const double* p;
-  long long stride;
-};
-__device__ __forceinline__ void load_xyz(const FanCoords& c, int32_t node, double (&x)[3])
-{
-#if B2F_FAN_SOA
-  const double* q = c.p + node;
-  x[0] = __ldg(q);
-  x[1] = __ldg(q + c.stride);
-  x[2] = __ldg(q + 2 * c.stride);
-#else
-  load_xyz(c.p, node, x);
-#endif
 }
 
 // Even permutation bringing local vertex a to position 0: tets m[k] = n[a ^ k] (double transpositions),
@@ -756,8 +714,8 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
 template <class Op, bool PER_BLOCK, bool SKIP_DIAG, bool SRC, class AccT, class ColsT>
-__device__ __forceinline__ void fan_step(const Op& op, const FanCoords& coords, const double (&X0)[3], AccT acc, ColsT cols,
-                                         int k, uint32_t wc, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
+__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
+                                         int k, uint32_t wc, uint32_t first_mask, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure)
 {
@@ -771,10 +729,23 @@ __device__ __forceinline__ void fan_step(const Op& op, const FanCoords& coords, 
       if (sO)
         store_block<BS, PER_BLOCK>(acc, k, sO, accO);
     }
-    load_block<BS, PER_BLOCK>(acc, k, sC, accC);
+    // first_mask = 8192 (bit 13) when the plan's first-visit marks apply: START words carry them in bits 20 / 21 (= mask << 7, << 8)
+    if (wc & (first_mask << 7)) {
+#pragma unroll
+      for (int e = 0; e < BS2; ++e)
+        accC[e] = 0.0;
+    }
+    else
+      load_block<BS, PER_BLOCK>(acc, k, sC, accC);
     if constexpr (NV == 4) {
       sO = (int)((wc >> 10) & 1023u);
-      load_block<BS, PER_BLOCK>(acc, k, sO, accO);
+      if (wc & (first_mask << 8)) {
+#pragma unroll
+        for (int e = 0; e < BS2; ++e)
+          accO[e] = 0.0;
+      }
+      else
+        load_block<BS, PER_BLOCK>(acc, k, sO, accO);
       double XB[3];
       load_xyz(coords, cols[sO], XB);
 #pragma unroll
@@ -787,7 +758,13 @@ __device__ __forceinline__ void fan_step(const Op& op, const FanCoords& coords, 
     return;
   }
   const bool odd = (wc >> 11) & 1u;
-  load_block<BS, PER_BLOCK>(acc, k, sC, accC);
+  if (wc & first_mask) { // first visit of the slot in this row: the accumulator starts from zero, the slab was not cleared
+#pragma unroll
+    for (int e = 0; e < BS2; ++e)
+      accC[e] = 0.0;
+  }
+  else
+    load_block<BS, PER_BLOCK>(acc, k, sC, accC);
   double out[BS2];
   if constexpr (NV == 4) {
     const bool dropN = (wc >> 10) & 1u;
@@ -963,11 +940,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   // the outer products from zero, the diagonal block is minus the sum of the row's other blocks (gradients of a cell sum
   // to zero), the map runs once per stored block after the walk, and accumulate mode adds the old values at the store.
   constexpr bool POST = Op::LINEAR_POST;
-#if B2F_FAN_SOA
-  const FanCoords FC{ A.coords_soa, A.soa_stride };
-#else
-  const FanCoords FC{ A.coords, 0 };
-#endif
+  const uint32_t fmask = LOCKSTEP ? 0u : A.fan_first_mask; // 8192 or 0, see AssembleArgs
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
 #if B2F_FAN_BULK_STORE
@@ -1011,7 +984,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     e_rbn = __ldg(A.row_index + row + 1);
     e_qb = __ldg(A.fan_ptr + row);
     e_qbn = __ldg(A.fan_ptr + row + 1);
-    load_xyz(FC, (int32_t)row, X0);
+    load_xyz(A.coords, (int32_t)row, X0);
     if (!PERM && A.node_is_own != nullptr)
       e_own = A.node_is_own[row];
   }
@@ -1105,7 +1078,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       }
     }
   }
-  else {
+  else if (fmask == 0u) { // with the plan's first-visit marks every slot of a walked row is stored before it is read: no clearing pass
     for (int q = t; q < nval; q += C::ROWS)
       acc_s[q] = 0.0;
   }
@@ -1118,7 +1091,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     const bool own = (A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0);
     qb = __ldg(A.fan_ptr + row);
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
-    load_xyz(FC, (int32_t)row, X0);
+    load_xyz(A.coords, (int32_t)row, X0);
 #endif
   }
 #if B2F_FAN_TILE_AHEAD > 0
@@ -1136,6 +1109,10 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     }
   }
 #endif
+  if (fmask != 0u && t < nrows && nstep == 0) { // rows that are not walked (not own, no cell) stay zero
+    for (int q = 0; q < k * BS2; ++q)
+      acc_s[(size_t)(rb - vbeg) * BS2 + q] = 0.0;
+  }
   mbar_wait(bar, phase);
 #if B2F_FAN_PERSIST
   phase ^= 1u;
@@ -1167,7 +1144,13 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     for (int x = 1; x < k; ++x)
       prefetch_l2(A.coords + 3ll * cols[x]);
     double diag[BS2];
-    load_block<BS, PER_BLOCK>(acc, k, B2F_DIAG_SLOT, diag);
+    if (fmask != 0u) { // the slab was not cleared (first-visit marks): the diagonal starts from zero like every other first load
+#pragma unroll
+      for (int e = 0; e < BS2; ++e)
+        diag[e] = 0.0;
+    }
+    else
+      load_block<BS, PER_BLOCK>(acc, k, B2F_DIAG_SLOT, diag);
     double measure = 0.0;
     if constexpr (LOCKSTEP) {
       static_assert(!LOCKSTEP || NV == 4, "the lockstep walk is for tetrahedra");
@@ -1176,7 +1159,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       int sl[3] = { 0, 0, 0 };
       double Xn[3];
       uint32_t w = st[0], wc = 0;
-      load_xyz(FC, cols[w & 1023u], Xn);
+      load_xyz(A.coords, cols[w & 1023u], Xn);
       double cv = 0.0, cvn = 0.0;
       uint32_t cidn = 0;
       if constexpr (Op::NEEDS_CELL) {
@@ -1196,7 +1179,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         for (int d = 0; d < 3; ++d)
           e[F][d] = Xn[d] - X0[d];
         if (more)
-          load_xyz(FC, cols[w & 1023u], Xn);
+          load_xyz(A.coords, cols[w & 1023u], Xn);
         sl[F] = (int)(wc & 1023u);
         load_block<BS, PER_BLOCK>(acc, k, sl[F], av[F]);
         const bool odd = (wc >> 13) & 1u;
@@ -1286,9 +1269,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
           sl[1] = (int)(wc & 1023u);
           sl[2] = (int)((wc >> 10) & 1023u);
           double XB[3];
-          load_xyz(FC, cols[sl[2]], XB);
+          load_xyz(A.coords, cols[sl[2]], XB);
           if (more)
-            load_xyz(FC, cols[w & 1023u], Xn);
+            load_xyz(A.coords, cols[w & 1023u], Xn);
           load_block<BS, PER_BLOCK>(acc, k, sl[1], av[1]);
           load_block<BS, PER_BLOCK>(acc, k, sl[2], av[2]);
 #pragma unroll
@@ -1335,7 +1318,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     int sP = 0, sQ = 0, sO = 0;
     double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
     uint32_t w = st[0];
-    load_xyz(FC, cols[w & 1023u], Xn);
+    load_xyz(A.coords, cols[w & 1023u], Xn);
     // AA: the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
     // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago.  Two
     // registers; the instantiations that have none to spare (reorder mode, fused source term, per-cell data) keep the short chain.
@@ -1392,7 +1375,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       enter(eP);
       if constexpr (AA) {
         if (p + 1 < nstep)
-          load_xyz(FC, cn, Xn);
+          load_xyz(A.coords, cn, Xn);
         if (p + 2 < nstep)
           cn = cols[w2 & 1023u];
         w = w1;
@@ -1402,9 +1385,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       }
       else if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
-        load_xyz(FC, cols[w & 1023u], Xn);
+        load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, FC, X0, acc, cols, k, wc, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
@@ -1414,7 +1397,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       enter(eQ);
       if constexpr (AA) {
         if (p + 1 < nstep)
-          load_xyz(FC, cn, Xn);
+          load_xyz(A.coords, cn, Xn);
         if (p + 2 < nstep)
           cn = cols[w2 & 1023u];
         w = w1;
@@ -1424,9 +1407,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       }
       else if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
-        load_xyz(FC, cols[w & 1023u], Xn);
+        load_xyz(A.coords, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, FC, X0, acc, cols, k, wc, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
@@ -1635,23 +1618,6 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
         F.coords = A.r_coords;
         F.slot_map = A.r_slot_map;
       }
-#if B2F_FAN_SOA == 2
-      // EXPERIMENT (tools/build_variant.sh -DB2F_FAN_SOA=2): the split copy is made here, before every launch, into a buffer
-      // owned by the launcher - the product form takes it from the handle (AssembleArgs::coords_soa)
-      if (F.coords_soa == nullptr) {
-        static double* soa = nullptr;
-        static long long cap = 0;
-        if (cap < F.nb_node) {
-          cudaFree(soa);
-          if (cudaMalloc(&soa, sizeof(double) * 3 * (size_t)F.nb_node) != cudaSuccess)
-            return cudaErrorMemoryAllocation;
-          cap = F.nb_node;
-        }
-        k_coords_to_soa<<<(unsigned)((F.nb_node + 255) / 256), 256, 0, stream>>>(F.coords, 0, F.nb_node, F.nb_node, soa);
-        F.coords_soa = soa;
-        F.soa_stride = F.nb_node;
-      }
-#endif
 #if B2F_FAN_PERSIST
       // one CTA per resident slot (B2F_FAN_PERSIST = waves of such CTAs; 1 = exactly the resident set)
       static int sm_count = 0;

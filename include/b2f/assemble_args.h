@@ -49,9 +49,9 @@ struct AssembleArgs
   const int32_t* caller_columns = nullptr; // caller-numbered columns / coordinates for the tiles that take the global fallback path
   const double* caller_coords = nullptr;
   const uint16_t* slot_map = nullptr;
-  // the fan kernel's own copy of the coordinates, x / y / z in three arrays of soa_stride doubles (null: the interleaved array is read)
-  const double* coords_soa = nullptr;
-  long long soa_stride = 0;
+  // 8192 when the step words carry first-visit marks AND this launch may use them (overwrite mode, every cell assembled): the
+  // first load of a slot then starts from zero and the slab is not cleared; 0 otherwise
+  uint32_t fan_first_mask = 0;
 };
 
 enum { VARIANT_CELL_ATOMIC = 1, VARIANT_CELL_ATOMIC_WARPAGG = 2, VARIANT_NODE_GATHER = 3, VARIANT_NODE_GATHER_SLOTS = 4 };

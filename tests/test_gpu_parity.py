@@ -509,6 +509,35 @@ def test_fan_plan_visits_every_incident_cell_once(mesh_name, fan_mode):
             assert (inv & 1) == odd, f"row {row} cell {cell}"
 
 
+@pytest.mark.parametrize("mesh_name", ["cube5", "cube7_shuffled", "cube4_mixed_orientation", "square9_shuffled", "square20"])
+def test_fan_plan_marks_first_visits(mesh_name):
+    """k_fan_first_flags: bit 13 of an emit word / bits 20, 21 of a START word are set exactly when the slot they load has
+    not been loaded before in its row (the kernel then starts that accumulator from zero and skips clearing the slab), and
+    every slot of a walked row is loaded at least once."""
+    bsr, m, dim, cells, coords = _setup(mesh_name, 1, True, 3, fan_mode=1)
+    plan = {k: _np(v) for k, v in bsr.plan().items()}
+    ri = _np(bsr.matrix().rowIndexWithEnd())
+    nv = cells.shape[1]
+    fan_ptr, steps = plan["fan_ptr"], plan["fan_steps"].view(np.uint32)
+    for row in range(ri.shape[0] - 1):
+        seen = set()
+
+        def check(slot, flag, what):
+            assert bool(flag) == (slot not in seen), f"row {row}: {what} slot {slot}, flag {flag}, seen {sorted(seen)}"
+            seen.add(slot)
+
+        for q in range(fan_ptr[row], fan_ptr[row + 1]):
+            w = int(steps[q])
+            if w & 0x80000000:
+                check(w & 1023, (w >> 20) & 1, "START N")
+                if nv == 4:
+                    check((w >> 10) & 1023, (w >> 21) & 1, "START O")
+            else:
+                check(w & 1023, (w >> 13) & 1, "emit")
+        if fan_ptr[row + 1] > fan_ptr[row]:
+            assert seen == set(range(1, int(ri[row + 1] - ri[row]))), f"row {row}: slots {sorted(seen)}"
+
+
 @pytest.mark.parametrize("mesh_name,bs", [("cube5", 1), ("square9_shuffled", 2), ("cube7_shuffled", 3)])
 def test_csr_global_numbering_on_device(mesh_name, bs):
     """Device replacement of the host renumbering loops of femutils/HypreDoFLinearSystem.cc:474-519."""
