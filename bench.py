@@ -336,8 +336,11 @@ def parity_sample(cells, coords, mat, own_rows, receiving_rows, nrows=10000, see
     # mesh holds a few nearly flat tetrahedra, where the determinant alone costs kappa * eps)
     ref64, _, _ = laplace_tet_rows_reference(cells, coords, ri, co, rows, extended=False)
     rel64 = (np.abs(ref64.astype(np.longdouble) - ref) / np.maximum(np.abs(ref), 1e-3 * rowmax))[mask]
+    # device against that plain fp64 host evaluation (the reference computes in fp64 too): the parity figure proper
+    relgh = (np.abs(got - ref64.astype(np.longdouble)) / np.maximum(np.abs(ref), 1e-3 * rowmax))[mask]
     return {"rows": int(rows.shape[0]), "entries": int(mask.sum()), "max_rel": float(rel.max()), "max_rel_pure": float(pure.max()), "over_1e-12": int((rel > 1e-12).sum()),
             "host_fp64_same_formula_max_rel": float(rel64.max()), "host_fp64_over_1e-12": int((rel64 > 1e-12).sum()),
+            "device_vs_host_fp64_max_rel": float(relgh.max()), "device_vs_host_fp64_over_1e-12": int((relgh > 1e-12).sum()),
             "columns_missing": missing, "receiving_rows": int(pick[0].shape[0]) if len(pick) > 1 else 0,
             "rule": "|d| / max(|ref|, 1e-3 * row max); ref = extended-precision host recomputation of the sampled rows (numpy longdouble, reference formula)"}
 

@@ -14,5 +14,8 @@ import json
 t=open('gpurun_out/scale_${TAG}_${n}gpu.json').read(); d=json.loads(t[t.index('{'):])
 print($n, d['scaling'], d['ms_per_step'], d['value'], d['parity_sample'], d['e2e'], d['config']['sparsity_build_ms'], d['config']['step_breakdown']); print(d.get('weak_scaling'))"
 done
-[ -n "$SCALE_REF" ] && timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NP --master-addr 127.0.0.1 --master-port 29531 bench.py --impl reference --gpus $NP --steps 2 --warmup 1 \
+if [ -n "$SCALE_REF" ]; then
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NP --master-addr 127.0.0.1 --master-port 29531 bench.py --impl reference --gpus $NP --steps 2 --warmup 1 \
   > gpurun_out/scale_ref_${TAG}_${NP}gpu.json 2> gpurun_out/scale_ref_${TAG}_${NP}gpu.err; echo "ref rc=$?"; cut -c1-400 gpurun_out/scale_ref_${TAG}_${NP}gpu.json
+fi
+true
