@@ -624,6 +624,9 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_EARLY_ROW
 #define B2F_FAN_EARLY_ROW 1
 #endif
+#ifndef B2F_FAN_ROWSUM4
+#define B2F_FAN_ROWSUM4 0
+#endif
 #ifndef B2F_FAN_ADDR_AHEAD
 #define B2F_FAN_ADDR_AHEAD 1
 #endif
@@ -1445,9 +1448,24 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       op.post(diag);
     }
     else if constexpr (DIAG_BY_ROW_SUM) {
+#if B2F_FAN_ROWSUM4
+      // four independent partial sums: the 14 shared-memory reads of a row no longer form one dependent chain
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      int x = 1;
+      for (; x + 3 < k; x += 4) {
+        s0 += acc[x];
+        s1 += acc[x + 1];
+        s2 += acc[x + 2];
+        s3 += acc[x + 3];
+      }
+      for (; x < k; ++x)
+        s0 += acc[x];
+      const double sum = (s0 + s1) + (s2 + s3);
+#else
       double sum = 0.0;
       for (int x = 1; x < k; ++x)
         sum += acc[x];
+#endif
       if constexpr (row_sum_mass<Op>::value)
         diag[0] = fma((double)(NV + 1), diag[0], -sum);
       else

@@ -6,8 +6,10 @@ mkdir -p gpurun_out
 B="python bench.py --steps 2 --warmup 3 --cpu-cells 100000 --no-parity"
 $B > gpurun_out/ncu_plain_$TAG.log 2>&1 || { echo "plain bench failed"; tail -5 gpurun_out/ncu_plain_$TAG.log; exit 1; }
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$TAG.csv $B > gpurun_out/ncu_launch_$TAG.log 2>&1; echo "ncu launches rc=$?"
+WANT=${NCU_CAPS:-fan build_fan row_unique pack_fan spmv ij_fill fan_elasticity fan_heat3d}
 cap() { # name regex skip cmd...
   local name=$1 rx=$2 skip=$3; shift 3
+  [[ " $WANT " == *" $name "* ]] || return 0
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$rx --launch-skip $skip -c 1 -f -o gpurun_out/ncu_${TAG}_$name "$@" > gpurun_out/ncu_${TAG}_$name.log 2>&1; echo "ncu $name rc=$?"
 }
 cap fan k_node_fan 4 $B

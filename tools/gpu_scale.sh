@@ -19,3 +19,7 @@ if [ -n "$SCALE_REF" ]; then
   > gpurun_out/scale_ref_${TAG}_${NP}gpu.json 2> gpurun_out/scale_ref_${TAG}_${NP}gpu.err; echo "ref rc=$?"; cut -c1-400 gpurun_out/scale_ref_${TAG}_${NP}gpu.json
 fi
 true
+if [ -n "$SCALE_PROBE" ]; then
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NP --master-addr 127.0.0.1 --master-port 29541 tools/pcie_probe.py > gpurun_out/pcie_probe_${TAG}_${NP}gpu.json 2> gpurun_out/pcie_probe_${TAG}_${NP}gpu.err; echo "probe rc=$?"; grep probe gpurun_out/pcie_probe_${TAG}_${NP}gpu.json
+fi
+true
