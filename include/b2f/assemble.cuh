@@ -624,12 +624,6 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_EARLY_ROW
 #define B2F_FAN_EARLY_ROW 1
 #endif
-#ifndef B2F_FAN_PEEL
-#define B2F_FAN_PEEL 0
-#endif
-#ifndef B2F_FAN_ROWSUM4
-#define B2F_FAN_ROWSUM4 0
-#endif
 #ifndef B2F_FAN_ADDR_AHEAD
 #define B2F_FAN_ADDR_AHEAD 1
 #endif
@@ -723,7 +717,7 @@ template <class Op, bool PER_BLOCK, bool SKIP_DIAG, bool SRC, class AccT, class 
 __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
                                          int k, uint32_t wc, uint32_t first_mask, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
-                                         double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure, const double* xb_pre = nullptr)
+                                         double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure)
 {
   constexpr int NV = Op::NV, BS = Op::BS, BS2 = BS * BS;
   sC = (int)(wc & 1023u);
@@ -753,13 +747,7 @@ __device__ __forceinline__ void fan_step(const Op& op, const double* __restrict_
       else
         load_block<BS, PER_BLOCK>(acc, k, sO, accO);
       double XB[3];
-      if (xb_pre != nullptr) { // the first START of a row: its second vertex was fetched together with the first (B2F_FAN_PEEL)
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
-          XB[d] = xb_pre[d];
-      }
-      else
-        load_xyz(coords, cols[sO], XB);
+      load_xyz(coords, cols[sO], XB);
 #pragma unroll
       for (int d = 0; d < 3; ++d)
         eO[d] = XB[d] - X0[d];
@@ -1381,68 +1369,6 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
 #else
 #define B2F_NEXT_WORD(pp) w = st[(pp) + 1];
 #endif
-#if B2F_FAN_PEEL
-    // Every walk begins with a START.  Tets: the second vertex of that first window is fetched here, together with the first,
-    // instead of inside the step (one exposed round trip less per row); the loop then runs Q-half first.
-    double XB0[3] = { 0.0, 0.0, 0.0 };
-    const bool pre = NV == 4 && (w & FAN_START) != 0u;
-    if (pre)
-      load_xyz(A.coords, cols[(w >> 10) & 1023u], XB0);
-    auto half_a = [&](const double* xb) -> bool {
-      // step p: P enters (Q is the newest)
-      uint32_t wc = w;
-      enter(eP);
-      if constexpr (AA) {
-        if (p + 1 < nstep)
-          load_xyz(A.coords, cn, Xn);
-        if (p + 2 < nstep)
-          cn = cols[w2 & 1023u];
-        w = w1;
-        w1 = w2;
-        if (p + 3 < nstep)
-          w2 = st[p + 3];
-      }
-      else if (p + 1 < nstep) {
-        B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
-      }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure, xb);
-      next_cell(p);
-      newest_is_Q = false;
-      return ++p >= nstep;
-    };
-    auto half_b = [&]() -> bool {
-      // step p: Q enters (P is the newest)
-      uint32_t wc = w;
-      enter(eQ);
-      if constexpr (AA) {
-        if (p + 1 < nstep)
-          load_xyz(A.coords, cn, Xn);
-        if (p + 2 < nstep)
-          cn = cols[w2 & 1023u];
-        w = w1;
-        w1 = w2;
-        if (p + 3 < nstep)
-          w2 = st[p + 3];
-      }
-      else if (p + 1 < nstep) {
-        B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
-      }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
-      next_cell(p);
-      newest_is_Q = true;
-      return ++p >= nstep;
-    };
-    if (!half_a(pre ? XB0 : nullptr)) {
-      while (true) {
-        if (half_b())
-          break;
-        if (half_a(nullptr))
-          break;
-      }
-    }
-#else
     while (true) {
       // step p: P enters (Q is the newest)
       uint32_t wc = w;
@@ -1489,7 +1415,6 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       if (++p >= nstep)
         break;
     }
-#endif
 #undef B2F_NEXT_WORD
     if (newest_is_Q) {
       if (sQ)
@@ -1520,24 +1445,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       op.post(diag);
     }
     else if constexpr (DIAG_BY_ROW_SUM) {
-#if B2F_FAN_ROWSUM4
-      // four independent partial sums: the 14 shared-memory reads of a row no longer form one dependent chain
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-      int x = 1;
-      for (; x + 3 < k; x += 4) {
-        s0 += acc[x];
-        s1 += acc[x + 1];
-        s2 += acc[x + 2];
-        s3 += acc[x + 3];
-      }
-      for (; x < k; ++x)
-        s0 += acc[x];
-      const double sum = (s0 + s1) + (s2 + s3);
-#else
       double sum = 0.0;
       for (int x = 1; x < k; ++x)
         sum += acc[x];
-#endif
       if constexpr (row_sum_mass<Op>::value)
         diag[0] = fma((double)(NV + 1), diag[0], -sum);
       else
