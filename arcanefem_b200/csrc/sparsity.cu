@@ -769,13 +769,45 @@ __global__ void __launch_bounds__(128) k_fan_pivot_hint(const int32_t* __restric
 // of a START word for its two slots), so the kernel starts the register from zero instead, and - every slot of a walked row
 // being stored at least once - does not have to clear the slab first: two passes less through the L1 data pipe, the unit the
 // fan kernel loads most.  One thread per row, 1024-slot bitmap in local memory.
-__global__ void __launch_bounds__(128) k_fan_first_flags(const int32_t* __restrict__ fan_ptr, long long nb_node, uint32_t* __restrict__ steps)
+__global__ void __launch_bounds__(128) k_fan_first_flags(const int32_t* __restrict__ fan_ptr, const int32_t* __restrict__ row_index, long long nb_node,
+                                                         uint32_t* __restrict__ steps)
 {
+  __shared__ uint32_t seen_s[8][128]; // 256 slots per thread, one column per thread (no bank conflicts)
   const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= nb_node)
     return;
   const int32_t qb = fan_ptr[row];
   const int n = fan_ptr[row + 1] - qb;
+  if (n == 0)
+    return;
+  const int k = row_index[row + 1] - row_index[row];
+  auto mark = [&](uint32_t w, bool f0, bool f1) {
+    if (w & 0x80000000u)
+      return w | (f0 ? 1u << 20 : 0u) | (f1 ? 1u << 21 : 0u);
+    return w | (f0 ? 1u << 13 : 0u);
+  };
+  if (k <= 256) {
+    const int t = threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      seen_s[i][t] = 0u;
+    auto first = [&](uint32_t slot) {
+      const uint32_t bit = 1u << (slot & 31u);
+      const uint32_t old = seen_s[slot >> 5][t];
+      seen_s[slot >> 5][t] = old | bit;
+      return (old & bit) == 0u;
+    };
+    for (int p = 0; p < n; ++p) {
+      const uint32_t w = steps[qb + p];
+      const bool f0 = first(w & 1023u);
+      const uint32_t so = (w & 0x80000000u) ? (w >> 10) & 1023u : 0u; // 0 for triangles (slot 0 is the diagonal, never a window vertex)
+      const bool f1 = so != 0u && first(so);
+      if (f0 || f1)
+        steps[qb + p] = mark(w, f0, f1);
+    }
+    return;
+  }
+  // rows with more than 256 blocks (very high valence; not walked, every cell is its own chain): 1024-slot bitmap in local memory
   uint32_t seen[32];
   for (int i = 0; i < 32; ++i)
     seen[i] = 0u;
@@ -786,19 +818,12 @@ __global__ void __launch_bounds__(128) k_fan_first_flags(const int32_t* __restri
     return f;
   };
   for (int p = 0; p < n; ++p) {
-    uint32_t w = steps[qb + p];
-    const uint32_t before = w;
-    if (w & 0x80000000u) {
-      if (first(w & 1023u))
-        w |= 1u << 20;
-      const uint32_t so = (w >> 10) & 1023u; // 0 for triangles (slot 0 is the diagonal, never a window vertex)
-      if (so != 0u && first(so))
-        w |= 1u << 21;
-    }
-    else if (first(w & 1023u))
-      w |= 1u << 13;
-    if (w != before)
-      steps[qb + p] = w;
+    const uint32_t w = steps[qb + p];
+    const bool f0 = first(w & 1023u);
+    const uint32_t so = (w & 0x80000000u) ? (w >> 10) & 1023u : 0u;
+    const bool f1 = so != 0u && first(so);
+    if (f0 || f1)
+      steps[qb + p] = mark(w, f0, f1);
   }
 }
 
@@ -1188,7 +1213,7 @@ int build_pattern(b2f_context_s* h, cudaStream_t stream)
     }
     h->fan_first = false;
     if (nb_step > 0 && h->opt.fan_mode != B2F_FAN_LOCKSTEP) {
-      k_fan_first_flags<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), nn, h->fan_steps.as<uint32_t>());
+      k_fan_first_flags<<<grid_for(nn, 128), 128, 0, stream>>>(h->fan_ptr.as<int32_t>(), ri, nn, h->fan_steps.as<uint32_t>());
       B2F_CUDA(cudaGetLastError());
       h->fan_first = true;
     }
