@@ -397,7 +397,7 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sp = []
-    for _ in range(2):  # second build: no module load / local-memory set-up inside the timed region
+    for _ in range(4):  # first build: module load / local-memory set-up inside the timed region; reported: median of the three warm ones
         ev0.record()
         bsr.computeSparsity()
         ev1.record()
@@ -472,7 +472,7 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
             plane = part["plane"]
             top = part["bounds"][rank + 1] - part["z0"]
             receiving = np.arange(top * plane, (top + 1) * plane, dtype=np.int64)
-    out = dict(W=W, ms_step=ms_step, own_nnz=own_nnz, own_cells_job=own_cells_job, nnz=nnz, nnzb=nnzb, nc=nc, nn=nn, nv=nv, sparsity_ms=sp[1], sparsity_cold_ms=sp[0], gen_s=gen_s,
+    out = dict(W=W, ms_step=ms_step, own_nnz=own_nnz, own_cells_job=own_cells_job, nnz=nnz, nnzb=nnzb, nc=nc, nn=nn, nv=nv, sparsity_ms=sorted(sp[1:])[1], sparsity_cold_ms=sp[0], gen_s=gen_s,
                clocks=clocks, stats=stats, value=own_nnz / (ms_step * 1e-3) / 1e9, overlapped=exchange is not None and not args.no_overlap)
 
     # --- parity of the matrix the timed loop left behind: a fixed sample of own rows against the host recomputation
@@ -576,7 +576,7 @@ def run_mode(args, workload, mode, torch, dist, comm, rank, world, local_rank, f
         # --- the rest of the path, each stage on its own (t_sparsity, t_dirichlet, t_tocsr, t_total)
         if world == 1 and workload == "poisson3d":
             try:
-                out["path"] = path_breakdown(torch, fem, gen, bsr, op, coords, sp[1], ms_step)
+                out["path"] = path_breakdown(torch, fem, gen, bsr, op, coords, sorted(sp[1:])[1], ms_step)
             except Exception as e:  # a reporting extra must never cost the bench line
                 out["path"] = {"error": f"{type(e).__name__}: {e}"}
         if rank == 0 and world == 1:
