@@ -72,12 +72,37 @@ __device__ __forceinline__ void load_cell_nodes(const int32_t* __restrict__ cell
   }
 }
 
+#ifndef B2F_CHECKED
+#define B2F_CHECKED 0
+#endif
 __device__ __forceinline__ void load_xyz(const double* __restrict__ coords, int32_t node, double (&x)[3])
 {
   const double* p = coords + 3ll * node;
   x[0] = __ldg(p);
   x[1] = __ldg(p + 1);
   x[2] = __ldg(p + 2);
+}
+
+// Coordinates as the fan kernel reads them: the plain array, plus - in the range-checked build (B2F_CHECKED, below) - the node
+// count and the violation counter, so that every gathered node id is checked.
+struct CoordView
+{
+  const double* p;
+#if B2F_CHECKED
+  long long nb_node;
+  unsigned long long* bad;
+#endif
+};
+__device__ __forceinline__ void load_xyz(const CoordView& c, int32_t node, double (&x)[3])
+{
+#if B2F_CHECKED
+  if (node < 0 || node >= c.nb_node) {
+    atomicAdd(c.bad, 1ull);
+    x[0] = x[1] = x[2] = 0.0;
+    return;
+  }
+#endif
+  load_xyz(c.p, node, x);
 }
 
 // Even permutation bringing local vertex a to position 0: tets m[k] = n[a ^ k] (double transpositions),
@@ -634,11 +659,34 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 // registers instead of re-deriving 64-bit generic pointers from the dynamic-smem base at every step.  The read-only arrays
 // (columns, step words) use plain asm (free to schedule); the accumulators use volatile asm, which keeps their loads and
 // stores in program order with respect to each other.
+// B2F_CHECKED (tools/build_variant.sh checked -DB2F_CHECKED=1): every shared-memory access of the walk is checked against the
+// calling thread's OWN range (its row's slots of the slab, its row's column ids, its row's step words) and every gathered node id
+// against [0, nb_node); violations are counted in counters[0] (b2f_stats.columns_not_found, which every parity test asserts to be
+// zero) and the access is skipped.  Stands in for compute-sanitizer, which is closed on the measurement pool: a walk that stays
+// inside its own ranges cannot race with another thread's, and cannot leave the tile.
+#ifndef B2F_CHECKED
+#define B2F_CHECKED 0
+#endif
+#if B2F_CHECKED
+#define B2F_RANGE_MEMBERS \
+  int lo, hi;             \
+  unsigned long long* bad;
+#define B2F_RANGE_TEST(i, fail_value)   \
+  if ((i) < lo || (i) >= hi) {          \
+    atomicAdd(bad, 1ull);               \
+    return fail_value;                  \
+  }
+#else
+#define B2F_RANGE_MEMBERS
+#define B2F_RANGE_TEST(i, fail_value)
+#endif
 struct SmemI32
 {
   uint32_t a;
+  B2F_RANGE_MEMBERS
   __device__ __forceinline__ int32_t operator[](int i) const
   {
+    B2F_RANGE_TEST(i, 0)
     int32_t v;
     asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a + 4u * (uint32_t)i));
     return v;
@@ -647,8 +695,10 @@ struct SmemI32
 struct SmemU32
 {
   uint32_t a;
+  B2F_RANGE_MEMBERS
   __device__ __forceinline__ uint32_t operator[](int i) const
   {
+    B2F_RANGE_TEST(i, 0x80000000u)
     uint32_t v;
     asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a + 4u * (uint32_t)i));
     return v;
@@ -657,14 +707,20 @@ struct SmemU32
 struct SmemF64
 {
   uint32_t a;
+  B2F_RANGE_MEMBERS
   __device__ __forceinline__ double ld(int i) const
   {
+    B2F_RANGE_TEST(i, 0.0)
     double v;
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a + 8u * (uint32_t)i));
     return v;
   }
   __device__ __forceinline__ double operator[](int i) const { return ld(i); }
-  __device__ __forceinline__ void st(int i, double v) const { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a + 8u * (uint32_t)i), "d"(v)); }
+  __device__ __forceinline__ void st(int i, double v) const
+  {
+    B2F_RANGE_TEST(i, )
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a + 8u * (uint32_t)i), "d"(v));
+  }
 };
 template <int BS, bool PER_BLOCK>
 __device__ __forceinline__ void load_block(SmemF64 acc, int k, int x, double (&out)[BS * BS])
@@ -714,7 +770,7 @@ __device__ __forceinline__ void store_block(double* __restrict__ acc, int k, int
 // receive the vertex that enters (eC is filled by the caller: edge vector C - row node for tets, the vertex for triangles); the caller alternates two register sets between the roles N and C, so the "C becomes
 // N" renaming costs no instruction.  Tets carry m = eN x eO.
 template <class Op, bool PER_BLOCK, bool SKIP_DIAG, bool SRC, class AccT, class ColsT>
-__device__ __forceinline__ void fan_step(const Op& op, const double* __restrict__ coords, const double (&X0)[3], AccT acc, ColsT cols,
+__device__ __forceinline__ void fan_step(const Op& op, const CoordView& coords, const double (&X0)[3], AccT acc, ColsT cols,
                                          int k, uint32_t wc, uint32_t first_mask, double cell, double (&eN)[3], double (&accN)[Op::BS * Op::BS], int& sN,
                                          double (&eO)[3], double (&accO)[Op::BS * Op::BS], int& sO, double (&m)[3], double (&eC)[3],
                                          double (&accC)[Op::BS * Op::BS], int& sC, double (&diag)[Op::BS * Op::BS], double& measure)
@@ -941,6 +997,11 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   // to zero), the map runs once per stored block after the walk, and accumulate mode adds the old values at the store.
   constexpr bool POST = Op::LINEAR_POST;
   const uint32_t fmask = LOCKSTEP ? 0u : A.fan_first_mask; // 8192 or 0, see AssembleArgs
+#if B2F_CHECKED
+  const CoordView CV{ A.coords, A.nb_node, A.counters };
+#else
+  const CoordView CV{ A.coords };
+#endif
   extern __shared__ __align__(16) unsigned char b2f_smem[];
   unsigned long long* bar = reinterpret_cast<unsigned long long*>(b2f_smem);
 #if B2F_FAN_BULK_STORE
@@ -984,7 +1045,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     e_rbn = __ldg(A.row_index + row + 1);
     e_qb = __ldg(A.fan_ptr + row);
     e_qbn = __ldg(A.fan_ptr + row + 1);
-    load_xyz(A.coords, (int32_t)row, X0);
+    load_xyz(CV, (int32_t)row, X0);
     if (!PERM && A.node_is_own != nullptr)
       e_own = A.node_is_own[row];
   }
@@ -1091,7 +1152,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     const bool own = (A.node_is_own == nullptr) || (A.node_is_own[out_row] != 0);
     qb = __ldg(A.fan_ptr + row);
     nstep = own ? (__ldg(A.fan_ptr + row + 1) - qb) : 0;
-    load_xyz(A.coords, (int32_t)row, X0);
+    load_xyz(CV, (int32_t)row, X0);
 #endif
   }
 #if B2F_FAN_TILE_AHEAD > 0
@@ -1127,9 +1188,15 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     const int acc_shift = dl * (PER_BLOCK ? BS2 : BS);
 #define B2F_DIAG_SLOT (A.diag_last ? k : 0) /* re-read from the parameter bank where it is used: no register lives across the walk */
 #if B2F_FAN_ASM_SMEM
+#if B2F_CHECKED
+    SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) - 8u * (uint32_t)acc_shift, acc_shift, acc_shift + k * BS2, A.counters };
+    SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) - 4u * (uint32_t)dl, dl, dl + k, A.counters };
+    SmemU32 st{ (uint32_t)__cvta_generic_to_shared(steps_s + (qb - abeg_al)), 0, nstep, A.counters };
+#else
     SmemF64 acc{ (uint32_t)__cvta_generic_to_shared(acc_s + (size_t)(rb - vbeg) * BS2) - 8u * (uint32_t)acc_shift };
     SmemI32 cols{ (uint32_t)__cvta_generic_to_shared(cols_s + (rb - vbeg_al)) - 4u * (uint32_t)dl };
     SmemU32 st{ (uint32_t)__cvta_generic_to_shared(steps_s + (qb - abeg_al)) };
+#endif
     // the addresses become opaque here, after the barrier: the asm loads below depend on them and cannot be hoisted above
     // the wait, and the compiler keeps them in registers instead of re-deriving them
     asm volatile("" : "+r"(acc.a), "+r"(cols.a), "+r"(st.a)::"memory");
@@ -1159,7 +1226,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       int sl[3] = { 0, 0, 0 };
       double Xn[3];
       uint32_t w = st[0], wc = 0;
-      load_xyz(A.coords, cols[w & 1023u], Xn);
+      load_xyz(CV, cols[w & 1023u], Xn);
       double cv = 0.0, cvn = 0.0;
       uint32_t cidn = 0;
       if constexpr (Op::NEEDS_CELL) {
@@ -1179,7 +1246,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         for (int d = 0; d < 3; ++d)
           e[F][d] = Xn[d] - X0[d];
         if (more)
-          load_xyz(A.coords, cols[w & 1023u], Xn);
+          load_xyz(CV, cols[w & 1023u], Xn);
         sl[F] = (int)(wc & 1023u);
         load_block<BS, PER_BLOCK>(acc, k, sl[F], av[F]);
         const bool odd = (wc >> 13) & 1u;
@@ -1269,9 +1336,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
           sl[1] = (int)(wc & 1023u);
           sl[2] = (int)((wc >> 10) & 1023u);
           double XB[3];
-          load_xyz(A.coords, cols[sl[2]], XB);
+          load_xyz(CV, cols[sl[2]], XB);
           if (more)
-            load_xyz(A.coords, cols[w & 1023u], Xn);
+            load_xyz(CV, cols[w & 1023u], Xn);
           load_block<BS, PER_BLOCK>(acc, k, sl[1], av[1]);
           load_block<BS, PER_BLOCK>(acc, k, sl[2], av[2]);
 #pragma unroll
@@ -1318,7 +1385,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     int sP = 0, sQ = 0, sO = 0;
     double Xn[3]; // coordinates of the entering vertex, prefetched one step ahead
     uint32_t w = st[0];
-    load_xyz(A.coords, cols[w & 1023u], Xn);
+    load_xyz(CV, cols[w & 1023u], Xn);
     // AA: the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
     // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago.  Two
     // registers; the instantiations that have none to spare (reorder mode, fused source term, per-cell data) keep the short chain.
@@ -1375,7 +1442,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       enter(eP);
       if constexpr (AA) {
         if (p + 1 < nstep)
-          load_xyz(A.coords, cn, Xn);
+          load_xyz(CV, cn, Xn);
         if (p + 2 < nstep)
           cn = cols[w2 & 1023u];
         w = w1;
@@ -1385,9 +1452,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       }
       else if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
+        load_xyz(CV, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, CV, X0, acc, cols, k, wc, fmask, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
       next_cell(p);
       newest_is_Q = false;
       if (++p >= nstep)
@@ -1397,7 +1464,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       enter(eQ);
       if constexpr (AA) {
         if (p + 1 < nstep)
-          load_xyz(A.coords, cn, Xn);
+          load_xyz(CV, cn, Xn);
         if (p + 2 < nstep)
           cn = cols[w2 & 1023u];
         w = w1;
@@ -1407,9 +1474,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       }
       else if (p + 1 < nstep) {
         B2F_NEXT_WORD(p)
-        load_xyz(A.coords, cols[w & 1023u], Xn);
+        load_xyz(CV, cols[w & 1023u], Xn);
       }
-      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, A.coords, X0, acc, cols, k, wc, fmask, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
+      fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, CV, X0, acc, cols, k, wc, fmask, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
       next_cell(p);
       newest_is_Q = true;
       if (++p >= nstep)
