@@ -649,6 +649,17 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_EARLY_ROW
 #define B2F_FAN_EARLY_ROW 1
 #endif
+// 1: operators with per-cell data get the cell ids of the tile's steps by a third bulk copy into shared memory (+4 B per step)
+#ifndef B2F_FAN_STAGE_CELLS
+#define B2F_FAN_STAGE_CELLS 1
+#endif
+// 1: HeatTet gathers its coordinates two steps ahead (see D2 in k_node_fan)
+#ifndef B2F_FAN_DEPTH2
+#define B2F_FAN_DEPTH2 1
+#endif
+#ifndef B2F_FAN_AA_CELL
+#define B2F_FAN_AA_CELL 1
+#endif
 #ifndef B2F_FAN_ADDR_AHEAD
 #define B2F_FAN_ADDR_AHEAD 1
 #endif
@@ -1013,6 +1024,11 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
   int32_t* cols_s = reinterpret_cast<int32_t*>(acc_s + (size_t)acc_blocks * BS2);
 #endif
   uint32_t* steps_s = reinterpret_cast<uint32_t*>(cols_s + acc_blocks + C::PAD);
+#if B2F_FAN_STAGE_CELLS
+  // operators with per-cell data: the cell id of every step is staged beside the step words (third bulk copy) instead of being
+  // read from global memory inside the walk
+  uint32_t* cells_s = steps_s + step_cap + C::PAD;
+#endif
 
   const int t = threadIdx.x;
   // Persistent form (B2F_FAN_PERSIST, launch_assemble_layout): the grid holds one CTA per resident slot of the device and
@@ -1086,11 +1102,15 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // the previous tile's reads of the staging areas (generic proxy) are ordered before the bulk copies that overwrite
     // them (async proxy); the __syncthreads at the end of the previous iteration has collected those reads
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    mbar_expect_tx(bar, (uint32_t)(ncols_cp + nstep_cp) * 4u);
+    mbar_expect_tx(bar, (uint32_t)(ncols_cp + nstep_cp + ((B2F_FAN_STAGE_CELLS && Op::NEEDS_CELL) ? nstep_cp : 0)) * 4u);
     if (ncols_cp > 0)
       tma_load_1d_stream(cols_s, A.columns + vbeg_al, (uint32_t)ncols_cp * 4u, bar);
     if (nstep_cp > 0)
       tma_load_1d_stream(steps_s, A.fan_steps + abeg_al, (uint32_t)nstep_cp * 4u, bar);
+#if B2F_FAN_STAGE_CELLS
+    if (Op::NEEDS_CELL && nstep_cp > 0)
+      tma_load_1d_stream(cells_s, A.fan_cell + abeg_al, (uint32_t)nstep_cp * 4u, bar);
+#endif
   }
   const int nval = (vend - vbeg) * BS2;
 #if B2F_FAN_BULK_STORE
@@ -1205,7 +1225,13 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     const int32_t* cols = cols_s + (rb - vbeg_al) - dl;
     const uint32_t* st = steps_s + (qb - abeg_al);
 #endif
+#if B2F_FAN_STAGE_CELLS
+    const uint32_t* cl = cells_s + (qb - abeg_al);
+#define B2F_CELL_AT(ptr) (*(ptr))
+#else
     const uint32_t* cl = A.fan_cell + qb;
+#define B2F_CELL_AT(ptr) __ldg(ptr)
+#endif
     // bring the coordinates of every neighbour of the row towards the SM now, in one round trip, instead of meeting
     // the misses one by one along the walk
     for (int x = 1; x < k; ++x)
@@ -1230,11 +1256,11 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       double cv = 0.0, cvn = 0.0;
       uint32_t cidn = 0;
       if constexpr (Op::NEEDS_CELL) {
-        cv = op.cell_value((long long)__ldg(cl));
+        cv = op.cell_value((long long)B2F_CELL_AT(cl));
         if (nstep > 1)
-          cvn = op.cell_value((long long)__ldg(cl + 1));
+          cvn = op.cell_value((long long)B2F_CELL_AT(cl + 1));
         if (nstep > 2)
-          cidn = __ldg(cl + 2);
+          cidn = B2F_CELL_AT(cl + 2);
       }
       bool more = false;
       // F: set that receives the entering vertex C; X = F+1, Y = F+2 hold the window; LY: Y leaves (else X).
@@ -1363,7 +1389,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
           if (p + 2 < nstep)
             cvn = op.cell_value((long long)cidn);
           if (p + 3 < nstep)
-            cidn = __ldg(cl + p + 3);
+            cidn = B2F_CELL_AT(cl + p + 3);
         }
       }
       // final window: every set but the free one of the last step
@@ -1388,11 +1414,23 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     load_xyz(CV, cols[w & 1023u], Xn);
     // AA: the address chain of the gather (step word -> column id -> coordinates) is spread over three steps: the word is read
     // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago.  Two
-    // registers; the instantiations that have none to spare (reorder mode, fused source term, per-cell data) keep the short chain.
-    constexpr bool AA = B2F_FAN_ADDR_AHEAD && !PERM && !SRC && !Op::NEEDS_CELL;
-    uint32_t w1 = 0u, w2 = 0u;
+    // registers; the instantiations that have none to spare (reorder mode, fused source term) keep the short chain.
+    constexpr bool AA = B2F_FAN_ADDR_AHEAD && !PERM && !SRC && (!Op::NEEDS_CELL || B2F_FAN_AA_CELL);
+    // D2 (HeatTet: 16 warps per SM, registers to spare): the coordinates are gathered TWO steps ahead into two register sets that
+    // alternate with the halves of the loop (Xn: even steps, Xo: odd steps); the words then run four steps ahead, the column id three.
+    constexpr bool D2 = AA && B2F_FAN_DEPTH2 && Op::NEEDS_CELL && NV == 4;
+    uint32_t w1 = 0u, w2 = 0u, w3 = 0u;
     int32_t cn = 0;
-    if constexpr (AA) {
+    double Xo[3] = { 0.0, 0.0, 0.0 };
+    if constexpr (D2) {
+      w1 = nstep > 1 ? st[1] : 0u;
+      w2 = nstep > 2 ? st[2] : 0u;
+      w3 = nstep > 3 ? st[3] : 0u;
+      if (nstep > 1)
+        load_xyz(CV, cols[w1 & 1023u], Xo);
+      cn = nstep > 2 ? cols[w2 & 1023u] : 0;
+    }
+    else if constexpr (AA) {
       w1 = nstep > 1 ? st[1] : 0u;
       w2 = nstep > 2 ? st[2] : 0u;
       cn = nstep > 1 ? cols[w1 & 1023u] : 0;
@@ -1405,11 +1443,11 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     double cv = 0.0, cvn = 0.0;
     uint32_t cidn = 0;
     if constexpr (Op::NEEDS_CELL) {
-      cv = op.cell_value((long long)__ldg(cl));
+      cv = op.cell_value((long long)B2F_CELL_AT(cl));
       if (nstep > 1)
-        cvn = op.cell_value((long long)__ldg(cl + 1));
+        cvn = op.cell_value((long long)B2F_CELL_AT(cl + 1));
       if (nstep > 2)
-        cidn = __ldg(cl + 2);
+        cidn = B2F_CELL_AT(cl + 2);
     }
     auto next_cell = [&](int pp) { // called after step pp
       if constexpr (Op::NEEDS_CELL) {
@@ -1417,7 +1455,7 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         if (pp + 2 < nstep)
           cvn = op.cell_value((long long)cidn);
         if (pp + 3 < nstep)
-          cidn = __ldg(cl + pp + 3);
+          cidn = B2F_CELL_AT(cl + pp + 3);
       }
     };
     auto enter = [&](double(&e)[3]) {
@@ -1440,7 +1478,18 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
       // step p: P enters (Q is the newest)
       uint32_t wc = w;
       enter(eP);
-      if constexpr (AA) {
+      if constexpr (D2) {
+        if (p + 2 < nstep)
+          load_xyz(CV, cn, Xn);
+        if (p + 3 < nstep)
+          cn = cols[w3 & 1023u];
+        w = w1;
+        w1 = w2;
+        w2 = w3;
+        if (p + 4 < nstep)
+          w3 = st[p + 4];
+      }
+      else if constexpr (AA) {
         if (p + 1 < nstep)
           load_xyz(CV, cn, Xn);
         if (p + 2 < nstep)
@@ -1461,8 +1510,25 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         break;
       // step p: Q enters (P is the newest)
       wc = w;
-      enter(eQ);
-      if constexpr (AA) {
+      if constexpr (D2) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+          eQ[d] = Xo[d] - X0[d];
+        if (p + 2 < nstep)
+          load_xyz(CV, cn, Xo);
+        if (p + 3 < nstep)
+          cn = cols[w3 & 1023u];
+        w = w1;
+        w1 = w2;
+        w2 = w3;
+        if (p + 4 < nstep)
+          w3 = st[p + 4];
+      }
+      else
+        enter(eQ);
+      if constexpr (D2) {
+      }
+      else if constexpr (AA) {
         if (p + 1 < nstep)
           load_xyz(CV, cn, Xn);
         if (p + 2 < nstep)
@@ -1664,7 +1730,7 @@ inline cudaError_t launch_assemble_layout(const AssembleArgs& A, const Op& op, i
     }
     acc_blocks = (acc_blocks + 3) & ~3;
     step_cap = (step_cap + 3) & ~3;
-    const size_t smem = C::smem_bytes(acc_blocks, step_cap);
+    const size_t smem = C::smem_bytes(acc_blocks, step_cap) + ((B2F_FAN_STAGE_CELLS && Op::NEEDS_CELL) ? (size_t)(step_cap + C::PAD) * sizeof(uint32_t) : 0);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
       return e;

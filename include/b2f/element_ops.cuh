@@ -52,6 +52,11 @@ namespace b2f {
 // Heat rows: diagonal from the row itself (off-diagonal sum + mass sum) instead of computing it per step.  Parity-exact to
 // 1e-12 but measured slower on B200 (heat3d 1.58 vs 1.51 ms, heat2d 1.50 vs 1.39 ms: the mass term per step costs more
 // than the diagonal it removes), so it is off; -DB2F_HEAT_ROW_SUM=1 builds it for A/B runs.
+// HeatTet: with the cell ids of the steps staged in shared memory (B2F_FAN_STAGE_CELLS) 4 CTAs of 128 rows fit an SM, so the
+// kernel is compiled for 16 warps (up to 128 registers: 107 used, no spill)
+#ifndef B2F_FAN_WARPS_HEATTET
+#define B2F_FAN_WARPS_HEATTET 16
+#endif
 #ifndef B2F_HEAT_ROW_SUM
 #define B2F_HEAT_ROW_SUM 0
 #endif
@@ -294,12 +299,15 @@ struct ElasticityTet
 };
 
 // modules/heat/FemModule.cc:678-770: lambda_cell * (dPhi_a.dPhi_b) * 0.25/area + (area/12)*(1+delta_ab)/dt, signed area (:606-612).
-struct HeatTri
+// CELL: the conductivity is a per-cell array (the reference's m_cell_lambda); false: one value for the mesh - that instantiation
+// needs no cell id, so the walk reads neither the plan's cell stream nor the array.
+template <bool CELL>
+struct HeatTriT
 {
   static constexpr int NV = 3, BS = 1;
   static constexpr int FAN_WARPS_PER_SM = 24; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
-  static constexpr bool NEEDS_CELL = true; // per-cell conductivity
+  static constexpr bool NEEDS_CELL = CELL; // per-cell conductivity
   static constexpr bool LINEAR_POST = false;
   static constexpr bool ROW_SUM_MASS = B2F_HEAT_ROW_SUM != 0; // row 0 = zero-row-sum stiffness + m (off the diagonal) / + 2 m (on it): see assemble.cuh
   double lambda, inv_dt;
@@ -311,7 +319,14 @@ struct HeatTri
     double m; // area / 12 / dt
   };
   __device__ __forceinline__ double mass(const Geom& G) const { return G.m; }
-  __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
+  // unconditional load in the per-cell form: a select on the pointer would wait for the load where it is issued and undo the prefetch
+  __device__ __forceinline__ double cell_value(long long cell) const
+  {
+    if constexpr (CELL)
+      return __ldg(cell_lambda + cell);
+    else
+      return lambda;
+  }
   __device__ __forceinline__ Geom prepare(const double (&X)[3][3], long long cell) const { return prepare_oriented(X, cell_value(cell), false); }
   // odd: X lists the cell's vertices in an odd permutation of the cell's own order (the signed area flips back)
   __device__ __forceinline__ Geom prepare_oriented(const double (&X)[3][3], double lam, bool odd) const
@@ -319,7 +334,7 @@ struct HeatTri
     Geom G;
     G.t = tri_geometry(X);
     const double area = odd ? -0.5 * G.t.a2 : 0.5 * G.t.a2;
-    G.ks = lam * 0.25 / area;
+    G.ks = (CELL ? lam : lambda) * 0.25 / area;
     G.m = area * (1.0 / 12.0) * inv_dt;
     return G;
   }
@@ -331,12 +346,13 @@ struct HeatTri
 };
 
 // 3D twin of the heat operator: lambda*V*(grad.grad) + (V/20)*(1+delta_ab)/dt.
-struct HeatTet
+template <bool CELL>
+struct HeatTetT
 {
   static constexpr int NV = 4, BS = 1;
-  static constexpr int FAN_WARPS_PER_SM = 20; // occupancy the fan kernel is compiled for (register budget)
+  static constexpr int FAN_WARPS_PER_SM = CELL ? B2F_FAN_WARPS_HEATTET : 20; // occupancy the fan kernel is compiled for (register budget)
   static constexpr bool ROW_SUM_ZERO = false; // element matrices have zero row sums (constants in the kernel)
-  static constexpr bool NEEDS_CELL = true;
+  static constexpr bool NEEDS_CELL = CELL;
   static constexpr bool LINEAR_POST = false;
   static constexpr bool ROW_SUM_MASS = B2F_HEAT_ROW_SUM != 0;
   double lambda, inv_dt;
@@ -347,13 +363,20 @@ struct HeatTet
     double ks, m;
   };
   __device__ __forceinline__ double mass(const Geom& G) const { return G.m; }
-  __device__ __forceinline__ double cell_value(long long cell) const { return cell_lambda ? __ldg(cell_lambda + cell) : lambda; }
+  // unconditional load in the per-cell form: a select on the pointer would wait for the load where it is issued and undo the prefetch
+  __device__ __forceinline__ double cell_value(long long cell) const
+  {
+    if constexpr (CELL)
+      return __ldg(cell_lambda + cell);
+    else
+      return lambda;
+  }
   __device__ __forceinline__ Geom prepare(const double (&X)[4][3], long long cell) const { return finish(tet_geometry(X), cell_value(cell), false); }
   __device__ __forceinline__ Geom finish(const TetGeom& T, double lam, bool) const
   {
     Geom G;
     G.t = T;
-    G.ks = lam * G.t.s;
+    G.ks = (CELL ? lam : lambda) * G.t.s;
     G.m = G.t.vol6 * (1.0 / 120.0) * inv_dt;
     return G;
   }
@@ -363,5 +386,10 @@ struct HeatTet
     out[0] = k + (a == b ? 2.0 * G.m : G.m);
   }
 };
+
+using HeatTri = HeatTriT<true>;
+using HeatTet = HeatTetT<true>;
+using HeatTriUniform = HeatTriT<false>;
+using HeatTetUniform = HeatTetT<false>;
 
 } // namespace b2f
