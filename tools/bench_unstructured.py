@@ -68,7 +68,7 @@ def measure(name, cells, coords, reorder, steps, warmup):
            "row_length_max": int(k.max()), "ms_per_step": round(ms, 4), "gnnz_per_s": round(nnzb / (ms * 1e-3) / 1e9, 2), "algorithmic_bytes": b_alg,
            "achieved_gbs": round(b_alg / (ms * 1e-3) / 1e9, 1), "frac_of_measured_hbm_peak": round(b_alg / (ms * 1e-3) / 1e9 / peak(), 4), "sparsity_build_ms": round(sparsity_ms, 2),
            "sparsity_by_lists": st["sparsity_by_lists"], "fan_steps": st["fan_steps"], "gather_fallback_tiles": st["gather_fallback_tiles"],
-           "columns_not_found": st["columns_not_found"], "parity_sample": {q: parity[q] for q in ("rows", "entries", "max_rel", "over_1e-12", "host_fp64_same_formula_max_rel", "columns_missing")}}
+           "columns_not_found": st["columns_not_found"], "parity_sample": {q: parity[q] for q in ("rows", "entries", "max_rel", "over_1e-12", "vs_extended_precision_max_rel", "columns_missing")}}
     print(json.dumps(out), flush=True)
     del bsr
     torch.cuda.empty_cache()
