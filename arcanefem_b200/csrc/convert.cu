@@ -7,7 +7,6 @@
 #include "b2f/assemble.cuh"
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
-#include <type_traits>
 
 namespace b2f {
 
@@ -38,14 +37,12 @@ namespace {
       cols[off + q] = columns[rb + q / BS] * BS + (q % BS);
   }
 
-  // LANES (8 or 16) lanes per scalar row: 16 when the rows are long enough to fill them (3D: 15 entries per row, one
-  // round of loads per row instead of two), 8 otherwise
-  template <int BS, bool PER_BLOCK, int LANES>
+  template <int BS, bool PER_BLOCK>
   __global__ void __launch_bounds__(256) k_spmv(const int32_t* __restrict__ row_index, const int32_t* __restrict__ columns, const double* __restrict__ values,
                                                 long long nb_node, const double* __restrict__ x, double* __restrict__ y)
   {
-    const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
-    const int l = threadIdx.x & (LANES - 1);
+    const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int l = threadIdx.x & 7;
     const bool valid = g < nb_node * BS;
     double s = 0.0;
     if (valid) {
@@ -53,13 +50,11 @@ namespace {
       const int i = (int)(g % BS);
       const int32_t rb = row_index[br];
       const int k = row_index[br + 1] - rb;
-      for (int q = l; q < k * BS; q += LANES) {
+      for (int q = l; q < k * BS; q += 8) {
         const int xb = q / BS, j = q % BS;
         s += values[value_index<BS, PER_BLOCK>(rb, k, xb, i, j)] * __ldg(x + (long long)columns[rb + xb] * BS + j);
       }
     }
-    if (LANES == 16)
-      s += __shfl_xor_sync(0xffffffffu, s, 8);
     s += __shfl_xor_sync(0xffffffffu, s, 4);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     s += __shfl_xor_sync(0xffffffffu, s, 1);
@@ -311,34 +306,23 @@ int spmv(b2f_context_s* h, const double* x, double* y, cudaStream_t s)
   const int32_t* ri = h->row_index.as<int32_t>();
   const int32_t* co = h->columns.as<int32_t>();
   const double* va = h->values.as<double>();
+  const unsigned grid = grid_for(nrow * 8, 256);
   const bool pb = h->per_block;
-  const bool wide = h->nb_nz > 10 * nrow; // mean scalar row length above 10: 16 lanes per row
-  const unsigned grid = grid_for(nrow * (wide ? 16 : 8), 256);
-  auto launch = [&](auto bs_c, auto pb_c) {
-    constexpr int BS = decltype(bs_c)::value;
-    constexpr bool PB = decltype(pb_c)::value;
-    if (wide)
-      k_spmv<BS, PB, 16><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
-    else
-      k_spmv<BS, PB, 8><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
-  };
-  using T = std::true_type;
-  using F = std::false_type;
   switch (h->bs) {
   case 1:
-    launch(std::integral_constant<int, 1>{}, T{});
+    k_spmv<1, true><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
     break;
   case 2:
     if (pb)
-      launch(std::integral_constant<int, 2>{}, T{});
+      k_spmv<2, true><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
     else
-      launch(std::integral_constant<int, 2>{}, F{});
+      k_spmv<2, false><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
     break;
   case 3:
     if (pb)
-      launch(std::integral_constant<int, 3>{}, T{});
+      k_spmv<3, true><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
     else
-      launch(std::integral_constant<int, 3>{}, F{});
+      k_spmv<3, false><<<grid, 256, 0, s>>>(ri, co, va, nn, x, y);
     break;
   }
   B2F_CUDA(cudaGetLastError());
