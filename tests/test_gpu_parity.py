@@ -364,6 +364,16 @@ def test_error_conventions():
     with pytest.raises(fem.B2FError) as e:
         b3.matrix().toCsr()
     assert e.value.status == -4
+    # the multi-GPU entry points refuse a handle without an exchange plan (b2f_ghost_plan), also the host-buffer one
+    import ctypes as C
+    from arcanefem_b200 import _lib
+    lib = _lib.load_library()
+    d = fem.Operator.laplace().desc(False)
+    host = torch.zeros(coords.shape[0] * 3, dtype=torch.float64).pin_memory()
+    assert lib.b2f_assemble_exchange(bsr._h, C.byref(d), None, None) == -4
+    assert lib.b2f_assemble_exchange_host(bsr._h, C.byref(d), None, C.c_void_p(host.data_ptr()), None, None) == -4
+    assert lib.b2f_assemble_exchange_host(bsr._h, C.byref(d), None, None, None, None) == -1
+    assert lib.b2f_ghost_exchange(bsr._h, None, None) == -4
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
