@@ -30,7 +30,7 @@ extern "C" {
 #endif
 
 #define B2F_VERSION_MAJOR 0
-#define B2F_VERSION_MINOR 2
+#define B2F_VERSION_MINOR 3
 
 typedef struct b2f_context_s* b2f_handle;
 typedef void* b2f_stream; /* cudaStream_t */
