@@ -657,6 +657,10 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_DEPTH2
 #define B2F_FAN_DEPTH2 1
 #endif
+// 1: the per-cell value of the next step is requested at the top of a step, with the coordinate gathers, not at its end
+#ifndef B2F_FAN_CELL_EARLY
+#define B2F_FAN_CELL_EARLY 1
+#endif
 #ifndef B2F_FAN_AA_CELL
 #define B2F_FAN_AA_CELL 1
 #endif
@@ -1503,8 +1507,14 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         B2F_NEXT_WORD(p)
         load_xyz(CV, cols[w & 1023u], Xn);
       }
+#if B2F_FAN_CELL_EARLY
+      if (p > 0)
+        next_cell(p - 1); // the per-cell value of this step moves in, the next one is requested together with the coordinates above
+#endif
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, CV, X0, acc, cols, k, wc, fmask, cv, eQ, accQ, sQ, eO, accO, sO, m, eP, accP, sP, diag, measure);
+#if !B2F_FAN_CELL_EARLY
       next_cell(p);
+#endif
       newest_is_Q = false;
       if (++p >= nstep)
         break;
@@ -1542,8 +1552,13 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
         B2F_NEXT_WORD(p)
         load_xyz(CV, cols[w & 1023u], Xn);
       }
+#if B2F_FAN_CELL_EARLY
+      next_cell(p - 1);
+#endif
       fan_step<Op, PER_BLOCK, DIAG_BY_ROW_SUM || POST, SRC>(op, CV, X0, acc, cols, k, wc, fmask, cv, eP, accP, sP, eO, accO, sO, m, eQ, accQ, sQ, diag, measure);
+#if !B2F_FAN_CELL_EARLY
       next_cell(p);
+#endif
       newest_is_Q = true;
       if (++p >= nstep)
         break;
