@@ -661,6 +661,10 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_CELL_EARLY
 #define B2F_FAN_CELL_EARLY 1
 #endif
+// 1: the outer-product operators on tets (elasticity 3D: 5 warps per SM, registers to spare) gather two steps ahead too
+#ifndef B2F_FAN_DEPTH2_POST
+#define B2F_FAN_DEPTH2_POST 1
+#endif
 #ifndef B2F_FAN_AA_CELL
 #define B2F_FAN_AA_CELL 1
 #endif
@@ -1420,9 +1424,9 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // three steps ahead, the column id two, so every load of a step starts from registers that were filled a step ago.  Two
     // registers; the instantiations that have none to spare (reorder mode, fused source term) keep the short chain.
     constexpr bool AA = B2F_FAN_ADDR_AHEAD && !PERM && !SRC && (!Op::NEEDS_CELL || B2F_FAN_AA_CELL);
-    // D2 (HeatTet: 16 warps per SM, registers to spare): the coordinates are gathered TWO steps ahead into two register sets that
+    // D2 (HeatTet at 16 warps per SM, ElasticityTet at 5: registers to spare): the coordinates are gathered TWO steps ahead into two register sets that
     // alternate with the halves of the loop (Xn: even steps, Xo: odd steps); the words then run four steps ahead, the column id three.
-    constexpr bool D2 = AA && B2F_FAN_DEPTH2 && Op::NEEDS_CELL && NV == 4;
+    constexpr bool D2 = AA && B2F_FAN_DEPTH2 && (Op::NEEDS_CELL || (B2F_FAN_DEPTH2_POST && POST)) && NV == 4;
     uint32_t w1 = 0u, w2 = 0u, w3 = 0u;
     int32_t cn = 0;
     double Xo[3] = { 0.0, 0.0, 0.0 };
