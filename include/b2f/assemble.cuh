@@ -665,6 +665,10 @@ __device__ __forceinline__ auto tri_prepare(const Op& op, const double (&X0)[3],
 #ifndef B2F_FAN_DEPTH2_POST
 #define B2F_FAN_DEPTH2_POST 1
 #endif
+// 1: HeatTet keeps the per-cell value two steps ahead (see CD2 in k_node_fan)
+#ifndef B2F_FAN_CELL_DEPTH2
+#define B2F_FAN_CELL_DEPTH2 1
+#endif
 #ifndef B2F_FAN_AA_CELL
 #define B2F_FAN_AA_CELL 1
 #endif
@@ -1450,15 +1454,40 @@ __global__ void __launch_bounds__(FanCfg<Op>::ROWS, Op::FAN_WARPS_PER_SM * 32 / 
     // per-cell datum of the operator (heat conductivity): cell id fetched two steps ahead, its value one step ahead
     double cv = 0.0, cvn = 0.0;
     uint32_t cidn = 0;
+#if B2F_FAN_CELL_DEPTH2
+    // HeatTet (registers to spare): the per-cell value runs two steps ahead (cv <- cvn <- cvn2), the cell id three
+    constexpr bool CD2 = Op::NEEDS_CELL && NV == 4;
+    double cvn2 = 0.0;
+#else
+    constexpr bool CD2 = false;
+#endif
     if constexpr (Op::NEEDS_CELL) {
       cv = op.cell_value((long long)B2F_CELL_AT(cl));
       if (nstep > 1)
         cvn = op.cell_value((long long)B2F_CELL_AT(cl + 1));
-      if (nstep > 2)
+      if constexpr (CD2) {
+#if B2F_FAN_CELL_DEPTH2
+        if (nstep > 2)
+          cvn2 = op.cell_value((long long)B2F_CELL_AT(cl + 2));
+        if (nstep > 3)
+          cidn = B2F_CELL_AT(cl + 3);
+#endif
+      }
+      else if (nstep > 2)
         cidn = B2F_CELL_AT(cl + 2);
     }
     auto next_cell = [&](int pp) { // called after step pp
-      if constexpr (Op::NEEDS_CELL) {
+      if constexpr (CD2) {
+#if B2F_FAN_CELL_DEPTH2
+        cv = cvn;
+        cvn = cvn2;
+        if (pp + 3 < nstep)
+          cvn2 = op.cell_value((long long)cidn);
+        if (pp + 4 < nstep)
+          cidn = B2F_CELL_AT(cl + pp + 4);
+#endif
+      }
+      else if constexpr (Op::NEEDS_CELL) {
         cv = cvn;
         if (pp + 2 < nstep)
           cvn = op.cell_value((long long)cidn);
